@@ -25,6 +25,9 @@
 extern "C" {
 #endif
 
+/* src/util/pipelines/pipelines.h:10 */
+enum { VPB_MAX_PIPELINE = 272 };
+
 /* ---- particles: src/species_advance/species_advance_aos.h:21-52 ---------- */
 
 typedef struct vpb_particle {

@@ -1,0 +1,131 @@
+/* vpic_b200.h -- C ABI of libvpic_b200.so, the B200 (sm_100a) implementation
+ * of VPIC's per-step PIC hot path.
+ *
+ * Part 1 exports THE REFERENCE'S OWN SYMBOLS for the path (same name, same
+ * argument meaning, same error behaviour), so the library links underneath the
+ * unmodified vpic_simulation driver and input decks in place of the
+ * reference's species_advance / sf_interface / field_advance translation
+ * units.  Struct types are our byte-compatible restatements
+ * from abi.h; in C the type names are irrelevant to the ABI.
+ *
+ * Part 2 is the small control surface a host needs on top: coherence between
+ * the host structs and the device mirrors, deposit mode, multi-GPU comm.
+ *
+ * Part 3 is a stand-alone host layer (grid / species / array constructors and
+ * a time step) mirroring the reference's constructors, for programs that do
+ * not link the reference at all (bench.py, tests).
+ *
+ * All entry points must be called from one host thread (the reference's rule:
+ * src/util/pipelines/pipelines_thread.c:529).  Failures follow the reference:
+ * print "Error at file(line)[rank]: ..." and exit(1); soft failures warn.
+ */
+#ifndef VPIC_B200_H
+#define VPIC_B200_H
+
+#include "vpic_b200/abi.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ======================= Part 1: reference symbols ======================== */
+
+/* src/species_advance/species_advance.h:65-66 */
+void sort_p( vpb_species_t * sp );
+/* src/species_advance/species_advance.h:73-76 */
+void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, const vpb_interpolator_array_t * ia );
+/* src/species_advance/species_advance.h:118-120 */
+double energy_p( const vpb_species_t * sp, const vpb_interpolator_array_t * ia );
+/* src/species_advance/species_advance.h:88-104 */
+void center_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia );
+void uncenter_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia );
+/* src/sf_interface/sf_interface.h:99-101 */
+void load_interpolator_array( vpb_interpolator_array_t * ia, const vpb_field_array_t * fa );
+/* src/sf_interface/sf_interface.h:147-148 */
+void clear_accumulator_array( vpb_accumulator_array_t * aa );
+/* src/sf_interface/sf_interface.h:158-159 */
+void reduce_accumulator_array( vpb_accumulator_array_t * aa );
+/* src/sf_interface/sf_interface.h:172-174 */
+void unload_accumulator_array( vpb_field_array_t * fa, const vpb_accumulator_array_t * aa );
+/* src/boundary/boundary.h:35-39 (pbc_list: opaque particle_bc_t list, may be NULL) */
+void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa );
+
+/* src/field_advance/field_advance.h:233-236.  Creates a field array whose
+   kernel table (field_advance.h:170-218) points at the functions below. */
+vpb_field_array_t * new_standard_field_array( vpb_grid_t * g, const vpb_material_t * m_list, float damp );
+void delete_field_array( vpb_field_array_t * fa );
+
+/* The kernel-table entries themselves (global symbols: the reference
+   checkpoints function pointers by name, src/field_advance/field_advance.c:17-58). */
+void vpic_b200_delete_fa( vpb_field_array_t * fa );
+void vpic_b200_advance_b( vpb_field_array_t * fa, float frac );       /* advance_b.cc:10-19     */
+void vpic_b200_advance_e( vpb_field_array_t * fa, float frac );       /* advance_e.cc:10-25     */
+void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ); /* energy_f.c:12-23       */
+void vpic_b200_clear_jf( vpb_field_array_t * fa );                    /* sfa.c:231-237          */
+void vpic_b200_synchronize_jf( vpb_field_array_t * fa );              /* remote.c:417-508       */
+void vpic_b200_clear_rhof( vpb_field_array_t * fa );                  /* sfa.c:239-245          */
+
+/* ======================= Part 2: control surface ========================== */
+
+enum { VPB_COHERENCE_STRICT = 0,   /* every call: host structs in, host structs out  */
+       VPB_COHERENCE_RESIDENT = 1  /* state lives on the device between calls; the
+                                      host syncs explicitly with the calls below     */ };
+enum { VPB_DEPOSIT_FAST = 0,       /* warp-reduced + atomics, FMA allowed            */
+       VPB_DEPOSIT_PARITY = 1      /* reference summation order, bit-exact currents  */ };
+
+int  vpic_b200_init( int device, int world_rank, int world_size ); /* returns SM count */
+void vpic_b200_finalize( void );
+void vpic_b200_set_coherence( int mode );
+void vpic_b200_set_deposit_mode( int mode );
+int  vpic_b200_abi_check( int sizeof_interpolator, int sizeof_accumulator, int sizeof_field,
+                          int sizeof_particle, int sizeof_grid, int sizeof_species ); /* 0 = ok */
+/* obj = any species_t / field_array_t / interpolator_array_t / accumulator_array_t */
+void vpic_b200_sync_to_host( void * obj );     /* device -> host struct arrays      */
+void vpic_b200_sync_from_host( void * obj );   /* host struct arrays -> device       */
+void vpic_b200_forget( void * obj );           /* drop the mirror (before free())    */
+void vpic_b200_device_synchronize( void );
+long long vpic_b200_launch_count( void );      /* kernels launched so far            */
+void * vpic_b200_stream( void );               /* cudaStream_t the kernels run on    */
+/* Device pointers of a mirror, for tests/benchmarks: which = 0 particles,
+   1 movers, 2 partition (species); 0 SoA planes (field); 0 coefficients
+   (interpolator); 0 accumulator. */
+void * vpic_b200_device_ptr( void * obj, int which );
+
+/* Synthetic loader used by bench.py: fills sp with ppc particles per cell,
+   uniform in each voxel, Maxwellian momenta (vth in units of c), weight w,
+   from a counter-based generator, directly on the device (no host copy). */
+void vpic_b200_load_uniform_maxwellian( vpb_species_t * sp, int ppc, float vth, float w, uint64_t seed );
+
+/* ======================= Part 3: stand-alone host layer =================== */
+
+/* src/grid/grid_structors.c, partition.c:25-182, ops.c:18-211 */
+vpb_grid_t * vpic_b200_new_grid( void );
+void vpic_b200_delete_grid( vpb_grid_t * g );
+void vpic_b200_partition_periodic_box( vpb_grid_t * g, double gx0, double gy0, double gz0,
+                                       double gx1, double gy1, double gz1,
+                                       int gnx, int gny, int gnz, int gpx, int gpy, int gpz );
+void vpic_b200_partition_absorbing_box( vpb_grid_t * g, double gx0, double gy0, double gz0,
+                                        double gx1, double gy1, double gz1,
+                                        int gnx, int gny, int gnz, int gpx, int gpy, int gpz, int pbc );
+void vpic_b200_partition_metal_box( vpb_grid_t * g, double gx0, double gy0, double gz0,
+                                    double gx1, double gy1, double gz1,
+                                    int gnx, int gny, int gnz, int gpx, int gpy, int gpz );
+void vpic_b200_set_fbc( vpb_grid_t * g, int boundary, int fbc );
+void vpic_b200_set_pbc( vpb_grid_t * g, int boundary, int pbc );
+/* src/species_advance/species_advance.c:102-146; host_arrays=0 keeps p/pm
+   device-only (sp->p == NULL), for problems larger than host memory. */
+vpb_species_t * vpic_b200_new_species( const char * name, float q, float m, size_t max_np, size_t max_nm,
+                                       int sort_interval, int sort_out_of_place, vpb_grid_t * g, int host_arrays );
+void vpic_b200_delete_species( vpb_species_t * sp );
+/* src/sf_interface/interpolator_array.cc:18-50, accumulator_array.c:52-73 */
+vpb_interpolator_array_t * vpic_b200_new_interpolator_array( vpb_grid_t * g );
+void vpic_b200_delete_interpolator_array( vpb_interpolator_array_t * ia );
+vpb_accumulator_array_t * vpic_b200_new_accumulator_array( vpb_grid_t * g, int n_pipeline );
+void vpic_b200_delete_accumulator_array( vpb_accumulator_array_t * aa );
+/* one-material list helper: src/material/material.c */
+vpb_material_t * vpic_b200_new_material( const char * name, float eps, float mu, float sigma );
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VPIC_B200_H */

@@ -1,0 +1,521 @@
+// vpb_fields.cu -- Yee FDTD kernels on the device SoA field planes.
+//   advance_b   reference: src/field_advance/standard/pipeline/advance_b_pipeline.{h,cc}
+//   advance_e   reference: .../pipeline/{vacuum_,}advance_e_pipeline.{h,cc}
+//   energy_f    reference: .../pipeline/{vacuum_,}energy_f_pipeline.{h,c}
+//   ghost / boundary planes: src/field_advance/standard/{local,remote}.c
+// Compiled with -fmad=false: every expression rounds like the reference.
+#include "vpb_runtime.h"
+
+namespace vpb {
+
+// ---------------------------------------------------------------------------
+// Bulk stencils.  One thread per lattice point of the (nx+1)(ny+1)(nz+1) block
+// that holds every updated component; x fastest => unit-stride plane access.
+// advance_b: 24 B read + 12 B written per cell = 36 B.
+// ---------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+k_advance_b( float * __restrict__ f, GridDev g, float px, float py, float pz ) {
+  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
+  const int n = mx*my*mz;
+  const size_t P = (size_t)g.nvp;
+  const float * __restrict__ ex = f + F_EX*P, * __restrict__ ey = f + F_EY*P, * __restrict__ ez = f + F_EZ*P;
+  float * __restrict__ cbx = f + F_CBX*P, * __restrict__ cby = f + F_CBY*P, * __restrict__ cbz = f + F_CBZ*P;
+  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
+    const int x = i % mx, t = i / mx, y = t % my, z = t / my;      // 0-based
+    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
+    const bool inx = x<g.nx, iny = y<g.ny, inz = z<g.nz;
+    const float ex0 = ex[v], ey0 = ey[v], ez0 = ez[v];
+    if( iny && inz ) cbx[v] -= ( py*( ez[v+g.sy]-ez0 ) - pz*( ey[v+g.sz]-ey0 ) );
+    if( inz && inx ) cby[v] -= ( pz*( ex[v+g.sz]-ex0 ) - px*( ez[v+1]   -ez0 ) );
+    if( inx && iny ) cbz[v] -= ( px*( ey[v+1]   -ey0 ) - py*( ex[v+g.sy]-ex0 ) );
+  }
+}
+
+// advance_e, vacuum variant (one material): 48 B read + 24 B written per cell.
+struct VacuumCoef {
+  float decayx, drivex, decayy, drivey, decayz, drivez;
+  float px_muz, px_muy, py_mux, py_muz, pz_muy, pz_mux, damp, cj;
+};
+
+__global__ void __launch_bounds__(256)
+k_advance_e_vacuum( float * __restrict__ f, GridDev g, VacuumCoef c ) {
+  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
+  const int n = mx*my*mz;
+  const size_t P = (size_t)g.nvp;
+  const float * __restrict__ cbx = f + F_CBX*P, * __restrict__ cby = f + F_CBY*P, * __restrict__ cbz = f + F_CBZ*P;
+  const float * __restrict__ jfx = f + F_JFX*P, * __restrict__ jfy = f + F_JFY*P, * __restrict__ jfz = f + F_JFZ*P;
+  float * __restrict__ ex = f + F_EX*P, * __restrict__ ey = f + F_EY*P, * __restrict__ ez = f + F_EZ*P;
+  float * __restrict__ tx = f + F_TCAX*P, * __restrict__ ty = f + F_TCAY*P, * __restrict__ tz = f + F_TCAZ*P;
+  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
+    const int x = i % mx, t = i / mx, y = t % my, z = t / my;
+    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
+    const float bx0 = cbx[v], by0 = cby[v], bz0 = cbz[v];
+    if( x<g.nx ) {
+      const float tca = ( c.py_muz*( bz0 - cbz[v-g.sy] ) - c.pz_muy*( by0 - cby[v-g.sz] ) ) - c.damp*tx[v];
+      tx[v] = tca;
+      ex[v] = c.decayx*ex[v] + c.drivex*( tca - c.cj*jfx[v] );
+    }
+    if( y<g.ny ) {
+      const float tca = ( c.pz_mux*( bx0 - cbx[v-g.sz] ) - c.px_muz*( bz0 - cbz[v-1] ) ) - c.damp*ty[v];
+      ty[v] = tca;
+      ey[v] = c.decayy*ey[v] + c.drivey*( tca - c.cj*jfy[v] );
+    }
+    if( z<g.nz ) {
+      const float tca = ( c.px_muy*( by0 - cby[v-1] ) - c.py_mux*( bx0 - cbx[v-g.sy] ) ) - c.damp*tz[v];
+      tz[v] = tca;
+      ez[v] = c.decayz*ez[v] + c.drivez*( tca - c.cj*jfz[v] );
+    }
+  }
+}
+
+// advance_e with per-point materials (advance_e_pipeline.h:50-75).
+// mat planes: 0 ematx 1 ematy 2 ematz 3 nmat 4 fmatx 5 fmaty 6 fmatz 7 cmat.
+__global__ void __launch_bounds__(256)
+k_advance_e_material( float * __restrict__ f, const int16_t * __restrict__ mat,
+                      const vpb_material_coefficient_t * __restrict__ m, GridDev g,
+                      float px, float py, float pz, float damp, float cj ) {
+  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
+  const int n = mx*my*mz;
+  const size_t P = (size_t)g.nvp;
+  const float * cbx = f + F_CBX*P, * cby = f + F_CBY*P, * cbz = f + F_CBZ*P;
+  const float * jfx = f + F_JFX*P, * jfy = f + F_JFY*P, * jfz = f + F_JFZ*P;
+  float * ex = f + F_EX*P, * ey = f + F_EY*P, * ez = f + F_EZ*P;
+  float * tx = f + F_TCAX*P, * ty = f + F_TCAY*P, * tz = f + F_TCAZ*P;
+  const int16_t * emx = mat + 0*P, * emy = mat + 1*P, * emz = mat + 2*P;
+  const int16_t * fmx = mat + 4*P, * fmy = mat + 5*P, * fmz = mat + 6*P;
+  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
+    const int x = i % mx, t = i / mx, y = t % my, z = t / my;
+    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
+    const int vx = v-1, vy = v-g.sy, vz = v-g.sz;
+    if( x<g.nx ) {
+      const float tca = ( py*( cbz[v]*m[fmz[v]].rmuz - cbz[vy]*m[fmz[vy]].rmuz ) -
+                          pz*( cby[v]*m[fmy[v]].rmuy - cby[vz]*m[fmy[vz]].rmuy ) ) - damp*tx[v];
+      tx[v] = tca;
+      ex[v] = m[emx[v]].decayx*ex[v] + m[emx[v]].drivex*( tca - cj*jfx[v] );
+    }
+    if( y<g.ny ) {
+      const float tca = ( pz*( cbx[v]*m[fmx[v]].rmux - cbx[vz]*m[fmx[vz]].rmux ) -
+                          px*( cbz[v]*m[fmz[v]].rmuz - cbz[vx]*m[fmz[vx]].rmuz ) ) - damp*ty[v];
+      ty[v] = tca;
+      ey[v] = m[emy[v]].decayy*ey[v] + m[emy[v]].drivey*( tca - cj*jfy[v] );
+    }
+    if( z<g.nz ) {
+      const float tca = ( px*( cby[v]*m[fmy[v]].rmuy - cby[vx]*m[fmy[vx]].rmuy ) -
+                          py*( cbx[v]*m[fmx[v]].rmux - cbx[vy]*m[fmx[vy]].rmux ) ) - damp*tz[v];
+      tz[v] = tca;
+      ez[v] = m[emz[v]].decayz*ez[v] + m[emz[v]].drivez*( tca - cj*jfz[v] );
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// energy_f: float products, double sums.  Per-block partials in a fixed grid,
+// then one block adds them in index order => run-to-run deterministic.
+// ---------------------------------------------------------------------------
+
+constexpr int EN_BLOCK = 256;
+
+template<bool VACUUM>
+__global__ void __launch_bounds__(EN_BLOCK)
+k_energy_f( double * __restrict__ partial, const float * __restrict__ f, const int16_t * __restrict__ mat,
+            const vpb_material_coefficient_t * __restrict__ m, GridDev g ) {
+  const int ncell = g.nx*g.ny*g.nz;
+  const size_t P = (size_t)g.nvp;
+  const float * ex = f + F_EX*P, * ey = f + F_EY*P, * ez = f + F_EZ*P;
+  const float * bx = f + F_CBX*P, * by = f + F_CBY*P, * bz = f + F_CBZ*P;
+  double e[6] = {0,0,0,0,0,0};
+  float qepsx = 0, qepsy = 0, qepsz = 0, hrmux = 0, hrmuy = 0, hrmuz = 0;
+  if( VACUUM ) {
+    qepsx = 0.25*m->epsx; qepsy = 0.25*m->epsy; qepsz = 0.25*m->epsz;
+    hrmux = 0.50*m->rmux; hrmuy = 0.50*m->rmuy; hrmuz = 0.50*m->rmuz;
+  }
+  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<ncell; i += gridDim.x*blockDim.x ) {
+    const int x = i % g.nx, t = i / g.nx, y = t % g.ny, z = t / g.ny;
+    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
+    const int vx = v+1, vy = v+g.sy, vz = v+g.sz, vyz = v+g.sy+g.sz, vzx = v+g.sz+1, vxy = v+1+g.sy;
+    if( VACUUM ) {
+      e[0] += (double)( qepsx*( ex[v]*ex[v] + ex[vy]*ex[vy] + ex[vz]*ex[vz] + ex[vyz]*ex[vyz] ) );
+      e[1] += (double)( qepsy*( ey[v]*ey[v] + ey[vz]*ey[vz] + ey[vx]*ey[vx] + ey[vzx]*ey[vzx] ) );
+      e[2] += (double)( qepsz*( ez[v]*ez[v] + ez[vx]*ez[vx] + ez[vy]*ez[vy] + ez[vxy]*ez[vxy] ) );
+      e[3] += (double)( hrmux*( bx[v]*bx[v] + bx[vx]*bx[vx] ) );
+      e[4] += (double)( hrmuy*( by[v]*by[v] + by[vy]*by[vy] ) );
+      e[5] += (double)( hrmuz*( bz[v]*bz[v] + bz[vz]*bz[vz] ) );
+    } else {
+      const int16_t * emx = mat + 0*P, * emy = mat + 1*P, * emz = mat + 2*P;
+      const int16_t * fmx = mat + 4*P, * fmy = mat + 5*P, * fmz = mat + 6*P;
+      e[0] += 0.25*(double)( m[emx[v]].epsx*ex[v]*ex[v] + m[emx[vy]].epsx*ex[vy]*ex[vy] + m[emx[vz]].epsx*ex[vz]*ex[vz] + m[emx[vyz]].epsx*ex[vyz]*ex[vyz] );
+      e[1] += 0.25*(double)( m[emy[v]].epsy*ey[v]*ey[v] + m[emy[vz]].epsy*ey[vz]*ey[vz] + m[emy[vx]].epsy*ey[vx]*ey[vx] + m[emy[vzx]].epsy*ey[vzx]*ey[vzx] );
+      e[2] += 0.25*(double)( m[emz[v]].epsz*ez[v]*ez[v] + m[emz[vx]].epsz*ez[vx]*ez[vx] + m[emz[vy]].epsz*ez[vy]*ez[vy] + m[emz[vxy]].epsz*ez[vxy]*ez[vxy] );
+      e[3] += 0.5 *(double)( m[fmx[v]].rmux*bx[v]*bx[v] + m[fmx[vx]].rmux*bx[vx]*bx[vx] );
+      e[4] += 0.5 *(double)( m[fmy[v]].rmuy*by[v]*by[v] + m[fmy[vy]].rmuy*by[vy]*by[vy] );
+      e[5] += 0.5 *(double)( m[fmz[v]].rmuz*bz[v]*bz[v] + m[fmz[vz]].rmuz*bz[vz]*bz[vz] );
+    }
+  }
+  __shared__ double s[6][EN_BLOCK/32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+# pragma unroll
+  for( int c=0; c<6; c++ ) {
+    double vsum = e[c];
+    for( int o=16; o; o>>=1 ) vsum += __shfl_down_sync( 0xffffffffu, vsum, o );
+    if( lane==0 ) s[c][w] = vsum;
+  }
+  __syncthreads();
+  if( threadIdx.x<6 ) {
+    double vsum = 0;
+    for( int k=0; k<EN_BLOCK/32; k++ ) vsum += s[threadIdx.x][k];
+    partial[ (size_t)blockIdx.x*6 + threadIdx.x ] = vsum;
+  }
+}
+
+__global__ void k_sum_partials( double * __restrict__ out, const double * __restrict__ partial, int nblock, int ncomp, double scale ) {
+  const int c = threadIdx.x;
+  if( c>=ncomp ) return;
+  double s = 0;
+  for( int b=0; b<nblock; b++ ) s += partial[ (size_t)b*ncomp + c ];
+  out[c] = s*scale;
+}
+
+// ---------------------------------------------------------------------------
+// Boundary / ghost planes.  Every operation of local.c / remote.c works on the
+// plane normal to axis X (Y=(X+1)%3, Z=(X+2)%3) over two index sets:
+//   "B-kind" (tangential B):  comp Y on u:1..nY+1,w:1..nZ ; comp Z on u:1..nY,w:1..nZ+1
+//   "E-kind" (tangential E/J): comp Y on u:1..nY,w:1..nZ+1 ; comp Z on u:1..nY+1,w:1..nZ
+// (remote.c:16-41).  One thread per plane item; these are tiny launches.
+// ---------------------------------------------------------------------------
+
+enum PlaneOpCode {
+  OP_PACK_B, OP_UNPACK_GHOST_B, OP_PACK_J, OP_FOLD_J,
+  OP_GHOST_B_COPY,      // PEC: ghost = +interior ; symmetric/pmc: ghost = -interior  (sign in w0)
+  OP_GHOST_B_ABSORB,    // Higdon ABC (local.c:80-107)
+  OP_TANG_E_ZERO,       // PEC: e = tca = 0 on the face (local.c:237-247)
+  OP_JF_SCALE,          // PEC: jf = 0 ; others: jf *= 2 (local.c:345-354); factor in w0
+  OP_NORM_B_ZERO        // symmetric: cbX = 0 on the face (local.c:282-284)
+};
+
+struct PlaneArgs {
+  int op, X, side;       // side: -1 low face, +1 high face
+  int plane;             // plane index the items live on (ghost / face)
+  float w0, w1;          // weights (rw,lw) / sign / factor / (decay, drive)
+  float cdt_dX, cdt_dY, cdt_dZ;
+  float * buf;           // packed face buffer
+};
+
+__global__ void __launch_bounds__(128)
+k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  const int s3[3] = { 1, g.sy, g.sz };
+  const int X = a.X, Y = (X+1)%3, Z = (X+2)%3;
+  const int nY = n3[Y], nZ = n3[Z], sX = s3[X], sY = s3[Y], sZ = s3[Z];
+  const size_t P = (size_t)g.nvp;
+  const bool bkind = ( a.op==OP_PACK_B || a.op==OP_UNPACK_GHOST_B || a.op==OP_GHOST_B_COPY || a.op==OP_GHOST_B_ABSORB );
+  int nA, uA, nB, uB;                       // item counts and u-extents of the two sets
+  if( a.op==OP_NORM_B_ZERO ) { uA = nY; nA = nY*nZ; uB = 1; nB = 0; }
+  else if( bkind ) { uA = nY+1; nA = (nY+1)*nZ; uB = nY;   nB = nY*(nZ+1); }
+  else             { uA = nY;   nA = nY*(nZ+1); uB = nY+1; nB = (nY+1)*nZ; }
+  const int t = blockIdx.x*blockDim.x + threadIdx.x;
+  if( t>=nA+nB ) return;
+  const bool isA = t<nA;
+  const int k = isA ? t : t-nA;
+  const int ue = isA ? uA : uB;
+  const int u = 1 + k%ue, w = 1 + k/ue;
+  const int v = a.plane*sX + u*sY + w*sZ;
+  const int comp = isA ? Y : Z;             // tangential component index
+  switch( a.op ) {
+  case OP_PACK_B: a.buf[t] = f[ (F_CBX+comp)*P + v ]; break;
+  case OP_PACK_J: a.buf[t] = f[ (F_JFX+comp)*P + v ]; break;
+  case OP_UNPACK_GHOST_B: {                 // remote.c:108-115: ghost = rw*recv + lw*interior
+    float * cb = f + (F_CBX+comp)*P;
+    cb[v] = a.w0*a.buf[t] + a.w1*cb[ v - a.side*sX ];
+  } break;
+  case OP_FOLD_J: {                         // remote.c:463-470: jf = lw*jf + rw*recv
+    float * jf = f + (F_JFX+comp)*P;
+    jf[v] = a.w1*jf[v] + a.w0*a.buf[t];
+  } break;
+  case OP_GHOST_B_COPY: {
+    float * cb = f + (F_CBX+comp)*P;
+    const float s = cb[ v - a.side*sX ];
+    cb[v] = a.w0<0 ? -s : s;
+  } break;
+  case OP_GHOST_B_ABSORB: {
+    // a.plane is the ghost plane; face plane = ghost for the high side, 1 for the low side
+    const int vf = ( a.side<0 ? 1 : a.plane )*sX + u*sY + w*sZ;
+    const int fh = v - a.side*sX;
+    float * cb = f + (F_CBX+comp)*P;
+    const float * eX = f + (F_EX+X)*P;
+    const float decay = a.w0, drive = a.w1;
+    if( isA ) {                              // cbY
+      const float * eZ = f + (F_EX+Z)*P;
+      float t1 = a.cdt_dX*( eZ[ vf - a.side*sX ] - eZ[vf] );
+      t1 = a.side<0 ? t1 : -t1;
+      float t2 = eX[ v + sZ - a.side*sX ];
+      t2 = a.cdt_dZ*( t2 - eX[fh] );
+      cb[v] = ( ( decay*cb[v] + drive*cb[fh] ) - t1 ) + t2;
+    } else {                                 // cbZ
+      const float * eY = f + (F_EX+Y)*P;
+      float t1 = a.cdt_dX*( eY[ vf - a.side*sX ] - eY[vf] );
+      t1 = a.side<0 ? t1 : -t1;
+      float t2 = eX[ v + sY - a.side*sX ];
+      t2 = a.cdt_dY*( t2 - eX[fh] );
+      cb[v] = ( ( decay*cb[v] + drive*cb[fh] ) + t1 ) - t2;
+    }
+  } break;
+  case OP_TANG_E_ZERO: f[ (F_EX+comp)*P + v ] = 0.f; f[ (F_TCAX+comp)*P + v ] = 0.f; break;
+  case OP_JF_SCALE: { float * jf = f + (F_JFX+comp)*P; jf[v] = a.w0==0.f ? 0.f : jf[v]*a.w0; } break;
+  case OP_NORM_B_ZERO: f[ (F_CBX+X)*P + v ] = 0.f; break;
+  }
+}
+
+static int plane_items( const GridDev & g, int X, int op ) {
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  const int nY = n3[(X+1)%3], nZ = n3[(X+2)%3];
+  if( op==OP_NORM_B_ZERO ) return nY*nZ;
+  return (nY+1)*nZ + nY*(nZ+1);
+}
+
+static void launch_plane( FieldMirror * m, PlaneArgs a ) {
+  Runtime & r = rt();
+  const GridDev & g = m->grid->dev;
+  int n = plane_items( g, a.X, a.op );
+  k_plane_op<<< div_up(n,128), 128, 0, r.stream >>>( m->d, g, a );
+  VPB_CHECK_LAUNCH(); r.launches++;
+}
+
+static inline bool face_is_remote( const GridMirror * gm, int X, int side ) {
+  int bc = gm->fbc[ X + ( side>0 ? 3 : 0 ) ];
+  return bc>=0 && bc<g_world_size;
+}
+static inline int face_bc( const GridMirror * gm, int X, int side ) { return gm->fbc[ X + ( side>0 ? 3 : 0 ) ]; }
+
+// Face transport.  Single-GPU: what leaves through -X arrives on our own +X
+// port (the reference self-sends through MPI, grid_comm.c:20-23), i.e. the
+// receive buffer IS the opposite send buffer.  Multi-GPU: vpb_comm.cu.
+
+// Device layout of m->d_face: [send_lo | send_hi | recv_lo | recv_hi], each face_floats long.
+static void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi ) {
+  float * slo = m->d_face, * shi = m->d_face + m->face_floats;
+  float * rlo = m->d_face + 2*m->face_floats, * rhi = m->d_face + 3*m->face_floats;
+  const GridMirror * gm = m->grid;
+  const bool rem_lo = face_is_remote( gm, X, -1 ), rem_hi = face_is_remote( gm, X, +1 );
+  *from_lo = nullptr; *from_hi = nullptr;
+  if( !rem_lo && !rem_hi ) return;
+  const bool self_lo = rem_lo && face_bc( gm, X, -1 )==g_world_rank;
+  const bool self_hi = rem_hi && face_bc( gm, X, +1 )==g_world_rank;
+  if( ( rem_lo && !self_lo ) || ( rem_hi && !self_hi ) ) {
+    comm_exchange_faces( m, X, rem_lo ? slo : nullptr, rem_hi ? shi : nullptr,
+                         rem_lo ? rlo : nullptr, rem_hi ? rhi : nullptr, nfloat );
+    if( rem_lo ) *from_lo = rlo;
+    if( rem_hi ) *from_hi = rhi;
+    return;
+  }
+  if( rem_lo ) *from_lo = shi;   // from the -X neighbour (ourselves): its +X message
+  if( rem_hi ) *from_hi = slo;
+}
+
+// remote.c:61-134 + local.c:50-122: fill every tangential-B ghost plane.
+static void fill_ghost_tang_b( FieldMirror * m ) {
+  const GridMirror * gm = m->grid; const GridDev & g = gm->dev; const vpb_grid_t * hg = gm->host;
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  const float d3[3] = { hg->dx, hg->dy, hg->dz };
+  const float cdt[3] = { hg->cvac*hg->dt*hg->rdx, hg->cvac*hg->dt*hg->rdy, hg->cvac*hg->dt*hg->rdz };
+  const float higend = ( g.nx>1 || g.ny>1 || g.nz>1 ) ? 1.03527618 : 1.;
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    // local boundary conditions
+    for( int side=-1; side<=1; side+=2 ) {
+      const int bc = face_bc( gm, X, side );
+      if( !( bc<0 || bc>=g_world_size ) ) continue;
+      PlaneArgs a{}; a.X = X; a.side = side; a.plane = side<0 ? 0 : n3[X]+1;
+      a.cdt_dX = cdt[X]; a.cdt_dY = cdt[Y]; a.cdt_dZ = cdt[Z];
+      switch( bc ) {
+      case VPB_PEC_FIELDS:       a.op = OP_GHOST_B_COPY; a.w0 =  1.f; break;
+      case VPB_SYMMETRIC_FIELDS:
+      case VPB_PMC_FIELDS:       a.op = OP_GHOST_B_COPY; a.w0 = -1.f; break;
+      case VPB_ABSORB_FIELDS: {
+        float drive = cdt[X]*higend;
+        float decay = (1-drive)/(1+drive);
+        drive = 2*drive/(1+drive);
+        a.op = OP_GHOST_B_ABSORB; a.w0 = decay; a.w1 = drive;
+      } break;
+      default: VPB_ERROR( "Bad boundary condition encountered." );
+      }
+      launch_plane( m, a );
+    }
+    // remote (or periodic-to-self) neighbours
+    const bool rem_lo = face_is_remote( gm, X, -1 ), rem_hi = face_is_remote( gm, X, +1 );
+    if( !rem_lo && !rem_hi ) continue;
+    const int nf = plane_items( g, X, OP_PACK_B );
+    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = -1; a.plane = 1;     a.buf = m->d_face;                  launch_plane( m, a ); }
+    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = +1; a.plane = n3[X]; a.buf = m->d_face + m->face_floats; launch_plane( m, a ); }
+    float * from_lo, * from_hi;
+    exchange_axis( m, X, nf, &from_lo, &from_hi );
+    // equal cell size on both sides (checked when the communicator is set up)
+    float lw = d3[X];
+    const float rw = (2.*d3[X])/(lw+d3[X]);
+    lw = (lw-d3[X])/(lw+d3[X]);
+    if( from_lo ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = -1; a.plane = 0;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; launch_plane( m, a ); }
+    if( from_hi ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; launch_plane( m, a ); }
+  }
+}
+
+} // namespace vpb
+
+using namespace vpb;
+
+static int stencil_grid( long long n ) {
+  long long b = ( n + 255 )/256, cap = (long long)rt().sm_count*16;
+  return (int)( b>cap ? cap : ( b<1 ? 1 : b ) );
+}
+
+extern "C" {
+
+// advance_b.cc:10-19 -> advance_b_pipeline.cc:52-125 (+ local_adjust_norm_b)
+void vpic_b200_advance_b( vpb_field_array_t * fa, float frac ) {
+  if( !fa ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  FieldMirror * m = mirror( fa );
+  to_device( m );
+  const GridDev & g = m->grid->dev; const vpb_grid_t * hg = fa->g;
+  const float px = (g.nx>1) ? frac*hg->cvac*hg->dt*hg->rdx : 0;
+  const float py = (g.ny>1) ? frac*hg->cvac*hg->dt*hg->rdy : 0;
+  const float pz = (g.nz>1) ? frac*hg->cvac*hg->dt*hg->rdz : 0;
+  k_advance_b<<< stencil_grid( (long long)(g.nx+1)*(g.ny+1)*(g.nz+1) ), 256, 0, r.stream >>>( m->d, g, px, py, pz );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
+    const int bc = face_bc( m->grid, X, side );
+    if( !( bc<0 || bc>=g_world_size ) ) continue;
+    if( bc==VPB_SYMMETRIC_FIELDS ) {
+      PlaneArgs a{}; a.op = OP_NORM_B_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
+      launch_plane( m, a );
+    } else if( bc!=VPB_PEC_FIELDS && bc!=VPB_PMC_FIELDS && bc!=VPB_ABSORB_FIELDS )
+      VPB_ERROR( "Bad boundary condition encountered." );
+  }
+  finish_write( m );
+}
+
+// advance_e.cc:10-25 / vacuum_advance_e.cc:10-25
+void vpic_b200_advance_e( vpb_field_array_t * fa, float frac ) {
+  if( !fa ) VPB_ERROR( "Bad args" );
+  if( frac!=1 ) VPB_ERROR( "standard advance_e does not support frac != 1 yet" );
+  Runtime & r = rt();
+  FieldMirror * m = mirror( fa );
+  to_device( m );
+  const GridDev & g = m->grid->dev; const vpb_grid_t * hg = fa->g;
+  const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
+  const float damp = prm->damp;
+  fill_ghost_tang_b( m );
+  const long long n = (long long)(g.nx+1)*(g.ny+1)*(g.nz+1);
+  if( m->n_mc==1 ) {
+    const vpb_material_coefficient_t * mc = prm->mc;
+    VacuumCoef c;
+    c.decayx = mc->decayx; c.drivex = mc->drivex; c.decayy = mc->decayy; c.drivey = mc->drivey;
+    c.decayz = mc->decayz; c.drivez = mc->drivez;
+    c.px_muz = ((g.nx>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdx : 0)*mc->rmuz;
+    c.px_muy = ((g.nx>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdx : 0)*mc->rmuy;
+    c.py_mux = ((g.ny>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdy : 0)*mc->rmux;
+    c.py_muz = ((g.ny>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdy : 0)*mc->rmuz;
+    c.pz_muy = ((g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0)*mc->rmuy;
+    c.pz_mux = ((g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0)*mc->rmux;
+    c.damp = damp; c.cj = hg->dt/hg->eps0;
+    k_advance_e_vacuum<<< stencil_grid( n ), 256, 0, r.stream >>>( m->d, g, c );
+  } else {
+    const float px = (g.nx>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdx : 0;
+    const float py = (g.ny>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdy : 0;
+    const float pz = (g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0;
+    k_advance_e_material<<< stencil_grid( n ), 256, 0, r.stream >>>( m->d, m->d_mat, m->d_mc, g, px, py, pz, damp, hg->dt/hg->eps0 );
+  }
+  VPB_CHECK_LAUNCH(); r.launches++;
+  // local_adjust_tang_e (local.c:224-264)
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
+    const int bc = face_bc( m->grid, X, side );
+    if( !( bc<0 || bc>=g_world_size ) ) continue;
+    if( bc==VPB_PEC_FIELDS ) {
+      PlaneArgs a{}; a.op = OP_TANG_E_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
+      launch_plane( m, a );
+    }
+  }
+  finish_write( m );
+}
+
+// energy_f.c:12-23 / vacuum_energy_f.c
+void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ) {
+  if( !en || !fa ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  FieldMirror * m = mirror( const_cast<vpb_field_array_t *>( fa ) );
+  to_device( m );
+  const GridDev & g = m->grid->dev; const vpb_grid_t * hg = fa->g;
+  const int ncell = g.nx*g.ny*g.nz;
+  int nb = div_up( ncell, EN_BLOCK ); if( nb>r.sm_count*4 ) nb = r.sm_count*4;
+  double * partial = (double *)scratch( sizeof(double)*6*(size_t)nb );
+  if( m->n_mc==1 ) k_energy_f<true ><<< nb, EN_BLOCK, 0, r.stream >>>( partial, m->d, m->d_mat, m->d_mc, g );
+  else             k_energy_f<false><<< nb, EN_BLOCK, 0, r.stream >>>( partial, m->d, m->d_mat, m->d_mc, g );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  const double v0 = 0.5*hg->eps0*hg->dV;
+  k_sum_partials<<< 1, 32, 0, r.stream >>>( m->d_en, partial, nb, 6, v0 );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  double local[6];
+  VPB_CUDA( cudaMemcpyAsync( local, m->d_en, sizeof(double)*6, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  if( g_world_size>1 ) comm_allsum_d( local, 6 );
+  for( int c=0; c<6; c++ ) en[c] = local[c];
+}
+
+// sfa.c:231-237 (the jfx,jfy,jfz planes are adjacent in the SoA block)
+void vpic_b200_clear_jf( vpb_field_array_t * fa ) {
+  if( !fa ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  FieldMirror * m = mirror( fa );
+  to_device( m );
+  VPB_CUDA( cudaMemsetAsync( m->comp( F_JFX ), 0, sizeof(float)*3*(size_t)m->grid->dev.nvp, r.stream ) );
+  r.launches++;
+  finish_write( m );
+}
+
+void vpic_b200_clear_rhof( vpb_field_array_t * fa ) {
+  if( !fa ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  FieldMirror * m = mirror( fa );
+  to_device( m );
+  VPB_CUDA( cudaMemsetAsync( m->comp( F_RHOF ), 0, sizeof(float)*(size_t)m->grid->dev.nvp, r.stream ) );
+  r.launches++;
+  finish_write( m );
+}
+
+// remote.c:417-508 (+ local_adjust_jf, local.c:335-368)
+void vpic_b200_synchronize_jf( vpb_field_array_t * fa ) {
+  if( !fa ) VPB_ERROR( "Bad args" );
+  FieldMirror * m = mirror( fa );
+  to_device( m );
+  const GridMirror * gm = m->grid; const GridDev & g = gm->dev; const vpb_grid_t * hg = fa->g;
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  const float d3[3] = { hg->dx, hg->dy, hg->dz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
+    const int bc = face_bc( gm, X, side );
+    if( !( bc<0 || bc>=g_world_size ) ) continue;
+    PlaneArgs a{}; a.op = OP_JF_SCALE; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
+    if( bc==VPB_PEC_FIELDS ) a.w0 = 0.f;
+    else if( bc==VPB_SYMMETRIC_FIELDS || bc==VPB_PMC_FIELDS || bc==VPB_ABSORB_FIELDS ) a.w0 = 2.f;
+    else VPB_ERROR( "Bad boundary condition encountered." );
+    launch_plane( m, a );
+  }
+  for( int X=0; X<3; X++ ) {
+    const bool rem_lo = face_is_remote( gm, X, -1 ), rem_hi = face_is_remote( gm, X, +1 );
+    if( !rem_lo && !rem_hi ) continue;
+    const int nf = plane_items( g, X, OP_PACK_J );
+    // both messages are packed before either is folded in (remote.c:474-481)
+    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = -1; a.plane = 1;       a.buf = m->d_face;                  launch_plane( m, a ); }
+    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.buf = m->d_face + m->face_floats; launch_plane( m, a ); }
+    float * from_lo, * from_hi;
+    exchange_axis( m, X, nf, &from_lo, &from_hi );
+    float rw = d3[X], lw = rw + d3[X];
+    rw /= lw; lw = d3[X]/lw; lw += lw; rw += rw;
+    // from the -X neighbour (its plane nX+1) -> our plane 1; from +X (its plane 1) -> our plane nX+1
+    if( from_lo ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = -1; a.plane = 1;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; launch_plane( m, a ); }
+    if( from_hi ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; launch_plane( m, a ); }
+  }
+  finish_write( m );
+}
+
+} // extern "C"

@@ -1,0 +1,249 @@
+// vpb_mirrors.cu -- interpolator / accumulator / species mirrors and the
+// control-surface entry points of vpic_b200.h part 2.
+#include "vpb_runtime.h"
+#include <cstring>
+
+namespace vpb {
+
+// ---- interpolator ----------------------------------------------------------
+
+InterpMirror * mirror( vpb_interpolator_array_t * ia ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !ia ) VPB_ERROR( "Bad args" );
+  auto it = r.interps.find( ia );
+  if( it!=r.interps.end() ) return it->second;
+  InterpMirror * m = new InterpMirror;
+  m->host = ia; m->grid = mirror( ia->g );
+  size_t bytes = sizeof(float)*IP_STRIDE*(size_t)m->grid->dev.nv;
+  VPB_CUDA( cudaMalloc( &m->d, bytes ) );
+  VPB_CUDA( cudaMemsetAsync( m->d, 0, bytes, r.stream ) );
+  r.interps[ia] = m;
+  return m;
+}
+
+void to_device( InterpMirror * m ) {
+  Runtime & r = rt();
+  if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
+  if( !m->host->i ) { if( m->dev_valid ) return; VPB_ERROR( "interpolator array has neither host nor device data" ); }
+  static_assert( sizeof(vpb_interpolator_t)==sizeof(float)*IP_STRIDE, "device interpolator layout == host layout" );
+  VPB_CUDA( cudaMemcpyAsync( m->d, m->host->i, sizeof(vpb_interpolator_t)*(size_t)m->grid->dev.nv, cudaMemcpyHostToDevice, r.stream ) );
+  m->dev_valid = true;
+}
+
+void to_host( InterpMirror * m ) {
+  Runtime & r = rt();
+  if( !m->dev_valid || m->host_valid || !m->host->i ) return;
+  VPB_CUDA( cudaMemcpyAsync( m->host->i, m->d, sizeof(vpb_interpolator_t)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  m->host_valid = true;
+}
+
+// ---- accumulator -----------------------------------------------------------
+// The device holds ONE accumulator copy; it corresponds to the host's copy 0
+// (sf_interface.h:107-113).  The per-pipeline private copies exist on the CPU
+// only to avoid races; on the device the warp-reduced atomics make them
+// unnecessary, and reduce_accumulator_array becomes a no-op.
+
+AccMirror * mirror( vpb_accumulator_array_t * aa ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !aa ) VPB_ERROR( "Bad args" );
+  auto it = r.accs.find( aa );
+  if( it!=r.accs.end() ) return it->second;
+  AccMirror * m = new AccMirror;
+  m->host = aa; m->grid = mirror( aa->g );
+  size_t bytes = sizeof(float)*ACC_STRIDE*(size_t)m->grid->dev.nv;
+  VPB_CUDA( cudaMalloc( &m->d, bytes ) );
+  VPB_CUDA( cudaMemsetAsync( m->d, 0, bytes, r.stream ) );
+  r.accs[aa] = m;
+  return m;
+}
+
+void to_device( AccMirror * m ) {
+  Runtime & r = rt();
+  if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
+  if( !m->host->a ) { if( m->dev_valid ) return; VPB_ERROR( "accumulator array has neither host nor device data" ); }
+  static_assert( sizeof(vpb_accumulator_t)==sizeof(float)*ACC_STRIDE, "device accumulator layout == host layout" );
+  VPB_CUDA( cudaMemcpyAsync( m->d, m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, cudaMemcpyHostToDevice, r.stream ) );
+  m->dev_valid = true;
+}
+
+void to_host( AccMirror * m ) {
+  Runtime & r = rt();
+  if( !m->dev_valid || m->host_valid || !m->host->a ) return;
+  VPB_CUDA( cudaMemcpyAsync( m->host->a, m->d, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  m->host_valid = true;
+}
+
+// ---- species ---------------------------------------------------------------
+
+SpeciesMirror * mirror( vpb_species_t * sp ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !sp ) VPB_ERROR( "Bad args" );
+  SpeciesMirror * m;
+  auto it = r.species.find( sp );
+  if( it!=r.species.end() ) m = it->second;
+  else {
+    m = new SpeciesMirror;
+    m->host = sp; m->grid = mirror( sp->g );
+    VPB_CUDA( cudaMalloc( &m->d_partition, sizeof(int)*( (size_t)m->grid->dev.nv + 1 ) ) );
+    VPB_CUDA( cudaMalloc( &m->d_counters, sizeof(int)*64 ) );
+    VPB_CUDA( cudaMemsetAsync( m->d_counters, 0, sizeof(int)*64, r.stream ) );
+    m->np = sp->np; m->nm = sp->nm;
+    r.species[sp] = m;
+  }
+  // The host may have re-allocated p / pm (boundary_p.cc:346-394): follow max_np.
+  if( (size_t)sp->max_np>m->cap_p ) {
+    vpb_particle_t * n; size_t cap = (size_t)sp->max_np;
+    VPB_CUDA( cudaMalloc( &n, sizeof(vpb_particle_t)*cap ) );
+    if( m->d_p ) {
+      if( m->dev_valid && m->np>0 )
+        VPB_CUDA( cudaMemcpyAsync( n, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyDeviceToDevice, r.stream ) );
+      VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+      VPB_CUDA( cudaFree( m->d_p ) );
+    }
+    m->d_p = n; m->cap_p = cap;
+  }
+  if( (size_t)sp->max_nm>m->cap_pm ) {
+    if( m->d_pm ) { VPB_CUDA( cudaStreamSynchronize( r.stream ) ); VPB_CUDA( cudaFree( m->d_pm ) ); }
+    m->cap_pm = (size_t)sp->max_nm;
+    VPB_CUDA( cudaMalloc( &m->d_pm, sizeof(vpb_particle_mover_t)*m->cap_pm ) );
+  }
+  return m;
+}
+
+void to_device( SpeciesMirror * m ) {
+  Runtime & r = rt();
+  if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
+  if( !m->host->p ) { if( m->dev_valid ) return; VPB_ERROR( "species \"%s\" has neither host nor device particles", m->host->name ); }
+  m->np = m->host->np; m->nm = m->host->nm;
+  if( m->np>0 )
+    VPB_CUDA( cudaMemcpyAsync( m->d_p, m->host->p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyHostToDevice, r.stream ) );
+  m->dev_valid = true; m->partition_dev_valid = false;
+}
+
+void to_host( SpeciesMirror * m ) {
+  Runtime & r = rt();
+  if( !m->dev_valid || m->host_valid ) return;
+  m->host->np = m->np;
+  if( m->host->p && m->np>0 )
+    VPB_CUDA( cudaMemcpyAsync( m->host->p, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyDeviceToHost, r.stream ) );
+  if( m->host->partition && m->partition_dev_valid )
+    VPB_CUDA( cudaMemcpyAsync( m->host->partition, m->d_partition, sizeof(int)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  if( m->host->p ) m->host_valid = true;
+}
+
+// The mover list and its count are what the host driver reads after advance_p
+// (src/vpic/advance.cc:78-101), so they travel in every coherence mode.
+void movers_to_host( SpeciesMirror * m ) {
+  Runtime & r = rt();
+  m->host->nm = m->nm;
+  if( m->host->pm && m->nm>0 )
+    VPB_CUDA( cudaMemcpyAsync( m->host->pm, m->d_pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+}
+
+} // namespace vpb
+
+using namespace vpb;
+
+// ---- control surface (vpic_b200.h part 2) ----------------------------------
+
+extern "C" {
+
+int vpic_b200_init( int device, int world_rank, int world_size ) {
+  Runtime & r = rt();
+  if( !r.initialised ) r.device = device<0 ? 0 : device;
+  g_world_rank = world_rank; g_world_size = world_size<1 ? 1 : world_size;
+  ensure_init();
+  return r.sm_count;
+}
+
+void vpic_b200_set_coherence( int mode ) {
+  if( mode!=VPB_COHERENCE_STRICT && mode!=VPB_COHERENCE_RESIDENT ) VPB_ERROR( "Bad args" );
+  rt().coherence = mode;
+}
+
+void vpic_b200_set_deposit_mode( int mode ) {
+  if( mode!=VPB_DEPOSIT_FAST && mode!=VPB_DEPOSIT_PARITY ) VPB_ERROR( "Bad args" );
+  rt().deposit_mode = mode;
+}
+
+int vpic_b200_abi_check( int s_interp, int s_acc, int s_field, int s_particle, int s_grid, int s_species ) {
+  int bad = 0;
+  if( s_interp  !=(int)sizeof(vpb_interpolator_t) ) bad |= 1;   // USE_V8/V16 padded layout
+  if( s_acc     !=(int)sizeof(vpb_accumulator_t)  ) bad |= 2;
+  if( s_field   !=(int)sizeof(vpb_field_t)        ) bad |= 4;
+  if( s_particle!=(int)sizeof(vpb_particle_t)     ) bad |= 8;
+  if( s_grid    !=(int)sizeof(vpb_grid_t)         ) bad |= 16;
+  if( s_species !=(int)sizeof(vpb_species_t)      ) bad |= 32;
+  return bad;
+}
+
+void vpic_b200_device_synchronize( void ) {
+  ensure_init();
+  VPB_CUDA( cudaStreamSynchronize( rt().stream ) );
+}
+
+long long vpic_b200_launch_count( void ) { return rt().launches; }
+void * vpic_b200_stream( void ) { ensure_init(); return (void *)rt().stream; }
+
+#define VPB_FIND( map, obj ) ( rt().map.find( obj )!=rt().map.end() ? rt().map[obj] : nullptr )
+
+void vpic_b200_sync_to_host( void * obj ) {
+  ensure_init();
+  if( auto m = VPB_FIND( species, obj ) ) { to_host( m ); movers_to_host( m ); return; }
+  if( auto m = VPB_FIND( fields,  obj ) ) { to_host( m ); return; }
+  if( auto m = VPB_FIND( interps, obj ) ) { to_host( m ); return; }
+  if( auto m = VPB_FIND( accs,    obj ) ) { to_host( m ); return; }
+}
+
+void vpic_b200_sync_from_host( void * obj ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( r.species.count( obj ) ) { auto m = mirror( (vpb_species_t *)obj ); m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
+  if( r.fields.count( obj )  ) { auto m = r.fields[obj];  m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
+  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
+  if( r.accs.count( obj )    ) { auto m = r.accs[obj];    m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
+  VPB_ERROR( "vpic_b200_sync_from_host: object %p has no device mirror yet", obj );
+}
+
+void vpic_b200_forget( void * obj ) {
+  Runtime & r = rt();
+  if( !r.initialised ) return;
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  if( r.species.count( obj ) ) { auto m = r.species[obj]; cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
+  if( r.fields.count( obj )  ) { auto m = r.fields[obj]; cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
+  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; cudaFree( m->d ); delete m; r.interps.erase( obj ); return; }
+  if( r.accs.count( obj )    ) { auto m = r.accs[obj]; cudaFree( m->d ); delete m; r.accs.erase( obj ); return; }
+  if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
+}
+
+void * vpic_b200_device_ptr( void * obj, int which ) {
+  if( auto m = VPB_FIND( species, obj ) ) return which==0 ? (void *)m->d_p : which==1 ? (void *)m->d_pm : (void *)m->d_partition;
+  if( auto m = VPB_FIND( fields,  obj ) ) return (void *)m->d;
+  if( auto m = VPB_FIND( interps, obj ) ) return (void *)m->d;
+  if( auto m = VPB_FIND( accs,    obj ) ) return (void *)m->d;
+  return nullptr;
+}
+
+void vpic_b200_finalize( void ) {
+  Runtime & r = rt();
+  if( !r.initialised ) return;
+  cudaStreamSynchronize( r.stream );
+  std::vector<const void *> keys;
+  for( auto & kv : r.species ) keys.push_back( kv.first );
+  for( auto & kv : r.fields  ) keys.push_back( kv.first );
+  for( auto & kv : r.interps ) keys.push_back( kv.first );
+  for( auto & kv : r.accs    ) keys.push_back( kv.first );
+  for( auto & kv : r.grids   ) keys.push_back( kv.first );
+  for( auto k : keys ) vpic_b200_forget( (void *)k );
+  if( r.d_scratch ) cudaFree( r.d_scratch ); r.d_scratch = nullptr; r.scratch_bytes = 0;
+  if( r.h_pinned ) cudaFreeHost( r.h_pinned ); r.h_pinned = nullptr; r.pinned_bytes = 0;
+}
+
+} // extern "C"

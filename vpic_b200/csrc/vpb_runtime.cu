@@ -1,0 +1,220 @@
+// vpb_runtime.cu -- runtime singleton, mirror registry, host<->device coherence.
+#include "vpb_runtime.h"
+#include <cstdarg>
+#include <cstring>
+
+namespace vpb {
+
+int g_world_rank = 0, g_world_size = 1;
+
+void fatal( const char * file, int line, const char * fmt, ... ) {
+  // Reference convention: src/util/util_base.h:267-273
+  fprintf( stderr, "Error at %s(%d)[%d]:\n\t", file, line, g_world_rank );
+  va_list ap; va_start( ap, fmt ); vfprintf( stderr, fmt, ap ); va_end( ap );
+  fprintf( stderr, "\n" ); fflush( stderr );
+  exit( 1 );
+}
+void warning( const char * file, int line, const char * fmt, ... ) {
+  fprintf( stderr, "Warning at %s(%d)[%d]:\n\t", file, line, g_world_rank );
+  va_list ap; va_start( ap, fmt ); vfprintf( stderr, fmt, ap ); va_end( ap );
+  fprintf( stderr, "\n" ); fflush( stderr );
+}
+
+Runtime & rt() { static Runtime r; return r; }
+
+void ensure_init() {
+  Runtime & r = rt();
+  if( r.initialised ) return;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount( &n );
+  if( e!=cudaSuccess || n<1 )
+    VPB_ERROR( "libvpic_b200 needs a CUDA device (B200, sm_100a); none is usable (%s). "
+               "There is no CPU fallback.", e==cudaSuccess ? "device count is 0" : cudaGetErrorString(e) );
+  if( r.device>=n ) r.device = r.device % n;
+  VPB_CUDA( cudaSetDevice( r.device ) );
+  cudaDeviceProp prop; VPB_CUDA( cudaGetDeviceProperties( &prop, r.device ) );
+  r.sm_count = prop.multiProcessorCount;
+  VPB_CUDA( cudaStreamCreateWithFlags( &r.stream, cudaStreamNonBlocking ) );
+  VPB_CUDA( cudaStreamCreateWithFlags( &r.copy_stream[0], cudaStreamNonBlocking ) );
+  VPB_CUDA( cudaStreamCreateWithFlags( &r.copy_stream[1], cudaStreamNonBlocking ) );
+  r.initialised = true;
+}
+
+void * scratch( size_t bytes ) {
+  Runtime & r = rt();
+  if( bytes>r.scratch_bytes ) {
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( r.d_scratch ) VPB_CUDA( cudaFree( r.d_scratch ) );
+    size_t want = bytes + bytes/16 + 4096;
+    VPB_CUDA( cudaMalloc( &r.d_scratch, want ) );
+    r.scratch_bytes = want;
+  }
+  return r.d_scratch;
+}
+
+void * pinned( size_t bytes ) {
+  Runtime & r = rt();
+  if( bytes>r.pinned_bytes ) {
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( r.h_pinned ) VPB_CUDA( cudaFreeHost( r.h_pinned ) );
+    size_t want = bytes + bytes/16 + 4096;
+    VPB_CUDA( cudaMallocHost( &r.h_pinned, want ) );
+    r.pinned_bytes = want;
+  }
+  return r.h_pinned;
+}
+
+// ---- grid mirror -----------------------------------------------------------
+
+GridMirror * mirror( const vpb_grid_t * g ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !g ) VPB_ERROR( "NULL grid" );
+  auto it = r.grids.find( g );
+  if( it!=r.grids.end() ) {
+    GridMirror * m = it->second;
+    if( m->dev.nx==g->nx && m->dev.ny==g->ny && m->dev.nz==g->nz ) return m;
+    if( m->d_neighbor ) cudaFree( m->d_neighbor );
+    delete m; r.grids.erase( it );
+  }
+  GridMirror * m = new GridMirror;
+  m->host = g;
+  GridDev & d = m->dev;
+  d.nx = g->nx; d.ny = g->ny; d.nz = g->nz;
+  d.sx = 1; d.sy = g->nx+2; d.sz = (g->nx+2)*(g->ny+2); d.nv = d.sz*(g->nz+2);
+  d.nvp = ( d.nv + 31 ) & ~31;
+  d.neighbor = nullptr;
+  if( d.nv!=g->nv ) VPB_ERROR( "grid_t.nv (%d) does not match (nx+2)(ny+2)(nz+2) (%d)", g->nv, d.nv );
+  static const int bnd[6] = { VPB_BOUNDARY(-1,0,0), VPB_BOUNDARY(0,-1,0), VPB_BOUNDARY(0,0,-1),
+                              VPB_BOUNDARY( 1,0,0), VPB_BOUNDARY(0, 1,0), VPB_BOUNDARY(0,0, 1) };
+  for( int f=0; f<6; f++ ) m->fbc[f] = g->bc[ bnd[f] ];
+
+  // Classify the particle boundary of each face from g->neighbor
+  // (src/grid/ops.c:58-86, 135-210) and check that the table is the regular
+  // box the arithmetic neighbour computation assumes.
+  const int n[3] = { g->nx, g->ny, g->nz };
+  const int64_t s[3] = { 1, d.sy, d.sz };
+  bool regular = g->neighbor!=nullptr;
+  if( !g->neighbor ) VPB_ERROR( "grid_t.neighbor is NULL" );
+  for( int f=0; f<6 && regular; f++ ) {
+    const int a = f%3, side = f<3 ? -1 : 1;
+    int cls = -1;
+    for( int z=1; z<=n[2] && regular; z++ ) for( int y=1; y<=n[1] && regular; y++ ) for( int x=1; x<=n[0]; x++ ) {
+      const int c[3] = { x, y, z };
+      const int64_t v = x + s[1]*y + s[2]*z;
+      const int64_t nb = g->neighbor[ 6*v + f ];
+      const bool on_face = side<0 ? c[a]==1 : c[a]==n[a];
+      if( !on_face ) { if( nb != g->rangel + v + side*s[a] ) { regular = false; break; } continue; }
+      int k;
+      if( nb==VPB_REFLECT_PARTICLES ) k = FACE_REFLECT;
+      else if( nb>=g->rangel && nb<=g->rangeh ) {
+        k = FACE_WRAP;
+        if( nb != g->rangel + v - side*s[a]*(n[a]-1) ) { regular = false; break; }
+      } else k = FACE_EXIT;
+      if( cls<0 ) cls = k; else if( cls!=k ) { regular = false; break; }
+    }
+    d.face[f] = cls<0 ? FACE_REFLECT : cls;
+  }
+  if( !regular ) {
+    // Irregular (set_region_bc etc.): keep an explicit compact table.
+    std::vector<int32_t> t( 6*(size_t)d.nv );
+    for( size_t i=0; i<t.size(); i++ ) {
+      int64_t nb = g->neighbor[i];
+      t[i] = nb==VPB_REFLECT_PARTICLES ? NB_REFLECT
+           : ( nb>=g->rangel && nb<=g->rangeh ) ? (int32_t)( nb - g->rangel ) : NB_EXIT;
+    }
+    VPB_CUDA( cudaMalloc( &m->d_neighbor, t.size()*sizeof(int32_t) ) );
+    VPB_CUDA( cudaMemcpy( m->d_neighbor, t.data(), t.size()*sizeof(int32_t), cudaMemcpyHostToDevice ) );
+    d.neighbor = m->d_neighbor;
+    for( int f=0; f<6; f++ ) d.face[f] = FACE_EXIT;
+  }
+  r.grids[g] = m;
+  return m;
+}
+
+// ---- field mirror ----------------------------------------------------------
+
+__global__ void k_field_aos_to_soa( const vpb_field_t * __restrict__ aos, float * __restrict__ soa,
+                                    int16_t * __restrict__ mat, int nv, int nvp ) {
+  int v = blockIdx.x*blockDim.x + threadIdx.x;
+  if( v>=nv ) return;
+  const float4 * src = reinterpret_cast<const float4 *>( aos + v );
+  float4 q0 = src[0], q1 = src[1], q2 = src[2], q3 = src[3];
+  soa[ 0*(size_t)nvp+v] = q0.x; soa[ 1*(size_t)nvp+v] = q0.y; soa[ 2*(size_t)nvp+v] = q0.z; soa[ 3*(size_t)nvp+v] = q0.w;
+  soa[ 4*(size_t)nvp+v] = q1.x; soa[ 5*(size_t)nvp+v] = q1.y; soa[ 6*(size_t)nvp+v] = q1.z; soa[ 7*(size_t)nvp+v] = q1.w;
+  soa[ 8*(size_t)nvp+v] = q2.x; soa[ 9*(size_t)nvp+v] = q2.y; soa[10*(size_t)nvp+v] = q2.z; soa[11*(size_t)nvp+v] = q2.w;
+  soa[12*(size_t)nvp+v] = q3.x; soa[13*(size_t)nvp+v] = q3.y; soa[14*(size_t)nvp+v] = q3.z; soa[15*(size_t)nvp+v] = q3.w;
+  if( mat ) {
+    const int16_t * ms = reinterpret_cast<const int16_t *>( aos + v ) + 32;
+#   pragma unroll
+    for( int c=0; c<8; c++ ) mat[ c*(size_t)nvp+v ] = ms[c];
+  }
+}
+
+__global__ void k_field_soa_to_aos( vpb_field_t * __restrict__ aos, const float * __restrict__ soa, int nv, int nvp ) {
+  int v = blockIdx.x*blockDim.x + threadIdx.x;
+  if( v>=nv ) return;
+  float4 * dst = reinterpret_cast<float4 *>( aos + v );   // material ids (last 16 B) untouched
+  dst[0] = make_float4( soa[ 0*(size_t)nvp+v], soa[ 1*(size_t)nvp+v], soa[ 2*(size_t)nvp+v], soa[ 3*(size_t)nvp+v] );
+  dst[1] = make_float4( soa[ 4*(size_t)nvp+v], soa[ 5*(size_t)nvp+v], soa[ 6*(size_t)nvp+v], soa[ 7*(size_t)nvp+v] );
+  dst[2] = make_float4( soa[ 8*(size_t)nvp+v], soa[ 9*(size_t)nvp+v], soa[10*(size_t)nvp+v], soa[11*(size_t)nvp+v] );
+  dst[3] = make_float4( soa[12*(size_t)nvp+v], soa[13*(size_t)nvp+v], soa[14*(size_t)nvp+v], soa[15*(size_t)nvp+v] );
+}
+
+FieldMirror * mirror( vpb_field_array_t * fa ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !fa ) VPB_ERROR( "Bad args" );
+  auto it = r.fields.find( fa );
+  if( it!=r.fields.end() ) return it->second;
+  FieldMirror * m = new FieldMirror;
+  m->host = fa; m->grid = mirror( fa->g );
+  const GridDev & d = m->grid->dev;
+  VPB_CUDA( cudaMalloc( &m->d, sizeof(float)*F_NCOMP*(size_t)d.nvp ) );
+  VPB_CUDA( cudaMemsetAsync( m->d, 0, sizeof(float)*F_NCOMP*(size_t)d.nvp, r.stream ) );
+  VPB_CUDA( cudaMalloc( &m->d_en, sizeof(double)*64 ) );
+  const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
+  if( !prm || !prm->mc || prm->n_mc<1 ) VPB_ERROR( "field array has no material coefficient table" );
+  m->n_mc = prm->n_mc;
+  VPB_CUDA( cudaMalloc( &m->d_mc, sizeof(vpb_material_coefficient_t)*(size_t)m->n_mc ) );
+  VPB_CUDA( cudaMemcpy( m->d_mc, prm->mc, sizeof(vpb_material_coefficient_t)*(size_t)m->n_mc, cudaMemcpyHostToDevice ) );
+  if( m->n_mc>1 ) VPB_CUDA( cudaMalloc( &m->d_mat, sizeof(int16_t)*8*(size_t)d.nvp ) );
+  // packed faces: 2 faces x (send+recv) of the largest plane, 3 comps worth
+  size_t a = (size_t)(d.nx+2)*(d.ny+2), b = (size_t)(d.ny+2)*(d.nz+2), c = (size_t)(d.nz+2)*(d.nx+2);
+  size_t mx = a>b ? a : b; if( c>mx ) mx = c;
+  m->face_floats = 2*mx + 32;
+  VPB_CUDA( cudaMalloc( &m->d_face, sizeof(float)*4*m->face_floats ) );
+  m->dev_valid = false; m->host_valid = true;
+  r.fields[fa] = m;
+  return m;
+}
+
+void to_device( FieldMirror * m ) {
+  Runtime & r = rt();
+  if( m->dev_valid && r.coherence!=VPB_COHERENCE_STRICT ) return;
+  if( m->dev_valid && !m->host_valid ) return;     // device is the only valid copy
+  if( !m->host->f ) { if( m->dev_valid ) return; VPB_ERROR( "field array has neither host nor device data" ); }
+  const GridDev & d = m->grid->dev;
+  if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv ) );
+  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyHostToDevice, r.stream ) );
+  k_field_aos_to_soa<<< div_up(d.nv,256), 256, 0, r.stream >>>( (const vpb_field_t *)m->d_stage, m->d, m->d_mat, d.nv, d.nvp );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  m->dev_valid = true;
+}
+
+void to_host( FieldMirror * m ) {
+  Runtime & r = rt();
+  if( !m->dev_valid || m->host_valid ) return;
+  if( !m->host->f ) return;                         // device-only array
+  const GridDev & d = m->grid->dev;
+  if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv ) );
+  // keep the material ids of the host copy: stage starts from the host bytes
+  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyHostToDevice, r.stream ) );
+  k_field_soa_to_aos<<< div_up(d.nv,256), 256, 0, r.stream >>>( (vpb_field_t *)m->d_stage, m->d, d.nv, d.nvp );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  VPB_CUDA( cudaMemcpyAsync( m->host->f, m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  m->host_valid = true;
+}
+
+} // namespace vpb

@@ -1,0 +1,170 @@
+// vpb_runtime.h -- device runtime underneath the C-ABI entry points.
+//
+// One process drives one B200.  The host driver (the reference's
+// vpic_simulation::advance, src/vpic/advance.cc:15-208, or our own
+// vpb_sim_* loop) owns plain host structs; this runtime keeps a device MIRROR
+// for each of them, keyed by the host struct's address, and the entry points
+// launch kernels on the mirrors.  There is no CPU fallback anywhere: if CUDA is
+// unusable every entry point dies with the reference's ERROR convention
+// (src/util/util_base.h:267-273: "Error at file(line)[rank]" then exit(1)).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstdint>
+#include <unordered_map>
+#include <vector>
+#include "vpic_b200/abi.h"
+#include "vpic_b200/vpic_b200.h"
+
+namespace vpb {
+
+extern int g_world_rank, g_world_size;
+
+[[noreturn]] void fatal( const char * file, int line, const char * fmt, ... );
+void warning( const char * file, int line, const char * fmt, ... );
+
+#define VPB_ERROR(...)   ::vpb::fatal( __FILE__, __LINE__, __VA_ARGS__ )
+#define VPB_WARNING(...) ::vpb::warning( __FILE__, __LINE__, __VA_ARGS__ )
+#define VPB_CUDA(call) do { cudaError_t e_ = (call); if( e_!=cudaSuccess ) \
+  ::vpb::fatal( __FILE__, __LINE__, "CUDA error %s: %s", cudaGetErrorName(e_), cudaGetErrorString(e_) ); } while(0)
+#define VPB_CHECK_LAUNCH() VPB_CUDA( cudaGetLastError() )
+
+// ---- interior layouts on the device ---------------------------------------
+
+// Fields are kept as structure-of-arrays: 16 float planes of nvp voxels each
+// (nvp = nv rounded up to 32 so every plane starts 128-B aligned).  The order
+// of the planes is the order of the floats in field_t.
+enum FieldComp { F_EX=0, F_EY, F_EZ, F_DIVE, F_CBX, F_CBY, F_CBZ, F_DIVB,
+                 F_TCAX, F_TCAY, F_TCAZ, F_RHOB, F_JFX, F_JFY, F_JFZ, F_RHOF, F_NCOMP };
+
+// Interpolator: the 18 coefficients of interpolator_t padded to IP_STRIDE
+// floats per voxel; first 18 floats in the reference's order.
+constexpr int IP_STRIDE = 20;   // floats per voxel (80 B, reference layout)
+constexpr int ACC_STRIDE = 12;  // floats per voxel (48 B, reference layout)
+
+// Particle boundary action per box face, derived from g->neighbor.
+enum FaceAction : int { FACE_WRAP = 0, FACE_REFLECT = 1, FACE_EXIT = 2 };
+
+struct GridDev {             // passed by value to kernels
+  int nx, ny, nz;
+  int sx, sy, sz, nv, nvp;
+  int face[6];               // FaceAction for -x,-y,-z,+x,+y,+z
+  const int32_t * neighbor;  // optional explicit table (6*nv), else nullptr
+};
+
+// Encoding of the explicit neighbour table: >=0 local voxel, NB_REFLECT, NB_EXIT.
+constexpr int32_t NB_REFLECT = -1;
+constexpr int32_t NB_EXIT    = -2;
+
+// ---- mirrors ---------------------------------------------------------------
+
+struct GridMirror {
+  const vpb_grid_t * host = nullptr;
+  GridDev dev{};
+  int32_t * d_neighbor = nullptr;
+  int fbc[6];                // field boundary per face: rank (>=0) or local code (<0)
+};
+
+struct FieldMirror {
+  vpb_field_array_t * host = nullptr;
+  GridMirror * grid = nullptr;
+  float   * d = nullptr;           // 16 * nvp floats
+  int16_t * d_mat = nullptr;       // 8 * nvp material ids (only if n_mc>1)
+  vpb_material_coefficient_t * d_mc = nullptr;
+  int   n_mc = 0;
+  float * d_stage = nullptr;       // AoS staging for host<->device conversion
+  double * d_en = nullptr;         // 6 doubles + scratch for energy_f
+  float * d_face = nullptr;        // packed face buffers for exchanges
+  size_t face_floats = 0;
+  bool dev_valid = false;          // device copy holds the latest data
+  bool host_valid = true;          // host copy holds the latest data
+  float * comp( int c ) const { return d + (size_t)c*grid->dev.nvp; }
+};
+
+struct InterpMirror {
+  vpb_interpolator_array_t * host = nullptr;
+  GridMirror * grid = nullptr;
+  float * d = nullptr;             // nv * IP_STRIDE floats
+  bool dev_valid = false, host_valid = true;
+};
+
+struct AccMirror {
+  vpb_accumulator_array_t * host = nullptr;
+  GridMirror * grid = nullptr;
+  float * d = nullptr;             // nv * 12 floats == host copy 0
+  bool dev_valid = false, host_valid = true;
+};
+
+struct SpeciesMirror {
+  vpb_species_t * host = nullptr;
+  GridMirror * grid = nullptr;
+  vpb_particle_t * d_p = nullptr;  size_t cap_p = 0;
+  vpb_particle_mover_t * d_pm = nullptr; size_t cap_pm = 0;
+  int * d_partition = nullptr;     // nv+1 ints
+  int * d_counters = nullptr;      // [0]=nm  [1]=n_ignored  [2..] scratch
+  int np = 0, nm = 0;              // device-side truth while resident
+  bool dev_valid = false, host_valid = true;
+  bool partition_dev_valid = false;
+  const vpb_particle_t * registered_p = nullptr; size_t registered_bytes = 0;
+};
+
+struct Runtime {
+  bool initialised = false;
+  int device = 0;
+  cudaStream_t stream = nullptr;      // compute
+  cudaStream_t copy_stream[2] = { nullptr, nullptr };
+  int coherence = VPB_COHERENCE_STRICT;
+  int deposit_mode = VPB_DEPOSIT_FAST;
+  int sm_count = 148;
+  // scratch shared by all species (sort destination, keys, scan space)
+  void * d_scratch = nullptr; size_t scratch_bytes = 0;
+  void * h_pinned = nullptr;  size_t pinned_bytes = 0;
+  long long launches = 0;             // kernels launched (for bench's gpu_launches)
+  std::unordered_map<const void *, GridMirror *>    grids;
+  std::unordered_map<const void *, FieldMirror *>   fields;
+  std::unordered_map<const void *, InterpMirror *>  interps;
+  std::unordered_map<const void *, AccMirror *>     accs;
+  std::unordered_map<const void *, SpeciesMirror *> species;
+};
+
+Runtime & rt();
+void ensure_init();
+void * scratch( size_t bytes );        // grow-only device scratch
+void * pinned( size_t bytes );         // grow-only pinned host scratch
+
+GridMirror    * mirror( const vpb_grid_t * g );
+FieldMirror   * mirror( vpb_field_array_t * fa );
+InterpMirror  * mirror( vpb_interpolator_array_t * ia );
+AccMirror     * mirror( vpb_accumulator_array_t * aa );
+SpeciesMirror * mirror( vpb_species_t * sp );
+
+// Coherence helpers.  to_device(): make the device copy current (uploads if the
+// host copy is the valid one, or always in STRICT mode).  to_host(): the
+// reverse.  mark_dev_written(): the device copy was modified by a kernel.
+void to_device( FieldMirror * m );   void to_host( FieldMirror * m );
+void to_device( InterpMirror * m );  void to_host( InterpMirror * m );
+void to_device( AccMirror * m );     void to_host( AccMirror * m );
+void to_device( SpeciesMirror * m ); void to_host( SpeciesMirror * m );
+void movers_to_host( SpeciesMirror * m );
+template<class M> inline void mark_dev_written( M * m ) { m->dev_valid = true; m->host_valid = false; }
+// In STRICT mode every entry point finishes by pushing what it wrote back.
+template<class M> inline void finish_write( M * m ) {
+  mark_dev_written( m );
+  if( rt().coherence==VPB_COHERENCE_STRICT ) to_host( m );
+}
+
+// cross-file internals
+struct PushCoef;
+void advance_p_parity( SpeciesMirror *, AccMirror *, InterpMirror *, const PushCoef & );
+void sort_movers_by_index( SpeciesMirror * );
+void comm_exchange_faces( FieldMirror * m, int X, float * slo, float * shi, float * rlo, float * rhi, int nfloat );
+void comm_allsum_d( double * v, int n );
+void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
+void release_sort_buffers();
+__global__ void k_sum_partials( double * out, const double * partial, int nblock, int ncomp, double scale );
+
+inline int div_up( long long a, long long b ) { return (int)( (a+b-1)/b ); }
+
+} // namespace vpb

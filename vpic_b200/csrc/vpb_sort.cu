@@ -1,0 +1,225 @@
+// vpb_sort.cu -- sort_p: stable counting sort of a species by voxel.
+// Reference: src/species_advance/standard/pipeline/sort_p_pipeline.c:143-371
+// (the result of its single-pipeline subsort is what we reproduce exactly:
+// particles grouped by voxel in ascending voxel order, ORIGINAL ORDER KEPT
+// inside each voxel, partition[v] = first index of voxel v).
+//
+// Device algorithm (all hand-written, no CUB):
+//   1. keys[i] = p[i].i and a voxel histogram (warp-aggregated atomics),
+//   2. exclusive scan of the histogram -> partition[],
+//   3. scatter the particle INDICES into their voxel's segment (atomic slots;
+//      order inside a segment is arbitrary at this point),
+//   4. sort every segment ascending (warp per voxel, bitonic) -> this is what
+//      makes the sort stable and run-to-run deterministic,
+//   5. gather the 32 B particles through the permutation into the spare buffer
+//      (coalesced 2 x 128-bit stores) and swap buffers.
+// Algorithmic traffic: 4 B key + 32 B read + 32 B write per particle (SURVEY
+// 8d: 68 B); this version moves ~120 B because of the index passes.
+#include "vpb_runtime.h"
+
+namespace vpb {
+
+// ---- generic exclusive scan of n ints (3 phases) ---------------------------
+constexpr int SCAN_T = 256, SCAN_E = 16, SCAN_TILE = SCAN_T*SCAN_E;
+
+__global__ void __launch_bounds__(SCAN_T)
+k_scan_tiles( const int * __restrict__ in, int * __restrict__ out, int * __restrict__ tile_sum, int n ) {
+  __shared__ int s_warp[SCAN_T/32];
+  const long long base = (long long)blockIdx.x*SCAN_TILE + (long long)threadIdx.x*SCAN_E;
+  int v[SCAN_E], sum = 0;
+# pragma unroll
+  for( int k=0; k<SCAN_E; k++ ) { v[k] = base+k<n ? in[base+k] : 0; sum += v[k]; }
+  // inclusive warp scan of per-thread sums
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = sum;
+  for( int o=1; o<32; o<<=1 ) { int t = __shfl_up_sync( 0xffffffffu, inc, o ); if( lane>=o ) inc += t; }
+  if( lane==31 ) s_warp[w] = inc;
+  __syncthreads();
+  if( w==0 ) {
+    int t = lane<SCAN_T/32 ? s_warp[lane] : 0, i2 = t;
+    for( int o=1; o<32; o<<=1 ) { int u = __shfl_up_sync( 0xffffffffu, i2, o ); if( lane>=o ) i2 += u; }
+    if( lane<SCAN_T/32 ) s_warp[lane] = i2 - t;             // exclusive warp offsets
+    if( lane==SCAN_T/32-1 ) tile_sum[blockIdx.x] = i2;
+  }
+  __syncthreads();
+  int run = s_warp[w] + inc - sum;
+# pragma unroll
+  for( int k=0; k<SCAN_E; k++ ) { if( base+k<n ) out[base+k] = run; run += v[k]; }
+}
+
+__global__ void k_scan_sums( int * __restrict__ tile_sum, int ntile ) {   // single block, sequential chunks
+  __shared__ int s_carry; __shared__ int s_warp[32];
+  if( threadIdx.x==0 ) s_carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for( int base=0; base<ntile; base+=blockDim.x ) {
+    const int i = base + threadIdx.x;
+    const int v = i<ntile ? tile_sum[i] : 0;
+    int inc = v;
+    for( int o=1; o<32; o<<=1 ) { int t = __shfl_up_sync( 0xffffffffu, inc, o ); if( lane>=o ) inc += t; }
+    if( lane==31 ) s_warp[w] = inc;
+    __syncthreads();
+    if( w==0 ) {
+      int t = lane<(int)(blockDim.x>>5) ? s_warp[lane] : 0, i2 = t;
+      for( int o=1; o<32; o<<=1 ) { int u = __shfl_up_sync( 0xffffffffu, i2, o ); if( lane>=o ) i2 += u; }
+      s_warp[lane] = i2 - t;
+    }
+    __syncthreads();
+    const int carry = s_carry;
+    if( i<ntile ) tile_sum[i] = carry + s_warp[w] + inc - v;
+    __syncthreads();
+    if( threadIdx.x==blockDim.x-1 ) s_carry = carry + s_warp[w] + inc;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_T)
+k_scan_add( int * __restrict__ out, int * __restrict__ out2, const int * __restrict__ tile_sum, int n ) {
+  const int add = tile_sum[blockIdx.x];
+  const long long base = (long long)blockIdx.x*SCAN_TILE;
+  for( int k=threadIdx.x; k<SCAN_TILE; k+=SCAN_T ) if( base+k<n ) { int v = out[base+k] + add; out[base+k] = v; if( out2 ) out2[base+k] = v; }
+}
+
+// exclusive scan in -> out (and a second copy out2 if not null); tmp >= div_up(n,SCAN_TILE) ints
+void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n ) {
+  Runtime & r = rt();
+  const int ntile = div_up( n, SCAN_TILE );
+  k_scan_tiles<<< ntile, SCAN_T, 0, r.stream >>>( in, out, tmp, n );
+  k_scan_sums<<< 1, 1024, 0, r.stream >>>( tmp, ntile );
+  k_scan_add<<< ntile, SCAN_T, 0, r.stream >>>( out, out2, tmp, n );
+  VPB_CHECK_LAUNCH(); r.launches += 3;
+}
+
+// ---- sort kernels ----------------------------------------------------------
+
+__global__ void __launch_bounds__(256)
+k_sort_hist( const vpb_particle_t * __restrict__ p, int np, int * __restrict__ keys, int * __restrict__ count ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  const int key = i<np ? p[i].i : -1;
+  if( i<np ) keys[i] = key;
+  const unsigned m = __match_any_sync( 0xffffffffu, key );
+  if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+}
+
+__global__ void __launch_bounds__(256)
+k_sort_scatter_idx( const int * __restrict__ keys, int np, int * __restrict__ next, int * __restrict__ perm ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  const int key = i<np ? keys[i] : -1;
+  const unsigned m = __match_any_sync( 0xffffffffu, key );
+  const int lane = threadIdx.x & 31, leader = __ffs( m )-1;
+  int base = 0;
+  if( key>=0 && lane==leader ) base = atomicAdd( next + key, __popc( m ) );
+  base = __shfl_sync( 0xffffffffu, base, leader );
+  if( key>=0 ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = i;
+}
+
+// Ascending sort of every voxel's segment of perm[].  One warp per voxel.
+// Segments <= 32: shuffle bitonic.  <= FIX_SMEM: bitonic in shared memory.
+// Larger: bitonic in global memory by the same warp (rare: > 2048 particles in
+// one voxel).
+constexpr int FIX_SMEM = 2048, FIX_WARPS = 4;
+
+__device__ __forceinline__ void bitonic_mem( int * a, int n2, int lane ) {   // n2 power of two, padded with INT_MAX
+  for( int k=2; k<=n2; k<<=1 ) for( int j=k>>1; j>0; j>>=1 ) {
+    for( int t=lane; t<n2/2; t+=32 ) {
+      const int lo = ( ( t & ~(j-1) )<<1 ) | ( t & (j-1) ), hi = lo | j;
+      const bool up = ( lo & k )==0;
+      const int x = a[lo], y = a[hi];
+      if( ( x>y )==up ) { a[lo] = y; a[hi] = x; }
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(32*FIX_WARPS)
+k_sort_fix( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch ) {
+  __shared__ int s[FIX_WARPS][FIX_SMEM];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int v = blockIdx.x*FIX_WARPS + w;
+  if( v>=nv ) return;
+  const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
+  if( n<=1 ) return;
+  if( n<=32 ) {
+    int x = lane<n ? perm[b+lane] : 0x7fffffff;
+    for( int k=2; k<=32; k<<=1 ) for( int j=k>>1; j>0; j>>=1 ) {
+      const int y = __shfl_xor_sync( 0xffffffffu, x, j );
+      const bool up = ( lane & k )==0, lower = ( lane & j )==0;
+      x = ( lower==up ) ? min( x, y ) : max( x, y );
+    }
+    if( lane<n ) perm[b+lane] = x;
+    return;
+  }
+  int n2 = 64; while( n2<n ) n2 <<= 1;
+  if( n2<=FIX_SMEM ) {
+    int * a = s[w];
+    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+    __syncwarp();
+    bitonic_mem( a, n2, lane );
+    for( int t=lane; t<n; t+=32 ) perm[b+t] = a[t];
+  } else {
+    // big_scratch holds 2*np ints: each huge segment uses the window starting
+    // at 2*b, which cannot overlap another segment's window of size n2 < 2n.
+    int * a = big_scratch + 2*(size_t)b;
+    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+    __threadfence_block(); __syncwarp();
+    bitonic_mem( a, n2, lane );
+    for( int t=lane; t<n; t+=32 ) perm[b+t] = a[t];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_sort_gather( const vpb_particle_t * __restrict__ in, const int * __restrict__ perm, vpb_particle_t * __restrict__ out, int np ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if( i>=np ) return;
+  const float4 * src = reinterpret_cast<const float4 *>( in + perm[i] );
+  const float4 a = __ldg( src ), b = __ldg( src+1 );
+  float4 * dst = reinterpret_cast<float4 *>( out + i );
+  dst[0] = a; dst[1] = b;
+}
+
+// spare particle buffer shared by all species (swapped with the sorted species)
+static vpb_particle_t * g_alt = nullptr; static size_t g_alt_cap = 0;
+void release_sort_buffers() { if( g_alt ) cudaFree( g_alt ); g_alt = nullptr; g_alt_cap = 0; }
+
+} // namespace vpb
+
+using namespace vpb;
+
+extern "C" void sort_p( vpb_species_t * sp ) {
+  if( !sp ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  SpeciesMirror * m = mirror( sp );
+  to_device( m );
+  sp->last_sorted = sp->g->step;
+  const GridDev & g = m->grid->dev;
+  const int np = m->np, nv = g.nv;
+  if( g_alt_cap<m->cap_p ) {
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( g_alt ) VPB_CUDA( cudaFree( g_alt ) );
+    VPB_CUDA( cudaMalloc( &g_alt, sizeof(vpb_particle_t)*m->cap_p ) );
+    g_alt_cap = m->cap_p;
+  }
+  // scratch: keys[np] perm[np] count[nv+1] next[nv+1] tiles big[2np]
+  const size_t npa = ( (size_t)np + 31 ) & ~(size_t)31, nva = ( (size_t)nv + 1 + 31 ) & ~(size_t)31;
+  const size_t ntile = (size_t)div_up( nv+1, SCAN_TILE ) + 32;
+  int * base = (int *)scratch( sizeof(int)*( 2*npa + 2*nva + ntile + 2*npa + 64 ) );
+  int * keys = base, * perm = keys + npa, * count = perm + npa, * next = count + nva, * tiles = next + nva, * big = tiles + ntile;
+  VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nv+1 ), r.stream ) );
+  if( np>0 ) {
+    k_sort_hist<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, np, keys, count );
+    VPB_CHECK_LAUNCH(); r.launches++;
+  }
+  exclusive_scan( count, m->d_partition, next, tiles, nv+1 );
+  if( np>0 ) {
+    k_sort_scatter_idx<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, next, perm );
+    k_sort_fix<<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big );
+    k_sort_gather<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, perm, g_alt, np );
+    VPB_CHECK_LAUNCH(); r.launches += 3;
+    // swap the species buffer with the spare
+    vpb_particle_t * t = m->d_p; size_t tc = m->cap_p;
+    m->d_p = g_alt; m->cap_p = g_alt_cap; g_alt = t; g_alt_cap = tc;
+  }
+  m->partition_dev_valid = true;
+  mark_dev_written( m );
+  if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
+}
