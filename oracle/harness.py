@@ -1,0 +1,120 @@
+"""TEST INFRASTRUCTURE -- NOT PART OF THE PRODUCT.
+
+Python access to the CPU checkers: the C restatement (oracle/liboracle.so) and,
+when it has been built, the compiled reference (oracle/_ref/libvpic_ref_*.so).
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+reference legs import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(_HERE))
+from vpic_b200 import abi                      # noqa: E402
+from vpic_b200.lib import Backend, _load       # noqa: E402
+
+ORACLE_LIB = os.path.join(_HERE, "liboracle.so")
+REF_SCALAR = os.path.join(_HERE, "_ref", "libvpic_ref_scalar.so")
+REF_SIMD = os.path.join(_HERE, "_ref", "libvpic_ref_simd.so")
+_P = C.c_void_p
+
+
+def build_oracle():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "liboracle.so"])
+
+
+def oracle_backend():
+    if not os.path.exists(ORACLE_LIB):
+        build_oracle()
+    L = _load(ORACLE_LIB)
+    L.orc_set_world.argtypes = [C.c_int, C.c_int]
+    L.orc_set_energy_pipelines.argtypes = [C.c_int]
+    return Backend("oracle", L, prefix="orc_")
+
+
+def have_ref(simd=False):
+    return os.path.exists(REF_SIMD if simd else REF_SCALAR)
+
+
+_ref_booted = {}
+
+
+def ref_backend(simd=False, tpp=1):
+    """The compiled reference.  One flavour (scalar or simd) per process."""
+    path = REF_SIMD if simd else REF_SCALAR
+    L = _load(path)
+    if path not in _ref_booted:
+        L.refshim_boot.argtypes = [C.c_int]
+        L.refshim_boot.restype = C.c_int
+        _ref_booted[path] = L.refshim_boot(tpp)
+    be = Backend("ref", L)
+    be.n_pipeline = _ref_booted[path]
+    return be
+
+
+class RefHost:
+    """Struct constructors of the reference itself (src/grid, src/material,
+    src/field_advance, src/species_advance, src/sf_interface)."""
+
+    def __init__(self, L):
+        self.L = L
+        d, i, f = C.c_double, C.c_int, C.c_float
+        sig = {
+            "new_grid": (_P, []),
+            "partition_periodic_box": (None, [_P] + [d] * 6 + [i] * 6),
+            "partition_metal_box": (None, [_P] + [d] * 6 + [i] * 6),
+            "partition_absorbing_box": (None, [_P] + [d] * 6 + [i] * 7),
+            "set_fbc": (None, [_P, i, i]), "set_pbc": (None, [_P, i, i]),
+            "material": (_P, [C.c_char_p] + [f] * 12),
+            "append_material": (_P, [_P, C.POINTER(_P)]),
+            "new_standard_field_array": (_P, [_P, _P, f]),
+            "new_interpolator_array": (_P, [_P]), "new_accumulator_array": (_P, [_P]),
+            "species": (_P, [C.c_char_p, f, f, C.c_size_t, C.c_size_t, i, i, _P]),
+        }
+        for name, (res, args) in sig.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+
+    def new_grid(self):
+        return self.L.new_grid()
+
+    def partition_periodic_box(self, g, lo, hi, n, topo):
+        self.L.partition_periodic_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo))
+
+    def partition_metal_box(self, g, lo, hi, n, topo):
+        self.L.partition_metal_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo))
+
+    def partition_absorbing_box(self, g, lo, hi, n, topo, pbc):
+        self.L.partition_absorbing_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo), int(pbc))
+
+    def set_fbc(self, g, boundary, fbc):
+        self.L.set_fbc(g, boundary, fbc)
+
+    def set_pbc(self, g, boundary, pbc):
+        self.L.set_pbc(g, boundary, pbc)
+
+    def material_list(self, eps=1.0, mu=1.0, sigma=0.0):
+        m = self.L.material(b"vacuum", eps, eps, eps, mu, mu, mu, sigma, sigma, sigma, 0.0, 0.0, 0.0)
+        head = _P(None)
+        self.L.append_material(m, C.byref(head))
+        return head.value
+
+    def field_array(self, g, m_list, damp):
+        return self.L.new_standard_field_array(g, m_list, damp)
+
+    def interpolator_array(self, g):
+        return self.L.new_interpolator_array(g)
+
+    def accumulator_array(self, g, n_pipeline):
+        return self.L.new_accumulator_array(g)      # n_pipeline is the booted --tpp
+
+    def species(self, name, q, m, max_np, max_nm, sort_interval, sort_out_of_place, g, host_arrays=True):
+        return self.L.species(name.encode(), q, m, max_np, max_nm, sort_interval, sort_out_of_place, g)
+
+
+def ref_facts(L):
+    L.refshim_fact_name.restype = C.c_char_p
+    L.refshim_fact_value.restype = C.c_long
+    return {L.refshim_fact_name(k).decode(): L.refshim_fact_value(k) for k in range(L.refshim_n_facts())}

@@ -1,0 +1,56 @@
+"""Shared problem builders for the tests: seeded synthetic states on the
+reference's POD structs, identical for every backend."""
+import numpy as np
+from vpic_b200 import Simulation, abi
+
+
+def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0.95, damp=0.0,
+             species=(("electron", -1.0, 1.0), ("ion", 1.0, 100.0)), ppc=8, max_np_factor=1.5,
+             sort_interval=0, n_pipeline=1, topo=(1, 1, 1)):
+    nx, ny, nz = n
+    L = length if length is not None else tuple(0.5 * k for k in n)
+    dx = [L[a] / n[a] for a in range(3)]
+    inv = sum(1.0 / d ** 2 for a, d in enumerate(dx) if n[a] > 1)
+    dt = dt_frac / np.sqrt(inv) if inv > 0 else dt_frac * dx[0]
+    s = Simulation(be, host, n_pipeline=n_pipeline)
+    s.define_grid(kind, (0, 0, 0), L, n, topo=topo, dt=float(np.float32(dt)))
+    s.define_fields(damp=damp)
+    ncell = nx * ny * nz
+    for name, q, m in species:
+        s.define_species(name, q, m, int(max_np_factor * ppc * ncell) + 64, sort_interval=sort_interval)
+    return s
+
+
+def random_particles(sim, sp, ppc, vth, seed, w=1.0):
+    g = sim.grid_struct(sim.g)
+    rng = np.random.default_rng(seed)
+    ncell = g.nx * g.ny * g.nz
+    np_ = ppc * ncell
+    p = np.zeros(np_, dtype=abi.particle_dtype)
+    cell = rng.integers(0, ncell, np_)
+    x, y, z = cell % g.nx, (cell // g.nx) % g.ny, cell // (g.nx * g.ny)
+    p["i"] = (x + 1) + (g.nx + 2) * ((y + 1) + (g.ny + 2) * (z + 1))
+    for k in ("dx", "dy", "dz"):
+        p[k] = rng.uniform(-1, 1, np_).astype(np.float32)
+    for k in ("ux", "uy", "uz"):
+        p[k] = (vth * rng.standard_normal(np_)).astype(np.float32)
+    p["w"] = np.float32(w)
+    sim.set_particles(sp, p)
+    return p
+
+
+def random_fields(sim, seed, amp=0.05):
+    g = sim.grid_struct(sim.g)
+    rng = np.random.default_rng(seed)
+    f = sim.fields()
+    for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "tcax", "tcay", "tcaz", "jfx", "jfy", "jfz"):
+        f[k] = (amp * rng.standard_normal(g.nv)).astype(np.float32)
+    return f
+
+
+def same_bits(a, b):
+    """Equal as IEEE values (so -0.0 == +0.0) and NaN-free."""
+    a, b = np.asarray(a), np.asarray(b)
+    if a.dtype.names:
+        return all(same_bits(a[n], b[n]) for n in a.dtype.names if not n.startswith("_"))
+    return a.shape == b.shape and bool(np.all(a == b))

@@ -1,0 +1,85 @@
+"""Pin the CPU oracle (oracle/*.c) against the compiled reference, function by
+function and over whole steps, bit for bit.  Needs oracle/_ref (only built where
+/root/reference exists); the committed golden fixtures cover the other machines."""
+import numpy as np
+import pytest
+from oracle import harness as H
+from common import make_sim, random_particles, random_fields, same_bits
+
+pytestmark = [pytest.mark.ref, pytest.mark.skipif(not H.have_ref(), reason="oracle/_ref not built")]
+
+CASES = [dict(kind="periodic", n=(6, 5, 4)), dict(kind="periodic", n=(16, 1, 1)),
+         dict(kind="periodic", n=(8, 1, 6)), dict(kind="metal", n=(5, 4, 6)),
+         dict(kind="absorbing", n=(5, 6, 4), damp=0.01)]
+
+
+def pair(**kw):
+    ob, rb = H.oracle_backend(), H.ref_backend()
+    so = make_sim(ob, None, **kw)
+    sr = make_sim(rb, H.RefHost(rb.L), **kw)
+    for k, (a, b) in enumerate(zip(so.species, sr.species)):
+        pa = random_particles(so, a, 8, 0.2, 100 + k)
+        sr.set_particles(b, pa)
+    f = random_fields(so, 7)
+    sr.fields()[:] = f
+    return so, sr
+
+
+def compare(so, sr, what=""):
+    assert same_bits(so.fields(), sr.fields()), "fields " + what
+    assert same_bits(so.interpolators(), sr.interpolators()), "interpolators " + what
+    ao, ar = so.accumulators(), sr.accumulators()
+    assert same_bits(ao, ar), "accumulators " + what
+    for a, b in zip(so.species, sr.species):
+        assert so.sp_struct(a).np == sr.sp_struct(b).np and so.sp_struct(a).nm == sr.sp_struct(b).nm
+        assert same_bits(so.particles(a), sr.particles(b)), "particles " + what
+        assert same_bits(so.movers(a), sr.movers(b)), "movers " + what
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_field_kernels(case):
+    so, sr = pair(**case)
+    for s in (so, sr):
+        s.be.load_interpolator_array(s.ia, s.fa)
+        s.be.advance_b(s.fa, 0.5)
+        s.be.synchronize_jf(s.fa)
+        s.be.advance_e(s.fa, 1.0)
+        s.be.advance_b(s.fa, 0.5)
+        s.be.advance_e(s.fa, 1.0)
+        s.be.load_interpolator_array(s.ia, s.fa)
+    compare(so, sr)
+    eo, er = so.be.energy_f6(so.fa), sr.be.energy_f6(sr.fa)
+    assert eo == er
+
+
+@pytest.mark.parametrize("case", CASES[:4])
+def test_particle_kernels(case):
+    so, sr = pair(**case)
+    for s in (so, sr):
+        s.be.load_interpolator_array(s.ia, s.fa)
+        s.be.clear_accumulator_array(s.aa)
+        for sp in s.species_in_list_order():
+            s.be.uncenter_p(sp, s.ia)
+            s.be.advance_p(sp, s.aa, s.ia)
+            s.be.center_p(sp, s.ia)
+        s.be.reduce_accumulator_array(s.aa)
+        s.be.clear_jf(s.fa)
+        s.be.unload_accumulator_array(s.fa, s.aa)
+        for sp in s.species_in_list_order():
+            s.be.sort_p(sp)
+    compare(so, sr)
+    for a, b in zip(so.species, sr.species):
+        nv = so.grid_struct(so.g).nv
+        assert np.array_equal(so.partition(a)[:nv], sr.partition(b)[:nv])
+        assert so.be.energy_p(a, so.ia) == sr.be.energy_p(b, sr.ia)
+
+
+@pytest.mark.parametrize("case", CASES[:4])
+def test_whole_steps(case):
+    so, sr = pair(sort_interval=3, **case)
+    for s in (so, sr):
+        s.initialize()
+    for step in range(12):
+        so.advance(); sr.advance()
+        compare(so, sr, f"step {step}")
+    assert so.energies() == sr.energies()

@@ -1,0 +1,190 @@
+"""Host-side time step: a Python mirror of vpic_simulation::advance()
+(reference: src/vpic/advance.cc:15-208) and of the parts of
+vpic_simulation::initialize() (src/vpic/initialize.cc:4-64) the hot path needs.
+
+It only sequences calls; every array lives in the POD structs of abi.py and
+every computation happens behind a `Backend` (lib.py).  With the product
+backend ("b200") all of it runs on the GPU.
+"""
+import ctypes as C
+import numpy as np
+from . import abi
+from .lib import load_b200, b200_backend
+
+_P = C.c_void_p
+
+
+class B200Host:
+    """Struct constructors from libvpic_b200.so part 3 (pure host code)."""
+
+    def __init__(self):
+        self.L = load_b200()
+
+    def new_grid(self):
+        return self.L.vpic_b200_new_grid()
+
+    def partition_periodic_box(self, g, lo, hi, n, topo):
+        self.L.vpic_b200_partition_periodic_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo))
+
+    def partition_metal_box(self, g, lo, hi, n, topo):
+        self.L.vpic_b200_partition_metal_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo))
+
+    def partition_absorbing_box(self, g, lo, hi, n, topo, pbc):
+        self.L.vpic_b200_partition_absorbing_box(g, *map(float, lo), *map(float, hi), *map(int, n), *map(int, topo), int(pbc))
+
+    def set_fbc(self, g, boundary, fbc):
+        self.L.vpic_b200_set_fbc(g, boundary, fbc)
+
+    def set_pbc(self, g, boundary, pbc):
+        self.L.vpic_b200_set_pbc(g, boundary, pbc)
+
+    def material_list(self, eps=1.0, mu=1.0, sigma=0.0):
+        return self.L.vpic_b200_new_material(b"vacuum", eps, mu, sigma)
+
+    def field_array(self, g, m_list, damp):
+        return self.L.new_standard_field_array(g, m_list, damp)
+
+    def interpolator_array(self, g):
+        return self.L.vpic_b200_new_interpolator_array(g)
+
+    def accumulator_array(self, g, n_pipeline):
+        return self.L.vpic_b200_new_accumulator_array(g, n_pipeline)
+
+    def species(self, name, q, m, max_np, max_nm, sort_interval, sort_out_of_place, g, host_arrays=True):
+        return self.L.vpic_b200_new_species(name.encode(), q, m, max_np, max_nm, sort_interval,
+                                            sort_out_of_place, g, 1 if host_arrays else 0)
+
+
+class Simulation:
+    """grid + fields + species + the reference's step sequence."""
+
+    def __init__(self, backend=None, host=None, n_pipeline=1):
+        self.be = backend if backend is not None else b200_backend()
+        self.host = host if host is not None else B200Host()
+        self.n_pipeline = n_pipeline
+        self.species = []          # definition order; the reference's list head is the LAST one
+        self.num_comm_round = 3    # src/vpic/vpic.cc:79
+        self.g = self.fa = self.ia = self.aa = None
+
+    # ---- setup (deck-like helpers, src/vpic/vpic.h:326-653) ----
+    def define_grid(self, kind, lo, hi, n, topo=(1, 1, 1), dt=None, cvac=1.0, eps0=1.0, pbc=-2):
+        g = self.host.new_grid()
+        gs = self.grid_struct(g)
+        gs.cvac, gs.eps0 = cvac, eps0
+        gs.dt = dt if dt is not None else 0.0
+        if kind == "periodic":
+            self.host.partition_periodic_box(g, lo, hi, n, topo)
+        elif kind == "metal":
+            self.host.partition_metal_box(g, lo, hi, n, topo)
+        elif kind == "absorbing":
+            self.host.partition_absorbing_box(g, lo, hi, n, topo, pbc)
+        else:
+            raise ValueError(kind)
+        self.g = g
+        return g
+
+    @staticmethod
+    def grid_struct(g):
+        return C.cast(g, C.POINTER(abi.Grid)).contents
+
+    def define_fields(self, damp=0.0, eps=1.0, mu=1.0, sigma=0.0):
+        self.m_list = self.host.material_list(eps, mu, sigma)
+        self.fa = self.host.field_array(self.g, self.m_list, damp)
+        self.ia = self.host.interpolator_array(self.g)
+        self.aa = self.host.accumulator_array(self.g, self.n_pipeline)
+
+    def define_species(self, name, q, m, max_np, max_nm=None, sort_interval=0, sort_out_of_place=1, host_arrays=True):
+        if max_nm is None:
+            max_nm = max(16, int(0.05 * max_np))
+        sp = self.host.species(name, q, m, max_np, max_nm, sort_interval, sort_out_of_place, self.g, host_arrays)
+        s = self.sp_struct(sp)
+        s.id = len(self.species)
+        # append_species pushes on the front of the list (species_advance.c:96-98)
+        s.next = C.cast(self.species[-1], C.POINTER(abi.Species)) if self.species else None
+        self.species.append(sp)
+        return sp
+
+    @staticmethod
+    def sp_struct(sp):
+        return C.cast(sp, C.POINTER(abi.Species)).contents
+
+    @property
+    def sp_list_head(self):
+        return self.species[-1] if self.species else None
+
+    def species_in_list_order(self):
+        return list(reversed(self.species))
+
+    # ---- array views ----
+    def particles(self, sp):
+        s = self.sp_struct(sp)
+        return abi.as_array(s.p, s.np, abi.particle_dtype)
+
+    def set_particles(self, sp, arr):
+        s = self.sp_struct(sp)
+        n = len(arr)
+        if n > s.max_np:
+            raise ValueError("too many particles")
+        abi.as_array(s.p, s.max_np, abi.particle_dtype)[:n] = arr
+        s.np = n
+        s.nm = 0
+
+    def fields(self):
+        fa = C.cast(self.fa, C.POINTER(abi.FieldArray)).contents
+        return abi.as_array(fa.f, self.grid_struct(self.g).nv, abi.field_dtype)
+
+    def interpolators(self):
+        ia = C.cast(self.ia, C.POINTER(abi.InterpolatorArray)).contents
+        return abi.as_array(ia.i, self.grid_struct(self.g).nv, abi.interp_dtype)
+
+    def accumulators(self):
+        aa = C.cast(self.aa, C.POINTER(abi.AccumulatorArray)).contents
+        return abi.as_array(aa.a, (aa.n_pipeline + 1) * aa.stride, np.dtype(("f4", (12,))))
+
+    def partition(self, sp):
+        s = self.sp_struct(sp)
+        return abi.as_array(s.partition, self.grid_struct(self.g).nv + 1, np.int32)
+
+    def movers(self, sp):
+        s = self.sp_struct(sp)
+        return abi.as_array(s.pm, s.nm, abi.mover_dtype)
+
+    # ---- initialize(): the tail of src/vpic/initialize.cc:33-54 ----
+    def initialize(self, uncenter=True):
+        be = self.be
+        be.load_interpolator_array(self.ia, self.fa)
+        if uncenter:
+            for sp in self.species_in_list_order():
+                be.uncenter_p(sp, self.ia)
+
+    # ---- advance(): src/vpic/advance.cc:15-208 ----
+    def advance(self):
+        be, g = self.be, self.grid_struct(self.g)
+        for sp in self.species_in_list_order():                       # :25-29
+            s = self.sp_struct(sp)
+            if s.sort_interval > 0 and (g.step % s.sort_interval) == 0:
+                be.sort_p(sp)
+        be.clear_accumulator_array(self.aa)                           # :36-37
+        for sp in self.species_in_list_order():                       # :49-50
+            be.advance_p(sp, self.aa, self.ia)
+        be.reduce_accumulator_array(self.aa)                          # :65-66
+        for _ in range(self.num_comm_round):                          # :73-77
+            be.boundary_p(None, self.sp_list_head, self.fa, self.aa)
+        for sp in self.species_in_list_order():                       # :78-101 (drop unprocessed movers)
+            if self.sp_struct(sp).nm:
+                raise RuntimeError("unprocessed particle movers left after boundary_p")
+        be.clear_jf(self.fa)                                          # :107-110
+        be.unload_accumulator_array(self.fa, self.aa)
+        be.synchronize_jf(self.fa)
+        be.advance_b(self.fa, 0.5)                                    # :123
+        be.advance_e(self.fa, 1.0)                                    # :127
+        be.advance_b(self.fa, 0.5)                                    # :137
+        be.load_interpolator_array(self.ia, self.fa)                  # :185
+        g.step += 1                                                   # :187
+
+    # ---- diagnostics: dump_energies (src/vpic/dump.cc:37-77) ----
+    def energies(self):
+        en = self.be.energy_f6(self.fa)
+        for sp in self.species_in_list_order():
+            en.append(self.be.energy_p(sp, self.ia))
+        return en
