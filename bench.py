@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py -- particle pushes/s (and Yee cell updates/s) of the VPIC hot path.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--cells XxYxZ] [--ppc P]
+  python bench.py --impl reference ...      # the reference's CPU code on host cores
+
+A "step" is one full PIC step (src/vpic/advance.cc:15-208) of the weak-scaled
+uniform-plasma configuration of BASELINE.json (512x256x256 cells per GPU, 2
+species; 32 particles per cell per species because species_t.np is 32-bit), on
+synthetic Maxwellian particles born on the device.  `value` counts every
+particle pushed by every rank per second of max-over-ranks device time for the
+WHOLE step (sort, push, deposit, unload, field advance, interpolator load).
+`roofline` is the advance_p kernel alone; `e2e` drives the same entry points
+with host-resident arrays (STRICT coherence: host->device and device->host
+copies inside every call); `cpu_baseline` is the reference's own SIMD build
+timed on this box's host cores on a bounded sample.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cells", default="512x256x256", help="cells per GPU")
+    ap.add_argument("--ppc", type=int, default=32, help="particles per cell per species")
+    ap.add_argument("--sort-interval", type=int, default=4)
+    ap.add_argument("--e2e-cells", default="256x128x128")
+    ap.add_argument("--cpu-cells", default="64x64x32")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-yee", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.samples.append([x.strip() for x in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            for k, n in enumerate(names):
+                if len(s) > 2 + k and s[2 + k].lower().startswith("active"):
+                    reasons.add(n)
+        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dims(s):
+    return tuple(int(x) for x in s.lower().split("x"))
+
+
+def uniform_plasma(be, host, n, ppc, sort_interval, topo=(1, 1, 1), host_arrays=False, n_pipeline=1):
+    """C1/C4 physics: dx = 0.5 c/wpe, dt = 0.95 Courant, e- (vth 0.1c) + ion (m=100, vth 0.01c)."""
+    import numpy as np
+    from vpic_b200 import Simulation
+    s = Simulation(be, host, n_pipeline=n_pipeline)
+    gn = tuple(n[a] * topo[a] for a in range(3))
+    L = tuple(0.5 * k for k in gn)
+    dt = 0.95 / np.sqrt(sum(1.0 / 0.25 for a in range(3) if gn[a] > 1))
+    s.define_grid("periodic", (0, 0, 0), L, gn, topo=topo, dt=float(np.float32(dt)))
+    s.define_fields(damp=0.0)
+    ncell = n[0] * n[1] * n[2]
+    cap = int(ppc * ncell * 1.02) + 1024
+    w = 0.125 / ppc                                    # n0 dV / ppc with n0 = 1
+    sp_e = s.define_species("electron", -1.0, 1.0, cap, max(4096, cap // 50), sort_interval, 1, host_arrays)
+    sp_i = s.define_species("ion", 1.0, 100.0, cap, max(4096, cap // 50), sort_interval, 1, host_arrays)
+    return s, ((sp_e, 0.1, w), (sp_i, 0.01, w))
+
+
+class EventTimer:
+    """CUDA-event timing on the library's own stream."""
+
+    def __init__(self, torch, stream_ptr, device):
+        self.torch = torch
+        self.stream = torch.cuda.ExternalStream(stream_ptr, device=device)
+        self.pairs = []
+
+    def wrap(self, fn):
+        def timed(*a):
+            e0 = self.torch.cuda.Event(enable_timing=True); e1 = self.torch.cuda.Event(enable_timing=True)
+            e0.record(self.stream); r = fn(*a); e1.record(self.stream)
+            self.pairs.append((e0, e1))
+            return r
+        return timed
+
+    def total_ms(self):
+        self.torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in self.pairs)
+        n = len(self.pairs)
+        self.pairs = []
+        return t, n
+
+
+def timed_steps(torch, sim, L, stream, steps, dist_barrier):
+    dist_barrier(); torch.cuda.synchronize()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    l0 = L.vpic_b200_launch_count()
+    e0.record(stream)
+    for _ in range(steps):
+        sim.advance()
+    e1.record(stream)
+    torch.cuda.synchronize(); dist_barrier()
+    return e0.elapsed_time(e1), L.vpic_b200_launch_count() - l0
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    from vpic_b200 import load_b200, b200_backend, B200Host
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    L = load_b200()
+    # each rank is a rank-0-of-1 periodic brick until the NCCL halo exchange lands
+    L.vpic_b200_init(local, 0, 1)
+    L.vpic_b200_set_coherence(1)           # RESIDENT
+    be, host = b200_backend(), B200Host()
+    stream = torch.cuda.ExternalStream(L.vpic_b200_stream(), device=local)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    n = dims(args.cells)
+    sim, sps = uniform_plasma(be, host, n, args.ppc, args.sort_interval)
+    for k, (sp, vth, w) in enumerate(sps):
+        L.vpic_b200_load_uniform_maxwellian(sp, args.ppc, vth, w, 1234 + 17 * k + 1000 * rank)
+    sim.initialize()
+    np_total = sum(sim.sp_struct(sp).np for sp, _, _ in sps)
+    tm = EventTimer(torch, L.vpic_b200_stream(), local)
+    be.advance_p = tm.wrap(be.advance_p)
+
+    for _ in range(args.warmup):
+        sim.advance()
+    tm.total_ms()
+    sampler = ClockSampler(local); sampler.start()
+    ms, launches = timed_steps(torch, sim, L, stream, args.steps, barrier)
+    sampler.stop_flag = True; sampler.join(timeout=2)
+    ap_ms, ap_calls = tm.total_ms()
+    if dist is not None:
+        t = torch.tensor([ms, ap_ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms, ap_ms = t.tolist()
+    pushes = np_total * world * args.steps
+    value = pushes / (ms * 1e-3)
+
+    # roofline of the dominant kernel (advance_p): SURVEY 8d algorithmic bytes
+    peak, peak_src = peaks()
+    bytes_per_push = 64.0 + 176.0 / args.ppc
+    ach = np_total * args.steps * bytes_per_push / (ap_ms * 1e-3) / 1e9
+    roofline = {"kernel": "k_advance_p", "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
+                "bytes_per_push": bytes_per_push, "ms_per_launch": ap_ms / max(ap_calls, 1),
+                "pushes_per_s_kernel_only": np_total * args.steps / (ap_ms * 1e-3),
+                "share_of_step": round(ap_ms / ms, 4)}
+    out = {"metric": "particle_pushes_per_sec", "value": value, "unit": "pushes/s", "n_gpus": world,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"uniform Maxwellian e-/ion plasma, periodic {args.cells} cells per GPU, "
+                                  f"2 species x {args.ppc} ppc, sort every {args.sort_interval} steps (BASELINE configs[3])",
+                      "particles_per_gpu": np_total, "l2": "inputs (particles, fields) far larger than the 126 MB L2",
+                      "parallelism": "1 GPU" if world == 1 else f"{world} independent periodic bricks (halo exchange not wired yet)"},
+           "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary()}
+    free_sim(L, sim)
+
+    if rank == 0 and not args.no_yee:
+        out["yee"] = bench_yee(torch, L, be, host, stream, peak)
+    if rank == 0 and not args.no_e2e:
+        out["e2e"] = bench_e2e(torch, L, be, host, stream, args)
+    else:
+        out["e2e"] = None
+    if rank == 0 and not args.no_cpu:
+        try:
+            out["cpu_baseline"] = cpu_baseline(args)
+        except Exception as e:      # the checker must never take the product's number down
+            out["cpu_baseline"] = {"error": repr(e)}
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.barrier(); dist.destroy_process_group()
+
+
+def free_sim(L, sim):
+    for sp in sim.species:
+        L.vpic_b200_delete_species(sp)
+    L.vpic_b200_delete_interpolator_array(sim.ia); L.vpic_b200_delete_accumulator_array(sim.aa)
+    L.delete_field_array(sim.fa); L.vpic_b200_delete_grid(sim.g)
+
+
+def bench_yee(torch, L, be, host, stream, peak, n=(256, 256, 256), steps=50):
+    """BASELINE configs[1]: vacuum EM wave, periodic 256^3, field kernels only."""
+    import numpy as np
+    from vpic_b200 import Simulation
+    s = Simulation(be, host)
+    s.define_grid("periodic", (0, 0, 0), tuple(float(k) for k in n), n, dt=float(np.float32(0.95 / np.sqrt(3.0))))
+    s.define_fields(damp=0.0)
+    f = s.fields(); g = s.grid_struct(s.g)
+    x = (np.arange(g.nv) % (g.nx + 2)).astype(np.float64)
+    f["ey"] = np.sin(2 * np.pi * (x - 1) / n[0]).astype(np.float32)
+    f["cbz"] = np.sin(2 * np.pi * (x - 0.5) / n[0]).astype(np.float32)
+    ncell = n[0] * n[1] * n[2]
+    res = {}
+    for name, fn, bpc in (("advance_b", lambda: be.advance_b(s.fa, 0.5), 36.0),
+                          ("advance_e", lambda: be.advance_e(s.fa, 1.0), 72.0),
+                          ("field_step", lambda: (be.advance_b(s.fa, 0.5), be.advance_e(s.fa, 1.0), be.advance_b(s.fa, 0.5)), 144.0)):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        res[name] = {"cell_updates_per_s": ncell / (ms * 1e-3), "ms": ms, "GB/s": ncell * bpc / (ms * 1e-3) / 1e9,
+                     "frac_of_hbm_peak": ncell * bpc / (ms * 1e-3) / 1e9 / peak, "bytes_per_cell": bpc}
+    res["workload"] = "vacuum, periodic %dx%dx%d (BASELINE configs[1])" % n
+    free_sim(L, s)
+    return res
+
+
+def bench_e2e(torch, L, be, host, stream, args, steps=3):
+    """Same step through the reference-facing entry points with HOST arrays:
+    STRICT coherence, so every call uploads what it reads from the host structs
+    and downloads what it wrote (particles, accumulators, fields ...)."""
+    import numpy as np
+    n = dims(args.e2e_cells)
+    L.vpic_b200_set_coherence(0)           # STRICT
+    try:
+        sim, sps = uniform_plasma(be, host, n, args.ppc, args.sort_interval, host_arrays=True)
+        for k, (sp, vth, w) in enumerate(sps):
+            L.vpic_b200_load_uniform_maxwellian(sp, args.ppc, vth, w, 99 + k)   # lands in the host arrays (STRICT)
+        sim.initialize()
+        np_total = sum(sim.sp_struct(sp).np for sp, _, _ in sps)
+        sim.advance()                      # warm-up (allocations, first touch)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            sim.advance()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        g = sim.grid_struct(sim.g)
+        nv = g.nv
+        # bytes per step, counted from the arrays each STRICT call moves (see vpb_mirrors.cu):
+        #   advance_p x2: particles up+down, accumulator up+down, interpolator up
+        #   sort (1/interval): particles up+down ; field calls: 80 B/voxel up+down each
+        part = np_total * 32
+        h2d = part + 2 * nv * (48 + 80) + part / args.sort_interval + 7 * nv * 80 + nv * 48
+        d2h = part + 2 * nv * 48 + part / args.sort_interval + 6 * nv * 80 + nv * 80 + nv * 48
+        res = {"value": np_total * steps / dt, "unit": "pushes/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt / steps * 1e3,
+               "workload": f"same physics, {args.e2e_cells} cells x 2 species x {args.ppc} ppc resident in HOST memory "
+                           f"(pageable, as the reference allocates it); STRICT coherence", "particles": np_total}
+        free_sim(L, sim)
+        return res
+    finally:
+        L.vpic_b200_set_coherence(1)
+
+
+def host_simd_ok():
+    try:
+        flags = open("/proc/cpuinfo").read()
+        return " avx2" in flags and " fma" in flags
+    except Exception:
+        return False
+
+
+def reference_run(args, steps, warmup):
+    """The reference's own CPU implementation of the step on the host cores."""
+    import numpy as np
+    from oracle import harness as H
+    cores = len(os.sched_getaffinity(0))
+    simd = host_simd_ok() and H.have_ref(simd=True)
+    if H.have_ref(simd=simd):
+        be = H.ref_backend(simd=simd, tpp=cores)
+        host, kind = H.RefHost(be.L), "reference"
+        build = "reference V4+V8 AVX2 build (oracle/_ref/libvpic_ref_simd.so)" if simd else "reference scalar build"
+        tpp = be.n_pipeline
+    else:
+        be, host, kind, build, tpp = H.oracle_backend(), None, "port", "C restatement oracle/liboracle.so", 1
+    n = dims(args.cpu_cells)
+    sim, sps = uniform_plasma(be, host, n, args.ppc, 20, host_arrays=True, n_pipeline=tpp)
+    rng = np.random.default_rng(5)
+    from vpic_b200 import abi
+    g = sim.grid_struct(sim.g)
+    ncell = g.nx * g.ny * g.nz
+    for sp, vth, w in sps:
+        npart = args.ppc * ncell
+        p = np.zeros(npart, dtype=abi.particle_dtype)
+        cell = np.repeat(np.arange(ncell), args.ppc)
+        x, y, z = cell % g.nx, (cell // g.nx) % g.ny, cell // (g.nx * g.ny)
+        p["i"] = (x + 1) + (g.nx + 2) * ((y + 1) + (g.ny + 2) * (z + 1))
+        for k in ("dx", "dy", "dz"):
+            p[k] = rng.uniform(-1, 1, npart).astype(np.float32)
+        for k in ("ux", "uy", "uz"):
+            p[k] = (vth * rng.standard_normal(npart)).astype(np.float32)
+        p["w"] = np.float32(w)
+        sim.set_particles(sp, p)
+    sim.initialize()
+    np_total = sum(sim.sp_struct(sp).np for sp, _, _ in sps)
+    t_ap = [0.0]
+    raw = be.advance_p
+
+    def timed_ap(*a):
+        t = time.perf_counter(); raw(*a); t_ap[0] += time.perf_counter() - t
+    be.advance_p = timed_ap
+    for _ in range(warmup):
+        sim.advance()
+    t_ap[0] = 0.0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.advance()
+    dt = time.perf_counter() - t0
+    return {"value": np_total * steps / dt, "unit": "pushes/s", "cores": tpp, "kind": kind,
+            "sample": f"{build}, --tpp {tpp}, {args.cpu_cells} cells x 2 species x {args.ppc} ppc "
+                      f"({np_total} particles), {steps} full steps",
+            "advance_p_only_pushes_per_s": np_total * steps / max(t_ap[0], 1e-9), "ms_per_step": dt / steps * 1e3}
+
+
+def cpu_baseline(args):
+    return reference_run(args, steps=3, warmup=1)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    r = reference_run(args, steps=max(1, min(args.steps, 5)), warmup=max(1, min(args.warmup, 2)))
+    out = {"impl": "reference", "metric": "particle_pushes_per_sec", "value": r["value"], "unit": "pushes/s",
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "uniform Maxwellian e-/ion plasma, periodic, 2 species (bounded CPU sample of BASELINE configs[3])"},
+           "cpu_baseline": r,
+           "e2e": {"value": r["value"], "unit": "pushes/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

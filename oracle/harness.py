@@ -48,7 +48,17 @@ def ref_backend(simd=False, tpp=1):
     if path not in _ref_booted:
         L.refshim_boot.argtypes = [C.c_int]
         L.refshim_boot.restype = C.c_int
-        _ref_booted[path] = L.refshim_boot(tpp)
+        # the reference prints a boot banner on stdout; keep stdout clean for
+        # callers that promise one JSON line (bench.py)
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            _ref_booted[path] = L.refshim_boot(tpp)
+            C.CDLL(None).fflush(None)
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
     be = Backend("ref", L)
     be.n_pipeline = _ref_booted[path]
     return be
