@@ -26,8 +26,8 @@ def gpu():
 
 
 def pair(gpu, ppc=8, vth=0.2, **kw):
-    so = make_sim(H.oracle_backend(), None, **kw)
-    sg = make_sim(gpu, None, **kw)
+    so = make_sim(H.oracle_backend(), None, ppc=ppc, **kw)
+    sg = make_sim(gpu, None, ppc=ppc, **kw)
     for k, (a, b) in enumerate(zip(so.species, sg.species)):
         sg.set_particles(b, random_particles(so, a, ppc, vth, 100 + k))
     sg.fields()[:] = random_fields(so, 7)
