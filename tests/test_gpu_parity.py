@@ -97,6 +97,7 @@ def test_sort_edge_cases(gpu):
         so.be.sort_p(a); sg.be.sort_p(b)
         assert np.array_equal(sg.partition(b)[:nv], so.partition(a)[:nv])
     so, sg = pair(gpu, kind="periodic", n=(2, 2, 2), ppc=700, max_np_factor=1.1)
+    nv = so.grid_struct(so.g).nv
     for a, b in zip(so.species, sg.species):
         p = so.particles(a); p["i"][: len(p) * 3 // 4] = p["i"][0]      # ~4200 in one voxel
         sg.particles(b)["i"][:] = p["i"]

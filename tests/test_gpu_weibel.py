@@ -33,9 +33,13 @@ def test_weibel_700_steps_vs_energies_gold():
     nz = b_sum > 0
     assert np.all(np.abs(b_sum_g[nz] - b_sum[nz]) <= 0.03 * b_sum[nz])
     assert np.all(np.abs(p_sum_g - p_sum) <= 0.01 * p_sum)
-    # ours: particle energies to print precision for the whole run, and the first
-    # 50 steps of every field energy to 1e-4 relative (of the component's max)
-    assert np.all(np.abs(got[:, 7:9] - gold[:, 7:9]) <= 2e-6 * gold[:, 7:9])
+    # ours (FAST deposit: currents are summed in a different order than the
+    # reference, so the chaotic 700-step run drifts at the 1e-5 level): particle
+    # energies to 1e-4 for the whole run, print precision for the first 50 steps,
+    # and the first 50 steps of every field energy to 1e-4 relative (of the
+    # component's max)
+    assert np.all(np.abs(got[:, 7:9] - gold[:, 7:9]) <= 1e-4 * gold[:, 7:9])
+    assert np.all(np.abs(got[:51, 7:9] - gold[:51, 7:9]) <= 2e-6 * gold[:51, 7:9])
     for c in range(1, 7):
         scale = max(gold[:51, c].max(), 1e-30)
         assert np.abs(got[:51, c] - gold[:51, c]).max() <= 1e-4 * scale, c

@@ -3,22 +3,28 @@
 // Reference: src/species_advance/standard/pipeline/advance_p_pipeline.cc:20-314,
 //            src/species_advance/standard/move_p.cc:216-353.
 //
-// B200 design (FAST deposit):
-//  * particle_t is streamed as two 128-bit loads / stores per particle; a warp
-//    owns a STRIP of consecutive particles split into two half strips (lanes
-//    0-15 / 16-31) so every half-warp access is a contiguous 512 B run.
-//  * the 18 interpolator coefficients are gathered with read-only 128-bit loads;
-//    with cell-sorted particles neighbouring lanes hit the same 80 B record so
-//    the gather is an L1 broadcast.
-//  * deposit: the 12 currents of the 32 particles of one iteration are staged in
-//    shared memory; 24 "walker" lanes (12 components x 2 half strips) then add
-//    them up sequentially along the strip, carrying the running sum across
-//    iterations while the voxel stays the same, and commit one red.global.add
-//    per component only when the voxel changes.  For sorted particles that is
-//    ~12 atomics per (voxel, warp) instead of 12 per particle.
-//  * particles that leave their voxel run move_p in the kernel (divergent, rare)
-//    and deposit their streaks with plain atomics; those that leave the rank's
-//    domain are appended to the mover list for boundary_p.
+// B200 design (FAST deposit), sized from the round-1 ncu capture
+// (profiles/r1a_advance_p.md): the first kernel was issue-bound at ~670 thread
+// instructions per push, more than half of them spent reducing currents and
+// walking divergent move_p loops.  This kernel:
+//
+//  * A warp owns a TILE of 32*AP_K consecutive particles (8 KB).  One elected
+//    lane brings the tile into shared memory with a single bulk asynchronous
+//    copy (cp.async.bulk, completion on an mbarrier), prefetches the warp's
+//    NEXT tile into L2 (cp.async.bulk.prefetch.L2), and after the push writes
+//    the tile back with one bulk store.  No per-particle LDG/STG at all.
+//  * Each LANE walks AP_K CONSECUTIVE particles of the tile (its own 256 B run
+//    of the array).  With cell-sorted particles a lane stays in one voxel for
+//    most of its run, so it keeps that voxel's 18 interpolator coefficients
+//    and the 12 running current sums in REGISTERS, and only when the voxel
+//    changes commits the sums with three 128-bit vector reductions
+//    (red.global.add.v4.f32) and re-gathers the coefficients.  Deposit cost
+//    drops from ~250 to ~15 instructions per push.
+//  * Particles that leave their voxel are not moved in line (that loop is
+//    divergent and ran at <10 % lane utilisation).  They are pushed on a
+//    per-warp queue in shared memory; whenever 32 are waiting the whole warp
+//    runs move_p on them with every lane busy.
+//
 // Algorithmic HBM traffic: 32 B read + 32 B written per particle plus, per
 // voxel, 80 B interpolator + 48 B accumulator read-modify-write (SURVEY 8d:
 // 64 + 176/ppc bytes per push).
@@ -26,107 +32,194 @@
 
 namespace vpb {
 
-constexpr int AP_WARPS   = 8;                 // warps per block
-constexpr int AP_ITERS   = 8;                 // iterations per strip
-constexpr int AP_STRIP   = 32*AP_ITERS;       // particles per warp
-constexpr int AP_HALF    = 16*AP_ITERS;       // particles per half strip
-constexpr int AP_SSTRIDE = 33;                // smem row stride (bank-conflict free)
+constexpr int AP_K      = 8;            // consecutive particles per lane
+constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
+constexpr int AP_WARPS  = 4;            // warps per block
+constexpr int AP_MINBLK = 4;            // resident blocks per SM the registers are budgeted for
+constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 
-__global__ void __launch_bounds__( 32*AP_WARPS )
-k_advance_p( vpb_particle_t * __restrict__ p, int np,
+struct __align__(128) WarpTile {
+  float4 tile[2*AP_TILE];               // the particles, array order (8 KB)
+  // queue of particles that left their voxel (structure of arrays)
+  int   q_idx[AP_QCAP];                 // index in sp->p
+  float q_dx[AP_QCAP], q_dy[AP_QCAP], q_dz[AP_QCAP];
+  int   q_i[AP_QCAP];
+  float q_dispx[AP_QCAP], q_dispy[AP_QCAP], q_dispz[AP_QCAP];
+  float q_q[AP_QCAP];
+  unsigned long long bar;               // mbarrier of the tile load
+};
+
+__device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_t)__cvta_generic_to_shared( p ); }
+
+__device__ __forceinline__ void red_add_v4( float * addr, float a, float b, float c, float d ) {
+  asm volatile( "red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory" );
+}
+
+__device__ __forceinline__ void commit_currents( float * __restrict__ acc, int voxel, const float * j ) {
+  float * a = acc + (size_t)voxel*ACC_STRIDE;
+  red_add_v4( a,   j[0], j[1], j[2],  j[3]  );
+  red_add_v4( a+4, j[4], j[5], j[6],  j[7]  );
+  red_add_v4( a+8, j[8], j[9], j[10], j[11] );
+}
+
+// Run move_p (move_p.cc:216-353) on up to 32 queued particles, one per lane.
+// Entries of the tile that is still in shared memory are finished there;
+// entries of tiles already written back are finished in global memory.
+__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane,
+                                                vpb_particle_t * __restrict__ p, long long t0, int cnt, bool tile_live,
+                                                float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
+                                                int max_nm, int * __restrict__ counters, const GridDev & g ) {
+  if( lane>=n ) return;
+  const int e = base + lane;
+  const int idx = S.q_idx[e];
+  const bool in_tile = tile_live && idx>=t0 && idx<t0+cnt;
+  float4 * slot = in_tile ? &S.tile[ 2*(int)( idx-t0 ) ] : reinterpret_cast<float4 *>( p + idx );
+  const float4 r1 = slot[1];
+  MoveState ms;
+  ms.dx = S.q_dx[e]; ms.dy = S.q_dy[e]; ms.dz = S.q_dz[e]; ms.i = S.q_i[e];
+  ms.ux = r1.x; ms.uy = r1.y; ms.uz = r1.z;
+  ms.dispx = S.q_dispx[e]; ms.dispy = S.q_dispy[e]; ms.dispz = S.q_dispz[e];
+  const float q = S.q_q[e];
+  float j[12];
+  int status; bool reflected = false;
+  do {
+    int vox;
+    const float ux0 = ms.ux, uy0 = ms.uy, uz0 = ms.uz;
+    status = move_p_streak( ms, q, g, j, vox );
+    reflected |= ( ms.ux!=ux0 ) | ( ms.uy!=uy0 ) | ( ms.uz!=uz0 );
+    commit_currents( acc, vox, j );
+  } while( status==1 );
+  slot[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
+  if( reflected ) slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );
+  if( status==2 ) {
+    const int k = atomicAdd( counters+0, 1 );
+    if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
+    else atomicAdd( counters+1, 1 );
+  }
+}
+
+__global__ void __launch_bounds__( 32*AP_WARPS, AP_MINBLK )
+k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
              const float * __restrict__ ip, float * __restrict__ acc,
              vpb_particle_mover_t * __restrict__ pm, int max_nm, int * __restrict__ counters,
              GridDev g, PushCoef c ) {
-  __shared__ float s_val[AP_WARPS][12*AP_SSTRIDE];
-  __shared__ int   s_vox[AP_WARPS][32];
+  __shared__ WarpTile s_all[AP_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int half = lane >> 4, hl = lane & 15;
-  const long long strip0 = ( (long long)blockIdx.x*AP_WARPS + warp )*AP_STRIP;
-  if( strip0>=np ) return;
-  float * sv = s_val[warp]; int * sx = s_vox[warp];
-  // walker state: lane (half, comp) sums component comp of its half strip
-  const int comp = hl;                        // 0..11 active
-  int cur = -1; float run = 0.f;
+  WarpTile & S = s_all[warp];
+  const int total_warps = gridDim.x*AP_WARPS;
+  const int gw = blockIdx.x*AP_WARPS + warp;
+  if( gw>=ntile ) return;
+  const uint32_t bar = smem_u32( &S.bar ), tile_s = smem_u32( S.tile );
+  if( lane==0 ) {
+    asm volatile( "mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory" );
+    asm volatile( "fence.mbarrier_init.release.cluster;" ::: "memory" );
+    asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
+  }
+  __syncwarp();
 
-  for( int it=0; it<AP_ITERS; it++ ) {
-    const long long idx = strip0 + (long long)half*AP_HALF + it*16 + hl;
-    const bool valid = idx<np;
-    float j[12];
-    int dep_vox = -1;
-    bool crosser = false;
-    MoveState ms; float q = 0.f, w_keep = 0.f;
-    if( valid ) {
-      float4 * pp = reinterpret_cast<float4 *>( p + idx );
-      const float4 r0 = pp[0], r1 = pp[1];
-      float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
-      float ux = r1.x, uy = r1.y, uz = r1.z; q = r1.w; w_keep = r1.w;
-      const Interp f = load_interp( ip, ii );
-      boris( f, c, dx, dy, dz, ux, uy, uz );
-      const float sux = ux, suy = uy, suz = uz;            // momentum to store
-      const float one = 1.0f, one_third = 1.0/3.0;
-      float v0 = one/sqrtf( one + ( ux*ux + ( uy*uy + uz*uz ) ) );
-      ux *= c.cdt_dx; uy *= c.cdt_dy; uz *= c.cdt_dz;
-      ux *= v0; uy *= v0; uz *= v0;
-      v0 = dx + ux; const float v1 = dy + uy, v2 = dz + uz;  // streak midpoint
-      const float v3 = v0 + ux, v4 = v1 + uy, v5 = v2 + uz;  // new position
-      q *= c.qsp;
-      if( v3<=one && v4<=one && v5<=one && -v3<=one && -v4<=one && -v5<=one ) {
-        pp[0] = make_float4( v3, v4, v5, r0.w );
-        pp[1] = make_float4( sux, suy, suz, r1.w );
-        streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
-        dep_vox = ii;
-      } else {
-        crosser = true;
-        ms.dx = dx; ms.dy = dy; ms.dz = dz; ms.i = ii;
-        ms.ux = sux; ms.uy = suy; ms.uz = suz;
-        ms.dispx = ux; ms.dispy = uy; ms.dispz = uz;
+  uint32_t phase = 0;
+  int qn = 0;                                  // queued crossers (warp uniform)
+  int cur = -1;                                // voxel whose coefficients / sums this lane holds
+  float run[12];
+# pragma unroll
+  for( int k=0; k<12; k++ ) run[k] = 0.f;
+  Interp f = {};
+
+  for( int tile=gw; tile<ntile; tile+=total_warps ) {
+    const long long t0 = (long long)tile*AP_TILE;
+    const int cnt = ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE;
+    if( lane==0 ) {
+      const uint32_t bytes = (uint32_t)cnt*32u;
+      asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
+      asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                    :: "r"(tile_s), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
+      const int nt = tile + total_warps;
+      if( nt<ntile ) {
+        const long long n0 = (long long)nt*AP_TILE;
+        const uint32_t nb = (uint32_t)( ( np - n0 < AP_TILE ) ? ( np - n0 ) : AP_TILE )*32u;
+        asm volatile( "cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p + n0), "r"(nb) : "memory" );
       }
     }
-    // ---- stage the in-voxel currents and walk them ----
-    sx[lane] = dep_vox;
-    if( dep_vox>=0 ) {
-#     pragma unroll
-      for( int k=0; k<12; k++ ) sv[ k*AP_SSTRIDE + lane ] = j[k];
+    {
+      uint32_t ok;
+      do {
+        asm volatile( "{ .reg .pred P1; mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2; selp.u32 %0, 1, 0, P1; }"
+                      : "=r"(ok) : "r"(bar), "r"(phase) : "memory" );
+      } while( !ok );
+      phase ^= 1u;
     }
-    __syncwarp();
-    if( comp<12 ) {
-      const int * vx = sx + 16*half;
-      const float * vv = sv + comp*AP_SSTRIDE + 16*half;
-#     pragma unroll
-      for( int k=0; k<16; k++ ) {
-        const int vox = vx[k];
-        if( vox>=0 ) {
-          if( vox!=cur ) {
-            if( cur>=0 ) atomicAdd( acc + (size_t)cur*ACC_STRIDE + comp, run );
-            cur = vox; run = 0.f;
-          }
-          run += vv[k];
+
+#   pragma unroll 1
+    for( int k=0; k<AP_K; k++ ) {
+      // rotate the start of each lane's run so the 128-bit shared accesses of a
+      // quarter warp spread over the banks
+      const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
+      bool cross = false;
+      float cdx = 0, cdy = 0, cdz = 0, cux = 0, cuy = 0, cuz = 0, cq = 0; int ci = 0;
+      if( loc<cnt ) {
+        const float4 r0 = S.tile[2*loc], r1 = S.tile[2*loc+1];
+        const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
+        float ux = r1.x, uy = r1.y, uz = r1.z;
+        if( ii!=cur ) {
+          if( cur>=0 ) commit_currents( acc, cur, run );
+#         pragma unroll
+          for( int m=0; m<12; m++ ) run[m] = 0.f;
+          cur = ii;
+          f = load_interp( ip, ii );
+        }
+        boris( f, c, dx, dy, dz, ux, uy, uz );
+        const float sux = ux, suy = uy, suz = uz;            // momentum to store
+        const float one = 1.0f, one_third = 1.0/3.0;
+        float v0 = one/sqrtf( one + ( ux*ux + ( uy*uy + uz*uz ) ) );
+        ux *= c.cdt_dx; uy *= c.cdt_dy; uz *= c.cdt_dz;
+        ux *= v0; uy *= v0; uz *= v0;
+        v0 = dx + ux; const float v1 = dy + uy, v2 = dz + uz;  // streak midpoint
+        const float v3 = v0 + ux, v4 = v1 + uy, v5 = v2 + uz;  // new position
+        const float q = r1.w*c.qsp;
+        S.tile[2*loc+1] = make_float4( sux, suy, suz, r1.w );
+        if( v3<=one && v4<=one && v5<=one && -v3<=one && -v4<=one && -v5<=one ) {
+          S.tile[2*loc] = make_float4( v3, v4, v5, r0.w );
+          float j[12];
+          streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
+#         pragma unroll
+          for( int m=0; m<12; m++ ) run[m] += j[m];
+        } else {
+          cross = true;
+          cdx = dx; cdy = dy; cdz = dz; ci = ii; cux = ux; cuy = uy; cuz = uz; cq = q;
+        }
+      }
+      const unsigned m = __ballot_sync( 0xffffffffu, cross );
+      if( m ) {
+        if( cross ) {
+          const int e = qn + __popc( m & ( ( 1u<<lane )-1u ) );
+          S.q_idx[e] = (int)( t0 + loc );
+          S.q_dx[e] = cdx; S.q_dy[e] = cdy; S.q_dz[e] = cdz; S.q_i[e] = ci;
+          S.q_dispx[e] = cux; S.q_dispy[e] = cuy; S.q_dispz[e] = cuz; S.q_q[e] = cq;
+        }
+        qn += __popc( m );
+        __syncwarp();
+        if( qn>=32 ) {
+          qn -= 32;
+          drain_crossers( S, qn, 32, lane, p, t0, cnt, true, acc, pm, max_nm, counters, g );
+          __syncwarp();
         }
       }
     }
+
+    // write the tile back: generic-proxy writes -> async-proxy bulk store
+    asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
     __syncwarp();
-    // ---- particles that left their voxel: move_p, streak by streak ----
-    if( crosser ) {
-      int status;
-      do {
-        int vox;
-        status = move_p_streak( ms, q, g, j, vox );
-        float * a = acc + (size_t)vox*ACC_STRIDE;
-#       pragma unroll
-        for( int k=0; k<12; k++ ) atomicAdd( a+k, j[k] );
-      } while( status==1 );
-      float4 * pp = reinterpret_cast<float4 *>( p + idx );
-      pp[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
-      pp[1] = make_float4( ms.ux, ms.uy, ms.uz, w_keep );
-      if( status==2 ) {
-        const int slot = atomicAdd( counters+0, 1 );
-        if( slot<max_nm ) {
-          reinterpret_cast<float4 *>( pm )[slot] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( (int)idx ) );
-        } else atomicAdd( counters+1, 1 );
-      }
+    if( lane==0 ) {
+      const uint32_t bytes = (uint32_t)cnt*32u;
+      asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(tile_s), "r"(bytes) : "memory" );
+      asm volatile( "cp.async.bulk.commit_group;" ::: "memory" );
+      asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );   // complete (not just read): later drains write the same lines
     }
+    __syncwarp();
   }
-  if( comp<12 && cur>=0 ) atomicAdd( acc + (size_t)cur*ACC_STRIDE + comp, run );
+
+  if( qn>0 ) drain_crossers( S, 0, qn, lane, p, 0, 0, false, acc, pm, max_nm, counters, g );
+  if( cur>=0 ) commit_currents( acc, cur, run );
 }
 
 } // namespace vpb
@@ -151,8 +244,16 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   if( ms->np>0 ) {
     if( r.deposit_mode==VPB_DEPOSIT_PARITY ) advance_p_parity( ms, ma, mi, c );
     else {
-      const int nblock = div_up( ms->np, AP_STRIP*AP_WARPS );
-      k_advance_p<<< nblock, 32*AP_WARPS, 0, r.stream >>>( ms->d_p, ms->np, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
+      static int blocks_per_sm = 0;
+      if( !blocks_per_sm ) {
+        VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
+        VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, k_advance_p, 32*AP_WARPS, 0 ) );
+        if( blocks_per_sm<1 ) VPB_ERROR( "k_advance_p does not fit on an SM" );
+      }
+      const int ntile = div_up( ms->np, AP_TILE );
+      int nblock = r.sm_count*blocks_per_sm;
+      if( nblock>div_up( ntile, AP_WARPS ) ) nblock = div_up( ntile, AP_WARPS );
+      k_advance_p<<< nblock, 32*AP_WARPS, 0, r.stream >>>( ms->d_p, ms->np, ntile, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
                                                             ms->d_counters, ms->grid->dev, c );
       VPB_CHECK_LAUNCH(); r.launches++;
     }
