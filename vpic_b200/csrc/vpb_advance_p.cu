@@ -35,7 +35,7 @@ namespace vpb {
 constexpr int AP_K      = 8;            // consecutive particles per lane
 constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
 constexpr int AP_WARPS  = 4;            // warps per block
-constexpr int AP_MINBLK = 4;            // resident blocks per SM the registers are budgeted for
+constexpr int AP_MINBLK = 5;            // resident blocks per SM the registers are budgeted for
 constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 
 struct __align__(128) WarpTile {
@@ -63,17 +63,15 @@ __device__ __forceinline__ void commit_currents( float * __restrict__ acc, int v
 }
 
 // Run move_p (move_p.cc:216-353) on up to 32 queued particles, one per lane.
-// Entries of the tile that is still in shared memory are finished there;
-// entries of tiles already written back are finished in global memory.
-__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane,
-                                                vpb_particle_t * __restrict__ p, long long t0, int cnt, bool tile_live,
+// The queue is emptied before its tile is written back, so every entry is
+// finished in the shared-memory copy of the tile.
+__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane, long long t0,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
                                                 int max_nm, int * __restrict__ counters, const GridDev & g ) {
   if( lane>=n ) return;
   const int e = base + lane;
   const int idx = S.q_idx[e];
-  const bool in_tile = tile_live && idx>=t0 && idx<t0+cnt;
-  float4 * slot = in_tile ? &S.tile[ 2*(int)( idx-t0 ) ] : reinterpret_cast<float4 *>( p + idx );
+  float4 * slot = &S.tile[ 2*(int)( idx-t0 ) ];
   const float4 r1 = slot[1];
   MoveState ms;
   ms.dx = S.q_dx[e]; ms.dy = S.q_dy[e]; ms.dz = S.q_dz[e]; ms.i = S.q_i[e];
@@ -81,16 +79,14 @@ __device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, i
   ms.dispx = S.q_dispx[e]; ms.dispy = S.q_dispy[e]; ms.dispz = S.q_dispz[e];
   const float q = S.q_q[e];
   float j[12];
-  int status; bool reflected = false;
+  int status;
   do {
     int vox;
-    const float ux0 = ms.ux, uy0 = ms.uy, uz0 = ms.uz;
     status = move_p_streak( ms, q, g, j, vox );
-    reflected |= ( ms.ux!=ux0 ) | ( ms.uy!=uy0 ) | ( ms.uz!=uz0 );
     commit_currents( acc, vox, j );
   } while( status==1 );
   slot[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
-  if( reflected ) slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );
+  slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );       // reflections flip a momentum component
   if( status==2 ) {
     const int k = atomicAdd( counters+0, 1 );
     if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
@@ -119,7 +115,8 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
 
   uint32_t phase = 0;
   int qn = 0;                                  // queued crossers (warp uniform)
-  int cur = -1;                                // voxel whose coefficients / sums this lane holds
+  int cur = -1;                                // voxel whose current sums this lane holds in run[]
+  int fvox = -1;                               // voxel whose coefficients this lane holds in f
   float run[12];
 # pragma unroll
   for( int k=0; k<12; k++ ) run[k] = 0.f;
@@ -160,12 +157,22 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
         const float4 r0 = S.tile[2*loc], r1 = S.tile[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
         float ux = r1.x, uy = r1.y, uz = r1.z;
+        if( ii!=fvox ) { f = load_interp( ip, ii ); fvox = ii; }
         if( ii!=cur ) {
-          if( cur>=0 ) commit_currents( acc, cur, run );
-#         pragma unroll
-          for( int m=0; m<12; m++ ) run[m] = 0.f;
-          cur = ii;
-          f = load_interp( ip, ii );
+          // A particle that strayed into this run since the last sort_p (the
+          // lane's next particle is back in the run's voxel) deposits on its
+          // own below and leaves the running sums alone.
+          bool stray = false;
+          if( k+1<AP_K ) {
+            const int nloc = lane*AP_K + ( ( k + 1 + lane ) & ( AP_K-1 ) );
+            stray = nloc<cnt && __float_as_int( S.tile[2*nloc].w )==cur;
+          }
+          if( !stray ) {
+            if( cur>=0 ) commit_currents( acc, cur, run );
+#           pragma unroll
+            for( int m=0; m<12; m++ ) run[m] = 0.f;
+            cur = ii;
+          }
         }
         boris( f, c, dx, dy, dz, ux, uy, uz );
         const float sux = ux, suy = uy, suz = uz;            // momentum to store
@@ -181,8 +188,10 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
           S.tile[2*loc] = make_float4( v3, v4, v5, r0.w );
           float j[12];
           streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
-#         pragma unroll
-          for( int m=0; m<12; m++ ) run[m] += j[m];
+          if( ii==cur ) {
+#           pragma unroll
+            for( int m=0; m<12; m++ ) run[m] += j[m];
+          } else commit_currents( acc, ii, j );
         } else {
           cross = true;
           cdx = dx; cdy = dy; cdz = dz; ci = ii; cux = ux; cuy = uy; cuz = uz; cq = q;
@@ -200,12 +209,19 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
         __syncwarp();
         if( qn>=32 ) {
           qn -= 32;
-          drain_crossers( S, qn, 32, lane, p, t0, cnt, true, acc, pm, max_nm, counters, g );
+          drain_crossers( S, qn, 32, lane, t0, acc, pm, max_nm, counters, g );
           __syncwarp();
         }
       }
     }
 
+    // finish the remaining crossers of this tile while it is still on chip
+    while( qn>0 ) {
+      const int n = qn<32 ? qn : 32;
+      qn -= n;
+      drain_crossers( S, qn, n, lane, t0, acc, pm, max_nm, counters, g );
+      __syncwarp();
+    }
     // write the tile back: generic-proxy writes -> async-proxy bulk store
     asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
     __syncwarp();
@@ -213,12 +229,11 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
       const uint32_t bytes = (uint32_t)cnt*32u;
       asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(tile_s), "r"(bytes) : "memory" );
       asm volatile( "cp.async.bulk.commit_group;" ::: "memory" );
-      asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );   // complete (not just read): later drains write the same lines
+      asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer may be reused
     }
     __syncwarp();
   }
 
-  if( qn>0 ) drain_crossers( S, 0, qn, lane, p, 0, 0, false, acc, pm, max_nm, counters, g );
   if( cur>=0 ) commit_currents( acc, cur, run );
 }
 

@@ -22,19 +22,35 @@ InterpMirror * mirror( vpb_interpolator_array_t * ia ) {
   return m;
 }
 
+// host layout (80 B records) <-> device layout (96 B records)
+__global__ void k_interp_restride( float * __restrict__ dst, int dstride, const float * __restrict__ src, int sstride, int nv ) {
+  const long long t = (long long)blockIdx.x*blockDim.x + threadIdx.x;
+  const long long v = t/5; const int q = (int)( t - 5*v );
+  if( v>=nv ) return;
+  reinterpret_cast<float4 *>( dst + v*dstride )[q] = reinterpret_cast<const float4 *>( src + v*sstride )[q];
+}
+
 void to_device( InterpMirror * m ) {
   Runtime & r = rt();
   if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
   if( !m->host->i ) { if( m->dev_valid ) return; VPB_ERROR( "interpolator array has neither host nor device data" ); }
-  static_assert( sizeof(vpb_interpolator_t)==sizeof(float)*IP_STRIDE, "device interpolator layout == host layout" );
-  VPB_CUDA( cudaMemcpyAsync( m->d, m->host->i, sizeof(vpb_interpolator_t)*(size_t)m->grid->dev.nv, cudaMemcpyHostToDevice, r.stream ) );
+  static_assert( sizeof(vpb_interpolator_t)==sizeof(float)*IP_HOST, "host interpolator layout" );
+  const int nv = m->grid->dev.nv;
+  if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(float)*IP_HOST*(size_t)nv ) );
+  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv, cudaMemcpyHostToDevice, r.stream ) );
+  k_interp_restride<<< div_up( 5LL*nv, 256 ), 256, 0, r.stream >>>( m->d, IP_STRIDE, m->d_stage, IP_HOST, nv );
+  VPB_CHECK_LAUNCH(); r.launches++;
   m->dev_valid = true;
 }
 
 void to_host( InterpMirror * m ) {
   Runtime & r = rt();
   if( !m->dev_valid || m->host_valid || !m->host->i ) return;
-  VPB_CUDA( cudaMemcpyAsync( m->host->i, m->d, sizeof(vpb_interpolator_t)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  const int nv = m->grid->dev.nv;
+  if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(float)*IP_HOST*(size_t)nv ) );
+  k_interp_restride<<< div_up( 5LL*nv, 256 ), 256, 0, r.stream >>>( m->d_stage, IP_HOST, m->d, IP_STRIDE, nv );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  VPB_CUDA( cudaMemcpyAsync( m->host->i, m->d_stage, sizeof(vpb_interpolator_t)*(size_t)nv, cudaMemcpyDeviceToHost, r.stream ) );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
 }
@@ -218,7 +234,7 @@ void vpic_b200_forget( void * obj ) {
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( r.species.count( obj ) ) { auto m = r.species[obj]; cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
   if( r.fields.count( obj )  ) { auto m = r.fields[obj]; cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
-  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; cudaFree( m->d ); delete m; r.interps.erase( obj ); return; }
+  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
   if( r.accs.count( obj )    ) { auto m = r.accs[obj]; cudaFree( m->d ); delete m; r.accs.erase( obj ); return; }
   if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
 }

@@ -39,9 +39,13 @@ void warning( const char * file, int line, const char * fmt, ... );
 enum FieldComp { F_EX=0, F_EY, F_EZ, F_DIVE, F_CBX, F_CBY, F_CBZ, F_DIVB,
                  F_TCAX, F_TCAY, F_TCAZ, F_RHOB, F_JFX, F_JFY, F_JFZ, F_RHOF, F_NCOMP };
 
-// Interpolator: the 18 coefficients of interpolator_t padded to IP_STRIDE
-// floats per voxel; first 18 floats in the reference's order.
-constexpr int IP_STRIDE = 20;   // floats per voxel (80 B, reference layout)
+// Interpolator: the 18 coefficients of interpolator_t, in the reference's
+// order, padded to IP_STRIDE floats per voxel.  96 B = three 32 B sectors, so
+// one voxel's record is fetched with three 256-bit loads (LDG.256, new on
+// sm_100) and never straddles a sector; the host layout is 80 B
+// (interpolator_t) and is converted at the coherence points only.
+constexpr int IP_STRIDE = 24;   // floats per voxel on the device
+constexpr int IP_HOST   = 20;   // floats per voxel in the host struct (80 B)
 constexpr int ACC_STRIDE = 12;  // floats per voxel (48 B, reference layout)
 
 // Particle boundary action per box face, derived from g->neighbor.
@@ -87,6 +91,7 @@ struct InterpMirror {
   vpb_interpolator_array_t * host = nullptr;
   GridMirror * grid = nullptr;
   float * d = nullptr;             // nv * IP_STRIDE floats
+  float * d_stage = nullptr;       // nv * IP_HOST floats, host layout, for host<->device conversion
   bool dev_valid = false, host_valid = true;
 };
 

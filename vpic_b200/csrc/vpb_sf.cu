@@ -9,7 +9,7 @@
 
 namespace vpb {
 
-// Algorithmic traffic: 24 B read (6 planes) + 72 B written per voxel.
+// Algorithmic traffic: 24 B read (6 planes) + 72 B written per voxel (96 B with the device padding).
 // One thread per interior voxel; x is the fastest index so the six plane reads
 // are unit-stride and the +y/+z neighbours come out of L1/L2.
 __global__ void __launch_bounds__(256)
@@ -44,7 +44,7 @@ k_load_interpolator( float * __restrict__ ip, const float * __restrict__ f, Grid
     w0 = bz[v]; w1 = bz[v+g.sz]; o4.x = half*( w1 + w0 ); o4.y = half*( w1 - w0 );
     o4.z = 0.f; o4.w = 0.f;
     float4 * dst = reinterpret_cast<float4 *>( ip + (size_t)v*IP_STRIDE );
-    dst[0] = o0; dst[1] = o1; dst[2] = o2; dst[3] = o3; dst[4] = o4;
+    dst[0] = o0; dst[1] = o1; dst[2] = o2; dst[3] = o3; dst[4] = o4; dst[5] = make_float4( 0.f, 0.f, 0.f, 0.f );
   }
 }
 
