@@ -74,6 +74,15 @@ enum { VPB_DEPOSIT_FAST = 0,       /* warp-reduced + atomics, FMA allowed       
        VPB_DEPOSIT_PARITY = 1      /* reference summation order, bit-exact currents  */ };
 
 int  vpic_b200_init( int device, int world_rank, int world_size ); /* returns SM count */
+/* rank / size only (host state for the grid partitioners; no CUDA needed) */
+void vpic_b200_set_world( int world_rank, int world_size );
+/* Multi-GPU transport (replaces src/util/mp for device buffers): one NCCL
+   communicator, one process per GPU.  Rank 0 obtains the 128-byte id, the host
+   program distributes it (MPI_Bcast in a reference build, torch.distributed in
+   the tests), every rank calls comm_init after vpic_b200_init. */
+int  vpic_b200_comm_unique_id( void * out, int nbytes );           /* returns bytes written */
+void vpic_b200_comm_init( const void * id_bytes, int nbytes );
+int  vpic_b200_comm_ready( void );
 void vpic_b200_finalize( void );
 void vpic_b200_set_coherence( int mode );
 void vpic_b200_set_deposit_mode( int mode );

@@ -128,3 +128,70 @@ def ref_facts(L):
     L.refshim_fact_name.restype = C.c_char_p
     L.refshim_fact_value.restype = C.c_long
     return {L.refshim_fact_name(k).decode(): L.refshim_fact_value(k) for k in range(L.refshim_n_facts())}
+
+
+# ---- multi-rank transport for the oracle (tests only) -------------------------
+
+_EXCH_PROTO = C.CFUNCTYPE(None, _P, C.c_int, _P, _P, _P, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int64))
+_exch_keepalive = []
+
+
+def install_gloo_exchange(sim):
+    """Route the oracle's face / particle messages of `sim`'s grid through
+    torch.distributed (gloo, CPU tensors).  A message sent out of the -X face
+    carries tag 2*X and arrives on the receiver's +X side, and vice versa, like
+    the reference's port numbering (src/grid/grid_comm.c:16-60)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    L = _load(ORACLE_LIB)
+    g = sim.grid_struct(sim.g)
+    bnd = lambda i, j, k: 13 + i + 3 * j + 9 * k
+    lo_b = [bnd(-1, 0, 0), bnd(0, -1, 0), bnd(0, 0, -1)]
+    hi_b = [bnd(1, 0, 0), bnd(0, 1, 0), bnd(0, 0, 1)]
+    rank_lo = [g.bc[b] for b in lo_b]
+    rank_hi = [g.bc[b] for b in hi_b]
+
+    def view(ptr, n):
+        return torch.from_numpy(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n,)))
+
+    me = dist.get_rank()
+
+    def exchange(user, X, slo, shi, rlo, rhi, sb, rb):
+        if rank_lo[X] == me and rank_hi[X] == me:       # periodic onto ourselves along this axis
+            if rhi and slo:
+                C.memmove(rhi, slo, sb[0])
+            if rlo and shi:
+                C.memmove(rlo, shi, sb[1])
+            return
+        reqs = []
+        if slo and sb[0] > 0:
+            reqs.append(dist.isend(view(slo, sb[0]).clone(), rank_lo[X], tag=2 * X))
+        if shi and sb[1] > 0:
+            reqs.append(dist.isend(view(shi, sb[1]).clone(), rank_hi[X], tag=2 * X + 1))
+        bufs = []
+        if rhi and rb[1] > 0:
+            t = torch.empty(rb[1], dtype=torch.uint8); bufs.append((rhi, t))
+            reqs.append(dist.irecv(t, rank_hi[X], tag=2 * X))
+        if rlo and rb[0] > 0:
+            t = torch.empty(rb[0], dtype=torch.uint8); bufs.append((rlo, t))
+            reqs.append(dist.irecv(t, rank_lo[X], tag=2 * X + 1))
+        for r in reqs:
+            r.wait()
+        for ptr, t in bufs:
+            C.memmove(ptr, t.numpy().ctypes.data, t.numel())
+
+    cb = _EXCH_PROTO(exchange)
+    _exch_keepalive.append(cb)
+    L.orc_set_exchange.argtypes = [_EXCH_PROTO, _P]
+    L.orc_set_exchange.restype = None
+    L.orc_set_exchange(cb, None)
+
+
+def set_world(rank, size):
+    """rank / size for the oracle and for the product's host-side partitioners."""
+    from vpic_b200.lib import load_b200
+    L = _load(ORACLE_LIB)
+    L.orc_set_world.argtypes = [C.c_int, C.c_int]
+    L.orc_set_world(rank, size)
+    load_b200().vpic_b200_set_world(rank, size)

@@ -1,0 +1,36 @@
+"""N>1 paths.  CPU: the 2-rank oracle over gloo against the 1-rank oracle (pins
+the decomposition / migration / ghost-exchange host logic).  GPU: the CUDA
+library on 2 GPUs over NCCL against the 2-rank oracle (needs 2 devices)."""
+import os
+import socket
+import subprocess
+import sys
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def launch(mode, nproc=2, timeout=900):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(free_port()),
+           os.path.join(ROOT, "tests", "multi_rank_check.py"), "--mode", mode]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "PASS" in r.stdout
+
+
+def test_two_rank_oracle_matches_one_rank_oracle_gloo():
+    launch("oracle")
+
+
+@pytest.mark.gpu
+def test_two_gpus_match_two_rank_oracle_nccl():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch("gpu")

@@ -74,7 +74,7 @@ def test_particle_kernels(case):
         assert so.be.energy_p(a, so.ia) == sr.be.energy_p(b, sr.ia)
 
 
-@pytest.mark.parametrize("case", CASES[:4])
+@pytest.mark.parametrize("case", CASES)
 def test_whole_steps(case):
     so, sr = pair(sort_interval=3, **case)
     for s in (so, sr):

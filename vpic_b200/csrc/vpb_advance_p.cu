@@ -51,17 +51,6 @@ struct __align__(128) WarpTile {
 
 __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_t)__cvta_generic_to_shared( p ); }
 
-__device__ __forceinline__ void red_add_v4( float * addr, float a, float b, float c, float d ) {
-  asm volatile( "red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory" );
-}
-
-__device__ __forceinline__ void commit_currents( float * __restrict__ acc, int voxel, const float * j ) {
-  float * a = acc + (size_t)voxel*ACC_STRIDE;
-  red_add_v4( a,   j[0], j[1], j[2],  j[3]  );
-  red_add_v4( a+4, j[4], j[5], j[6],  j[7]  );
-  red_add_v4( a+8, j[8], j[9], j[10], j[11] );
-}
-
 // Run move_p (move_p.cc:216-353) on up to 32 queued particles, one per lane.
 // The queue is emptied before its tile is written back, so every entry is
 // finished in the shared-memory copy of the tile.
@@ -280,6 +269,7 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   if( cnt[1] ) VPB_WARNING( "Species \"%s\" ran out of storage for %i movers", sp->name, cnt[1] );   // advance_p_pipeline.cc:301-305
   ms->nm = cnt[0]<(int)ms->cap_pm ? cnt[0] : (int)ms->cap_pm;
   if( ms->nm>1 ) sort_movers_by_index( ms );
+  ms->movers_sorted = true;
   mark_dev_written( ms ); mark_dev_written( ma );
   movers_to_host( ms );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ms ); to_host( ma ); }

@@ -1,18 +1,383 @@
 // vpb_boundary.cu -- boundary_p: particles that left the rank's domain.
-// Reference: src/boundary/boundary_p.cc:36-518.
-#include "vpb_runtime.h"
+// Reference: src/boundary/boundary_p.cc:36-518 and accumulate_rhob,
+// src/species_advance/standard/rho_p.cc:125-171.
+//
+// The reference walks each species' movers in REVERSE order, turns every one
+// into "absorbed" (charge to rhob) or "sent" (a 48 B injector appended to the
+// face's message), back-fills the hole with the last particle, then appends
+// the injectors it received (faces 0..5, each message in reverse) and finishes
+// their displacement with move_p.  That sequential recipe fixes the order of
+// the particle array afterwards, which sort_p's stable output depends on, so
+// the device version reproduces it exactly, in parallel:
+//   * the k-th mover in processing order gets the k-th slot of its face's
+//     message (block-wide ranking per chunk of 1024 movers),
+//   * all movers leave, so the holes below the new end of the array are filled,
+//     largest hole first, by the surviving particles of the tail, last first --
+//     which is a closed-form pairing found with two binary searches per tail
+//     particle (k_bnd_backfill),
+//   * received injectors are ranked per species the same way and moved with
+//     every lane busy.
+// Messages travel as device buffers over NCCL (vpb_comm.cu): counts, then
+// payloads, like boundary_p.cc:292-316.
+#include "vpb_push.cuh"
+#include <vector>
+
+namespace vpb {
+
+constexpr int BND_T = 1024;           // threads of the single ranking block
+constexpr int BND_MAX_SP = 16;        // species ids the inject kernel can address
+
+struct BndFaces {
+  int kind[6];                        // ParticleFaceKind
+  int nb_n[6];                        // neighbour extent along the face axis
+  vpb_particle_injector_t * send[6];  // device message bodies
+  int * face_count;                   // [6] injectors packed so far (all species)
+};
+
+// Ranks of the threads of a block among those holding the same key (0..NKEY-1,
+// or <0 for "none"), in thread order.  Returns the rank and leaves the
+// per-key totals of this chunk in s_tot.
+template<int NKEY>
+__device__ __forceinline__ int block_rank_by_key( int key, int (*s_w)[NKEY], int * s_tot ) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for( int t=threadIdx.x; t<(BND_T/32)*NKEY; t+=BND_T ) (&s_w[0][0])[t] = 0;
+  __syncthreads();
+  const unsigned m = __match_any_sync( 0xffffffffu, key );
+  const int r_in_warp = __popc( m & ( ( 1u<<lane )-1u ) );
+  if( key>=0 && r_in_warp==0 ) s_w[w][key] = __popc( m );
+  __syncthreads();
+  int before = 0;
+  if( key>=0 ) for( int k=0; k<w; k++ ) before += s_w[k][key];
+  if( threadIdx.x<NKEY ) { int t = 0; for( int k=0; k<BND_T/32; k++ ) t += s_w[k][threadIdx.x]; s_tot[threadIdx.x] = t; }
+  __syncthreads();
+  return before + r_in_warp;
+}
+
+// accumulate_rhob, rho_p.cc:125-171 (separate multiply and add, as compiled).
+__device__ __forceinline__ void accumulate_rhob_dev( float * __restrict__ rhob, const GridDev & g,
+                                                     float dx, float dy, float dz, int v, float w, float q_r8V ) {
+  float w0 = dx, w1 = dy, w2, w3, w4, w5, w6, w7 = q_r8V*w;
+  w6 = w7 - w0*w7; w7 = w7 + w0*w7;
+  w4 = w6 - w1*w6; w5 = w7 - w1*w7;
+  w6 = w6 + w1*w6; w7 = w7 + w1*w7;
+  w0 = w4 - dz*w4; w1 = w5 - dz*w5; w2 = w6 - dz*w6; w3 = w7 - dz*w7;
+  w4 = w4 + dz*w4; w5 = w5 + dz*w5; w6 = w6 + dz*w6; w7 = w7 + dz*w7;
+  int x = v; const int z = x/g.sz;
+  if( z==1    ) { w0 += w0; w1 += w1; w2 += w2; w3 += w3; }
+  if( z==g.nz ) { w4 += w4; w5 += w5; w6 += w6; w7 += w7; }
+  x -= g.sz*z; const int y = x/g.sy;
+  if( y==1    ) { w0 += w0; w1 += w1; w4 += w4; w5 += w5; }
+  if( y==g.ny ) { w2 += w2; w3 += w3; w6 += w6; w7 += w7; }
+  x -= g.sy*y;
+  if( x==1    ) { w0 += w0; w2 += w2; w4 += w4; w6 += w6; }
+  if( x==g.nx ) { w1 += w1; w3 += w3; w5 += w5; w7 += w7; }
+  atomicAdd( rhob + v,           w0 ); atomicAdd( rhob + v+1,           w1 );
+  atomicAdd( rhob + v+g.sy,      w2 ); atomicAdd( rhob + v+g.sy+1,      w3 );
+  atomicAdd( rhob + v+g.sz,      w4 ); atomicAdd( rhob + v+g.sz+1,      w5 );
+  atomicAdd( rhob + v+g.sz+g.sy, w6 ); atomicAdd( rhob + v+g.sz+g.sy+1, w7 );
+}
+
+// One species: absorb or pack every mover, in the reference's processing
+// order (last mover first).  Single block; chunks of BND_T movers.
+__global__ void __launch_bounds__(BND_T)
+k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int nm,
+                int sp_id, float q_r8V, float * __restrict__ rhob, GridDev g, BndFaces a, int * __restrict__ n_unknown ) {
+  __shared__ int s_w[BND_T/32][6];
+  __shared__ int s_tot[6], s_base[6];
+  if( threadIdx.x<6 ) s_base[threadIdx.x] = a.face_count[threadIdx.x];
+  __syncthreads();
+  for( int c0=0; c0<nm; c0+=BND_T ) {
+    const int r = c0 + threadIdx.x;              // position in processing order
+    int key = -1, face = 0, voxel = 0, i = 0;
+    float4 r0 = {}, r1 = {}, d = {};
+    if( r<nm ) {
+      d = reinterpret_cast<const float4 *>( pm )[ nm-1-r ];
+      i = __float_as_int( d.w );
+      r0 = reinterpret_cast<const float4 *>( p + i )[0];
+      r1 = reinterpret_cast<const float4 *>( p + i )[1];
+      const int vi = __float_as_int( r0.w );
+      face = vi & 7; voxel = vi >> 3;
+      const int kind = face<6 ? a.kind[face] : PK_CUSTOM;
+      if( kind==PK_ABSORB ) accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V );
+      else if( kind==PK_REMOTE ) key = face;
+      else atomicAdd( n_unknown, 1 );
+    }
+    const int rank = block_rank_by_key<6>( key, s_w, s_tot );
+    if( key>=0 ) {
+      // the same voxel seen from the neighbour brick (boundary_p.cc:215-230)
+      const int axis = face>=3 ? face-3 : face;
+      int c[3] = { voxel % g.sy, ( voxel / g.sy ) % ( g.ny+2 ), voxel / g.sz };
+      int rn[3] = { g.nx, g.ny, g.nz };
+      rn[axis] = a.nb_n[face];
+      c[axis] = face<3 ? rn[axis] : 1;
+      const int nv_i = c[0] + ( rn[0]+2 )*( c[1] + ( rn[1]+2 )*c[2] );
+      float pos[3] = { r0.x, r0.y, r0.z };
+      pos[axis] = face<3 ? 1.f : -1.f;
+      float4 * out = reinterpret_cast<float4 *>( a.send[face] + s_base[face] + rank );
+      out[0] = make_float4( pos[0], pos[1], pos[2], __int_as_float( nv_i ) );
+      out[1] = r1;
+      out[2] = make_float4( d.x, d.y, d.z, __int_as_float( sp_id ) );
+    }
+    __syncthreads();
+    if( threadIdx.x<6 ) s_base[threadIdx.x] += s_tot[threadIdx.x];
+    __syncthreads();
+  }
+  if( threadIdx.x<6 ) a.face_count[threadIdx.x] = s_base[threadIdx.x];
+}
+
+// All nm movers (ascending particle index in pm) leave.  The reference's
+// "p[i] = p[--np]" walked over the movers in reverse is equivalent to: the
+// k-th largest hole below new_np receives the k-th largest surviving particle
+// of the tail [new_np, np).
+__device__ __forceinline__ int lower_bound_idx( const vpb_particle_mover_t * pm, int n, int key ) {   // first m with pm[m].i >= key
+  int lo = 0, hi = n;
+  while( lo<hi ) { const int mid = ( lo+hi )>>1; if( pm[mid].i<key ) lo = mid+1; else hi = mid; }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256)
+k_bnd_backfill( vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int nm, int np ) {
+  const int new_np = np - nm;
+  const int j = new_np + blockIdx.x*blockDim.x + threadIdx.x;
+  if( j>=np ) return;
+  const int lb = lower_bound_idx( pm, nm, j );
+  if( lb<nm && pm[lb].i==j ) return;                 // j itself leaves
+  const int n_below = lower_bound_idx( pm, nm, new_np );   // holes below the new end
+  const int removed_gt = nm - lb;                    // leaving particles above j
+  const int k = ( np-1-j ) - removed_gt;             // j is the k-th largest survivor of the tail
+  const int hole = pm[ n_below-1-k ].i;
+  const float4 a = reinterpret_cast<const float4 *>( p + j )[0], b = reinterpret_cast<const float4 *>( p + j )[1];
+  reinterpret_cast<float4 *>( p + hole )[0] = a;
+  reinterpret_cast<float4 *>( p + hole )[1] = b;
+}
+
+struct BndInject {
+  const vpb_particle_injector_t * recv[6];
+  int start[7];                        // prefix sums of the received counts, faces 0..5
+  vpb_particle_t * p[BND_MAX_SP];
+  vpb_particle_mover_t * pm[BND_MAX_SP];
+  int np[BND_MAX_SP], nm[BND_MAX_SP], max_nm[BND_MAX_SP];
+  float q[BND_MAX_SP];
+  int * counters;                      // [0..MAX_SP) injected, [MAX_SP..2 MAX_SP) movers appended, [2 MAX_SP..) movers dropped
+};
+
+// Append the received particles (faces 0..5, each message last-first) to their
+// species and finish their move (boundary_p.cc:440-494).
+__global__ void __launch_bounds__(BND_T)
+k_bnd_inject( BndInject a, float * __restrict__ acc, GridDev g ) {
+  __shared__ int s_w[BND_T/32][BND_MAX_SP];
+  __shared__ int s_tot[BND_MAX_SP], s_base[BND_MAX_SP];
+  if( threadIdx.x<BND_MAX_SP ) s_base[threadIdx.x] = 0;
+  __syncthreads();
+  const int total = a.start[6];
+  for( int c0=0; c0<total; c0+=BND_T ) {
+    const int r = c0 + threadIdx.x;
+    int key = -1; float4 i0 = {}, i1 = {}, i2 = {};
+    if( r<total ) {
+      int face = 0;
+      while( r>=a.start[face+1] ) face++;
+      const int n = a.start[face+1] - a.start[face];
+      const float4 * src = reinterpret_cast<const float4 *>( a.recv[face] + ( n-1-( r-a.start[face] ) ) );
+      i0 = src[0]; i1 = src[1]; i2 = src[2];
+      key = __float_as_int( i2.w );
+      if( key<0 || key>=BND_MAX_SP || !a.p[key] ) key = -1;      // unknown species: dropped (counted below)
+    }
+    const int rank = block_rank_by_key<BND_MAX_SP>( key, s_w, s_tot );
+    if( key>=0 ) {
+      const int idx = a.np[key] + s_base[key] + rank;
+      MoveState ms;
+      ms.dx = i0.x; ms.dy = i0.y; ms.dz = i0.z; ms.i = __float_as_int( i0.w );
+      ms.ux = i1.x; ms.uy = i1.y; ms.uz = i1.z;
+      ms.dispx = i2.x; ms.dispy = i2.y; ms.dispz = i2.z;
+      const float q = a.q[key]*i1.w;
+      float j[12]; int status;
+      do {
+        int vox;
+        status = move_p_streak( ms, q, g, j, vox );
+        commit_currents( acc, vox, j );
+      } while( status==1 );
+      float4 * dst = reinterpret_cast<float4 *>( a.p[key] + idx );
+      dst[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
+      dst[1] = make_float4( ms.ux, ms.uy, ms.uz, i1.w );
+      if( status==2 ) {
+        const int k = a.nm[key] + atomicAdd( a.counters + BND_MAX_SP + key, 1 );
+        if( k<a.max_nm[key] ) reinterpret_cast<float4 *>( a.pm[key] )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
+        else atomicAdd( a.counters + 2*BND_MAX_SP + key, 1 );
+      }
+    } else if( r<total ) atomicAdd( a.counters + 3*BND_MAX_SP, 1 );
+    __syncthreads();
+    if( threadIdx.x<BND_MAX_SP ) s_base[threadIdx.x] += s_tot[threadIdx.x];
+    __syncthreads();
+  }
+  if( threadIdx.x<BND_MAX_SP ) a.counters[threadIdx.x] = s_base[threadIdx.x];
+}
+
+} // namespace vpb
 
 using namespace vpb;
 
+namespace {
+
+struct BndBuffers {
+  vpb_particle_injector_t * send[6] = {}, * recv[6] = {};
+  size_t send_cap[6] = {}, recv_cap[6] = {};
+  int * d_int = nullptr;     // [0..6) face_count  [8..14) recv counts  [16] n_unknown  [32..32+4*MAX_SP] inject counters
+} B;
+
+void grow( vpb_particle_injector_t ** buf, size_t * cap, size_t want ) {
+  if( want<=*cap ) return;
+  VPB_CUDA( cudaStreamSynchronize( rt().stream ) );
+  if( *buf ) VPB_CUDA( cudaFree( *buf ) );
+  *cap = want + want/4 + 256;
+  VPB_CUDA( cudaMalloc( buf, sizeof(vpb_particle_injector_t)*( *cap ) ) );
+}
+
+// Grow a species' device particle storage (the reference reallocates sp->p the
+// same way, boundary_p.cc:346-361).  Host arrays, when present, belong to the
+// host program and are not reallocated from here.
+void grow_particles( SpeciesMirror * m, size_t want ) {
+  if( want<=m->cap_p ) return;
+  vpb_species_t * sp = m->host;
+  if( sp->p ) VPB_ERROR( "species \"%s\": %zu particles after migration exceed max_np=%d; raise max_np "
+                         "(host-resident particle arrays are not resized by the device library)", sp->name, want, sp->max_np );
+  Runtime & r = rt();
+  size_t n = want + (size_t)( 0.3125*(double)want );
+  if( n>(size_t)INT32_MAX ) n = (size_t)INT32_MAX;
+  if( n<want ) VPB_ERROR( "species \"%s\": particle count exceeds 32-bit storage", sp->name );
+  VPB_WARNING( "Resizing local %s particle storage from %i to %zu", sp->name, sp->max_np, n );
+  vpb_particle_t * np_;
+  VPB_CUDA( cudaMalloc( &np_, sizeof(vpb_particle_t)*n ) );
+  if( m->np>0 ) VPB_CUDA( cudaMemcpyAsync( np_, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyDeviceToDevice, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  VPB_CUDA( cudaFree( m->d_p ) );
+  m->d_p = np_; m->cap_p = n; sp->max_np = (int)n;
+}
+
+} // namespace
+
+namespace vpb {
+void release_boundary_buffers() {
+  for( int f=0; f<6; f++ ) { cudaFree( B.send[f] ); cudaFree( B.recv[f] ); B.send[f] = B.recv[f] = nullptr; B.send_cap[f] = B.recv_cap[f] = 0; }
+  cudaFree( B.d_int ); B.d_int = nullptr;
+}
+}
+
 extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa ) {
-  (void)pbc_list;
-  if( !sp_list || !fa || !aa ) VPB_ERROR( "Bad args" );
-  // On a single rank whose faces are periodic-to-self or reflecting, move_p
-  // never hands a particle over (boundary_p.cc:111-112), so there is nothing
-  // to do unless some species has movers.
+  if( !sp_list ) return;                                        // boundary_p.cc:77
+  if( !fa || !aa || sp_list->g!=aa->g || fa->g!=aa->g ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  std::vector<SpeciesMirror *> sps;
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
     SpeciesMirror * m = mirror( sp );
-    if( m->nm>0 ) VPB_ERROR( "species \"%s\" has %d particles on domain boundaries; device boundary_p "
-                             "(absorb / remote migration) is not available in this build yet", sp->name, m->nm );
+    to_device( m );
+    sps.push_back( m );
+    if( sp->id<0 || sp->id>=BND_MAX_SP ) VPB_ERROR( "species id %d is outside the device boundary handler's range", sp->id );
   }
+  GridMirror * gm = sps[0]->grid;
+  const GridDev & g = gm->dev;
+  bool any_remote = false;
+  for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) any_remote = true;
+  long long nm_tot = 0;
+  for( SpeciesMirror * m : sps ) nm_tot += m->nm;
+  if( !any_remote && nm_tot==0 ) return;                        // nothing left the domain and nobody to talk to
+  if( nm_tot>0 && pbc_list ) {
+    for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_CUSTOM )
+      VPB_ERROR( "custom particle boundary handlers (host callbacks) are not available on the device yet" );
+  }
+  FieldMirror * mf = mirror( fa );
+  AccMirror   * ma = mirror( aa );
+  to_device( mf ); to_device( ma );
+  if( !B.d_int ) VPB_CUDA( cudaMalloc( &B.d_int, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ) ) );
+  VPB_CUDA( cudaMemsetAsync( B.d_int, 0, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ), r.stream ) );
+
+  // ---- load the send buffers, absorb, back-fill (boundary_p.cc:130-283) ----
+  BndFaces bf;
+  for( int f=0; f<6; f++ ) {
+    bf.kind[f] = gm->pkind[f]; bf.nb_n[f] = gm->nb_n[f];
+    if( gm->pkind[f]==PK_REMOTE ) grow( &B.send[f], &B.send_cap[f], (size_t)nm_tot );
+    bf.send[f] = B.send[f];
+  }
+  bf.face_count = B.d_int;
+  bool touched_rhob = false;
+  for( SpeciesMirror * m : sps ) {
+    if( m->nm<=0 ) continue;
+    if( !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
+    const vpb_species_t * sp = m->host;
+    const float q_r8V = sp->q*sp->g->r8V;
+    k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16 );
+    k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
+    VPB_CHECK_LAUNCH(); r.launches += 2;
+    for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_ABSORB ) touched_rhob = true;
+    m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
+    mark_dev_written( m );
+  }
+  int h_int[32];
+  VPB_CUDA( cudaMemcpyAsync( h_int, B.d_int, sizeof(int)*32, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  if( h_int[16] ) VPB_WARNING( "Unknown boundary interaction ... dropping %d particles", h_int[16] );   // boundary_p.cc:259-260
+  int n_send[6], n_recv[6] = { 0, 0, 0, 0, 0, 0 };
+  for( int f=0; f<6; f++ ) n_send[f] = h_int[f];
+
+  // ---- exchange counts, then injectors (boundary_p.cc:285-316) ----
+  if( any_remote ) {
+    for( int X=0; X<3; X++ ) {
+      const int lo = X, hi = X+3;
+      const int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
+      if( rank_lo<0 && rank_hi<0 ) continue;
+      comm_sendrecv( rank_lo, rank_hi, B.d_int+lo, 4, B.d_int+hi, 4, B.d_int+8+lo, 4, B.d_int+8+hi, 4 );
+    }
+    VPB_CUDA( cudaMemcpyAsync( n_recv, B.d_int+8, sizeof(int)*6, cudaMemcpyDeviceToHost, r.stream ) );
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) grow( &B.recv[f], &B.recv_cap[f], (size_t)n_recv[f] ); else n_recv[f] = 0;
+    const size_t S = sizeof(vpb_particle_injector_t);
+    for( int X=0; X<3; X++ ) {
+      const int lo = X, hi = X+3;
+      const int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
+      if( rank_lo<0 && rank_hi<0 ) continue;
+      if( n_send[lo]+n_send[hi]+n_recv[lo]+n_recv[hi]==0 ) continue;
+      comm_sendrecv( rank_lo, rank_hi, B.send[lo], S*(size_t)n_send[lo], B.send[hi], S*(size_t)n_send[hi],
+                     B.recv[lo], S*(size_t)n_recv[lo], B.recv[hi], S*(size_t)n_recv[hi] );
+    }
+  }
+
+  // ---- inject (boundary_p.cc:318-494) ----
+  int max_inj = 0;
+  for( int f=0; f<6; f++ ) max_inj += n_recv[f];
+  if( max_inj>0 ) {
+    BndInject bi = {};
+    bi.start[0] = 0;
+    for( int f=0; f<6; f++ ) { bi.recv[f] = B.recv[f]; bi.start[f+1] = bi.start[f] + n_recv[f]; }
+    for( SpeciesMirror * m : sps ) {
+      grow_particles( m, (size_t)m->np + (size_t)max_inj );
+      const int id = m->host->id;
+      bi.p[id] = m->d_p; bi.pm[id] = m->d_pm; bi.np[id] = m->np; bi.nm[id] = m->nm; bi.max_nm[id] = (int)m->cap_pm;
+      bi.q[id] = m->host->q;
+    }
+    bi.counters = B.d_int + 32;
+    k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
+    VPB_CHECK_LAUNCH(); r.launches++;
+    int h_cnt[4*BND_MAX_SP+1];
+    VPB_CUDA( cudaMemcpyAsync( h_cnt, B.d_int+32, sizeof(h_cnt), cudaMemcpyDeviceToHost, r.stream ) );
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( h_cnt[3*BND_MAX_SP] ) VPB_WARNING( "Dropped %d received particles of unknown species", h_cnt[3*BND_MAX_SP] );
+    for( SpeciesMirror * m : sps ) {
+      const int id = m->host->id;
+      m->np += h_cnt[id];
+      const int app = h_cnt[BND_MAX_SP+id], drop = h_cnt[2*BND_MAX_SP+id];
+      if( drop ) VPB_WARNING( "%i particles were not completed moved to their final location this timestep for species \"%s\"", drop, m->host->name );
+      m->nm += app - drop;
+      if( app-drop>0 ) m->movers_sorted = false;
+      if( h_cnt[id] ) { m->partition_dev_valid = false; mark_dev_written( m ); }
+    }
+    mark_dev_written( ma );
+  }
+  if( touched_rhob ) mark_dev_written( mf );
+
+  for( SpeciesMirror * m : sps ) {
+    m->host->np = m->np;
+    if( m->nm>1 && !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
+    movers_to_host( m );
+    if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
+  }
+  if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ma ); to_host( mf ); }
 }

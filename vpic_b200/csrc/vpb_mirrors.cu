@@ -138,6 +138,16 @@ void to_device( SpeciesMirror * m ) {
   m->np = m->host->np; m->nm = m->host->nm;
   if( m->np>0 )
     VPB_CUDA( cudaMemcpyAsync( m->d_p, m->host->p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyHostToDevice, r.stream ) );
+  // pending movers travel with the particles (the host may have added some:
+  // inject_particle, emitters; src/vpic/misc.cc:86-99)
+  if( m->nm>(int)m->cap_pm ) VPB_ERROR( "species \"%s\": nm=%d exceeds max_nm=%zu", m->host->name, m->nm, m->cap_pm );
+  if( m->nm>0 && m->host->pm ) {
+    VPB_CUDA( cudaMemcpyAsync( m->d_pm, m->host->pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, cudaMemcpyHostToDevice, r.stream ) );
+    m->movers_sorted = false;
+    for( int k=1; k<m->nm; k++ ) if( m->host->pm[k].i<=m->host->pm[k-1].i ) goto unsorted;
+    m->movers_sorted = true;
+    unsorted:;
+  }
   m->dev_valid = true; m->partition_dev_valid = false;
 }
 
@@ -170,6 +180,13 @@ using namespace vpb;
 // ---- control surface (vpic_b200.h part 2) ----------------------------------
 
 extern "C" {
+
+// world_rank / world_size as the reference's src/util/mp reports them; pure host
+// state (the grid partitioners use it), no CUDA needed.
+void vpic_b200_set_world( int world_rank, int world_size ) {
+  g_world_size = world_size<1 ? 1 : world_size;
+  g_world_rank = world_rank<0 ? 0 : world_rank;
+}
 
 int vpic_b200_init( int device, int world_rank, int world_size ) {
   Runtime & r = rt();
@@ -258,6 +275,7 @@ void vpic_b200_finalize( void ) {
   for( auto & kv : r.accs    ) keys.push_back( kv.first );
   for( auto & kv : r.grids   ) keys.push_back( kv.first );
   for( auto k : keys ) vpic_b200_forget( (void *)k );
+  release_boundary_buffers(); release_sort_buffers(); comm_shutdown();
   if( r.d_scratch ) cudaFree( r.d_scratch ); r.d_scratch = nullptr; r.scratch_bytes = 0;
   if( r.h_pinned ) cudaFreeHost( r.h_pinned ); r.h_pinned = nullptr; r.pinned_bytes = 0;
 }

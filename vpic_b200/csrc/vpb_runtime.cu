@@ -96,24 +96,39 @@ GridMirror * mirror( const vpb_grid_t * g ) {
   const int64_t s[3] = { 1, d.sy, d.sz };
   bool regular = g->neighbor!=nullptr;
   if( !g->neighbor ) VPB_ERROR( "grid_t.neighbor is NULL" );
+  if( !g->range ) VPB_ERROR( "grid_t.range is NULL" );
+  const int64_t rangem = g->range[g_world_size];
+  for( int f=0; f<6; f++ ) { m->pkind[f] = PK_LOCAL; m->nb_n[f] = 0; }
   for( int f=0; f<6 && regular; f++ ) {
     const int a = f%3, side = f<3 ? -1 : 1;
-    int cls = -1;
+    int cls = -1, kind = PK_LOCAL;
     for( int z=1; z<=n[2] && regular; z++ ) for( int y=1; y<=n[1] && regular; y++ ) for( int x=1; x<=n[0]; x++ ) {
       const int c[3] = { x, y, z };
       const int64_t v = x + s[1]*y + s[2]*z;
       const int64_t nb = g->neighbor[ 6*v + f ];
       const bool on_face = side<0 ? c[a]==1 : c[a]==n[a];
       if( !on_face ) { if( nb != g->rangel + v + side*s[a] ) { regular = false; break; } continue; }
-      int k;
+      int k, pk = PK_LOCAL;
       if( nb==VPB_REFLECT_PARTICLES ) k = FACE_REFLECT;
       else if( nb>=g->rangel && nb<=g->rangeh ) {
         k = FACE_WRAP;
         if( nb != g->rangel + v - side*s[a]*(n[a]-1) ) { regular = false; break; }
-      } else k = FACE_EXIT;
-      if( cls<0 ) cls = k; else if( cls!=k ) { regular = false; break; }
+      } else {
+        k = FACE_EXIT;
+        pk = nb==VPB_ABSORB_PARTICLES ? PK_ABSORB : ( nb>=0 && nb<=rangem ) ? PK_REMOTE : PK_CUSTOM;
+      }
+      if( cls<0 ) { cls = k; kind = pk; } else if( cls!=k || kind!=pk ) { regular = false; break; }
     }
     d.face[f] = cls<0 ? FACE_REFLECT : cls;
+    m->pkind[f] = kind;
+    if( kind==PK_REMOTE ) {
+      const int rank = g->bc[ bnd[f] ];
+      if( rank<0 || rank>=g_world_size ) { regular = false; break; }
+      const int64_t rnc = g->range[rank+1] - g->range[rank];
+      const int64_t plane = (int64_t)( n[(a+1)%3]+2 )*( n[(a+2)%3]+2 );
+      if( rnc%plane ) VPB_ERROR( "the brick of rank %d does not match this rank's face %d", rank, f );
+      m->nb_n[f] = (int)( rnc/plane ) - 2;
+    }
   }
   if( !regular ) {
     // Irregular (set_region_bc etc.): keep an explicit compact table.
@@ -126,7 +141,7 @@ GridMirror * mirror( const vpb_grid_t * g ) {
     VPB_CUDA( cudaMalloc( &m->d_neighbor, t.size()*sizeof(int32_t) ) );
     VPB_CUDA( cudaMemcpy( m->d_neighbor, t.data(), t.size()*sizeof(int32_t), cudaMemcpyHostToDevice ) );
     d.neighbor = m->d_neighbor;
-    for( int f=0; f<6; f++ ) d.face[f] = FACE_EXIT;
+    for( int f=0; f<6; f++ ) { d.face[f] = FACE_EXIT; m->pkind[f] = PK_CUSTOM; }
   }
   r.grids[g] = m;
   return m;

@@ -64,11 +64,20 @@ constexpr int32_t NB_EXIT    = -2;
 
 // ---- mirrors ---------------------------------------------------------------
 
+// What boundary_p does with a particle that left through a box face
+// (src/boundary/boundary_p.cc:196-260).
+enum ParticleFaceKind : int { PK_LOCAL = 0,    // wrap / reflect: move_p never hands these over
+                              PK_ABSORB = 1,   // absorb_particles: accumulate_rhob, drop
+                              PK_REMOTE = 2,   // neighbouring rank: send an injector
+                              PK_CUSTOM = 3 }; // user handler (host callback): not on the device
+
 struct GridMirror {
   const vpb_grid_t * host = nullptr;
   GridDev dev{};
   int32_t * d_neighbor = nullptr;
   int fbc[6];                // field boundary per face: rank (>=0) or local code (<0)
+  int pkind[6];              // ParticleFaceKind per face
+  int nb_n[6];               // for PK_REMOTE: the neighbour brick's cell count along the face axis
 };
 
 struct FieldMirror {
@@ -110,6 +119,7 @@ struct SpeciesMirror {
   int * d_partition = nullptr;     // nv+1 ints
   int * d_counters = nullptr;      // [0]=nm  [1]=n_ignored  [2..] scratch
   int np = 0, nm = 0;              // device-side truth while resident
+  bool movers_sorted = true;       // d_pm ascending in particle index
   bool dev_valid = false, host_valid = true;
   bool partition_dev_valid = false;
   const vpb_particle_t * registered_p = nullptr; size_t registered_bytes = 0;
@@ -165,7 +175,12 @@ struct PushCoef;
 void advance_p_parity( SpeciesMirror *, AccMirror *, InterpMirror *, const PushCoef & );
 void sort_movers_by_index( SpeciesMirror * );
 void comm_exchange_faces( FieldMirror * m, int X, float * slo, float * shi, float * rlo, float * rhi, int nfloat );
+void comm_sendrecv( int rank_lo, int rank_hi, const void * slo, size_t nslo, const void * shi, size_t nshi,
+                    void * rlo, size_t nrlo, void * rhi, size_t nrhi );   // device buffers, byte counts; rank<0 = no neighbour
 void comm_allsum_d( double * v, int n );
+bool comm_ready();
+void comm_shutdown();
+void release_boundary_buffers();
 void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
 void release_sort_buffers();
 __global__ void k_sum_partials( double * out, const double * partial, int nblock, int ncomp, double scale );

@@ -37,6 +37,8 @@ def load_b200():
     d, i, f = C.c_double, C.c_int, C.c_float
     sig = {
         "vpic_b200_init": (i, [i, i, i]), "vpic_b200_finalize": (None, []),
+        "vpic_b200_set_world": (None, [i, i]), "vpic_b200_comm_unique_id": (i, [_P, i]),
+        "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []),
         "vpic_b200_set_coherence": (None, [i]), "vpic_b200_set_deposit_mode": (None, [i]),
         "vpic_b200_abi_check": (i, [i] * 6),
         "vpic_b200_sync_to_host": (None, [_P]), "vpic_b200_sync_from_host": (None, [_P]),
