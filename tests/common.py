@@ -6,7 +6,7 @@ from vpic_b200 import Simulation, abi
 
 def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0.95, damp=0.0,
              species=(("electron", -1.0, 1.0), ("ion", 1.0, 100.0)), ppc=8, max_np_factor=1.5,
-             sort_interval=0, n_pipeline=1, topo=(1, 1, 1)):
+             sort_interval=0, n_pipeline=1, topo=(1, 1, 1), max_nm=None):
     nx, ny, nz = n
     L = length if length is not None else tuple(0.5 * k for k in n)
     dx = [L[a] / n[a] for a in range(3)]
@@ -17,7 +17,7 @@ def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0
     s.define_fields(damp=damp)
     ncell = nx * ny * nz
     for name, q, m in species:
-        s.define_species(name, q, m, int(max_np_factor * ppc * ncell) + 64, sort_interval=sort_interval)
+        s.define_species(name, q, m, int(max_np_factor * ppc * ncell) + 64, max_nm=max_nm, sort_interval=sort_interval)
     return s
 
 

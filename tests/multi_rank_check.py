@@ -75,7 +75,7 @@ def build(be, kind, gn, topo, rank, ppc, seed, sort_interval=3):
     idx = (rank % topo[0], (rank // topo[0]) % topo[1], rank // (topo[0] * topo[1]))
     origin = tuple(idx[a] * ln[a] for a in range(3))
     L = tuple(0.5 * k for k in gn)
-    s = make_sim(be, None, kind=kind, n=gn, length=L, topo=topo, ppc=2 * ppc, sort_interval=sort_interval, max_np_factor=2.0)
+    s = make_sim(be, None, kind=kind, n=gn, length=L, topo=topo, ppc=2 * ppc, sort_interval=sort_interval, max_np_factor=2.0, max_nm=4000)
     for k, sp in enumerate(s.species):
         p, cells = global_particles(gn, ppc, 0.25, seed + k)
         s.set_particles(sp, local_slice(p, cells, origin, ln))

@@ -128,6 +128,28 @@ def test_whole_steps_fast_mode(gpu, case):
     assert np.allclose(eg, eo, rtol=1e-6)
 
 
+def test_absorbing_box_boundary_p(gpu):
+    """Particles leave through absorbing walls: boundary_p on the device must
+    remove the same particles, leave the array in the reference's back-filled
+    order, and put their charge into rhob."""
+    so, sg = pair(gpu, sort_interval=3, vth=0.3, max_nm=2000, **CASES[5])
+    for s in (so, sg):
+        s.initialize()
+    n0 = [so.sp_struct(a).np for a in so.species]
+    for step in range(8):
+        so.advance(); sg.advance()
+        for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "jfx", "jfy", "jfz", "rhob"):
+            assert close(sg.fields()[k], so.fields()[k], 5e-5), (k, step)
+        for a, b in zip(so.species, sg.species):
+            assert so.sp_struct(a).np == sg.sp_struct(b).np, step
+            assert same_bits(sg.particles(b), so.particles(a)), step      # same survivors, same order
+            sg.particles(b)[:] = so.particles(a)
+        sg.fields()[:] = so.fields()
+        sg.interpolators()[:] = so.interpolators()
+    assert all(so.sp_struct(a).np < n for a, n in zip(so.species, n0)), "nothing was absorbed"
+    assert np.abs(so.fields()["rhob"]).max() > 0
+
+
 def test_resident_mode_matches_strict(gpu):
     L = load_b200()
     so, sg = pair(gpu, kind="periodic", n=(12, 6, 5), sort_interval=2)

@@ -11,10 +11,9 @@
 // the device version reproduces it exactly, in parallel:
 //   * the k-th mover in processing order gets the k-th slot of its face's
 //     message (block-wide ranking per chunk of 1024 movers),
-//   * all movers leave, so the holes below the new end of the array are filled,
-//     largest hole first, by the surviving particles of the tail, last first --
-//     which is a closed-form pairing found with two binary searches per tail
-//     particle (k_bnd_backfill),
+//   * all movers leave, so every surviving particle of the tail follows its own
+//     chain of "p[i] = p[--np]" copies to a hole below the new end of the array
+//     (k_bnd_backfill),
 //   * received injectors are ranked per species the same way and moved with
 //     every lane busy.
 // Messages travel as device buffers over NCCL (vpb_comm.cu): counts, then
@@ -126,9 +125,12 @@ k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_
 }
 
 // All nm movers (ascending particle index in pm) leave.  The reference's
-// "p[i] = p[--np]" walked over the movers in reverse is equivalent to: the
-// k-th largest hole below new_np receives the k-th largest surviving particle
-// of the tail [new_np, np).
+// "p[i] = p[--np]" walked over the movers in reverse means: step k (k=1..nm)
+// copies position np-k onto the k-th largest leaving index r_k.  A surviving
+// particle of the tail [new_np, np) at position np-k therefore lands on r_k;
+// if r_k is itself inside the tail it is picked up again at step np-r_k, and so
+// on until it reaches a hole below new_np.  Every tail survivor follows its
+// own chain, independently of the others.
 __device__ __forceinline__ int lower_bound_idx( const vpb_particle_mover_t * pm, int n, int key ) {   // first m with pm[m].i >= key
   int lo = 0, hi = n;
   while( lo<hi ) { const int mid = ( lo+hi )>>1; if( pm[mid].i<key ) lo = mid+1; else hi = mid; }
@@ -142,10 +144,12 @@ k_bnd_backfill( vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __
   if( j>=np ) return;
   const int lb = lower_bound_idx( pm, nm, j );
   if( lb<nm && pm[lb].i==j ) return;                 // j itself leaves
-  const int n_below = lower_bound_idx( pm, nm, new_np );   // holes below the new end
-  const int removed_gt = nm - lb;                    // leaving particles above j
-  const int k = ( np-1-j ) - removed_gt;             // j is the k-th largest survivor of the tail
-  const int hole = pm[ n_below-1-k ].i;
+  int k = np - j, hole;
+  for(;;) {
+    hole = pm[ nm-k ].i;                             // r_k
+    if( hole<new_np ) break;
+    k = np - hole;
+  }
   const float4 a = reinterpret_cast<const float4 *>( p + j )[0], b = reinterpret_cast<const float4 *>( p + j )[1];
   reinterpret_cast<float4 *>( p + hole )[0] = a;
   reinterpret_cast<float4 *>( p + hole )[1] = b;
