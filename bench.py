@@ -158,8 +158,14 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     L = load_b200()
-    # each rank is a rank-0-of-1 periodic brick until the NCCL halo exchange lands
-    L.vpic_b200_init(local, 0, 1)
+    L.vpic_b200_init(local, rank, world)
+    if world > 1:                          # one NCCL communicator for ghost faces, currents and migrating particles
+        buf = (C.c_char * 128)()
+        if rank == 0:
+            L.vpic_b200_comm_unique_id(buf, 128)
+        box = [bytes(buf)]
+        dist.broadcast_object_list(box, src=0)
+        L.vpic_b200_comm_init(box[0], 128)
     L.vpic_b200_set_coherence(1)           # RESIDENT
     be, host = b200_backend(), B200Host()
     stream = torch.cuda.ExternalStream(L.vpic_b200_stream(), device=local)
@@ -169,7 +175,7 @@ def run_b200(args):
             dist.barrier()
 
     n = dims(args.cells)
-    sim, sps = uniform_plasma(be, host, n, args.ppc, args.sort_interval)
+    sim, sps = uniform_plasma(be, host, n, args.ppc, args.sort_interval, topo=(world, 1, 1))
     for k, (sp, vth, w) in enumerate(sps):
         L.vpic_b200_load_uniform_maxwellian(sp, args.ppc, vth, w, 1234 + 17 * k + 1000 * rank)
     sim.initialize()
@@ -204,7 +210,8 @@ def run_b200(args):
            "config": {"workload": f"uniform Maxwellian e-/ion plasma, periodic {args.cells} cells per GPU, "
                                   f"2 species x {args.ppc} ppc, sort every {args.sort_interval} steps (BASELINE configs[3])",
                       "particles_per_gpu": np_total, "l2": "inputs (particles, fields) far larger than the 126 MB L2",
-                      "parallelism": "1 GPU" if world == 1 else f"{world} independent periodic bricks (halo exchange not wired yet)"},
+                      "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, slab decomposition ({world},1,1): ghost-B / jf face exchange and "
+                                                                          f"particle migration over NCCL every step"},
            "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary()}
     free_sim(L, sim)
 

@@ -150,6 +150,22 @@ def test_absorbing_box_boundary_p(gpu):
     assert np.abs(so.fields()["rhob"]).max() > 0
 
 
+def test_many_movers_sorted_on_device(gpu):
+    """> 2048 particles leave in one step: exercises the multi-chunk device sort
+    of the mover list that fixes boundary_p's processing order."""
+    so, sg = pair(gpu, kind="absorbing", n=(32, 24, 20), ppc=10, vth=0.8, max_nm=40000, damp=0.01)
+    for s in (so, sg):
+        s.initialize()
+    n0 = so.sp_struct(so.species[0]).np
+    for step in range(2):
+        so.advance(); sg.advance()
+        for a, b in zip(so.species, sg.species):
+            assert so.sp_struct(a).np == sg.sp_struct(b).np
+            assert same_bits(sg.particles(b), so.particles(a)), step
+        sg.fields()[:] = so.fields(); sg.interpolators()[:] = so.interpolators()
+    assert n0 - so.sp_struct(so.species[0]).np > 2 * 2048      # ~3800 leave per step
+
+
 def test_resident_mode_matches_strict(gpu):
     L = load_b200()
     so, sg = pair(gpu, kind="periodic", n=(12, 6, 5), sort_interval=2)

@@ -102,15 +102,65 @@ k_load_maxwellian( vpb_particle_t * __restrict__ p, long long np, int ppc, GridD
 
 // Movers come out of advance_p in atomic-append order; the reference's order
 // (single pipeline) is ascending particle index, and boundary_p's back-fill
-// makes the final particle order depend on it.  The list is short.
+// makes the final particle order depend on it.  Bitonic sort of the 16 B
+// movers by .i on the device: chunks of MS_CHUNK in shared memory, the wide
+// compare-exchange steps in global memory.
+constexpr int MS_CHUNK = 2048, MS_T = 1024;
+
+__device__ __forceinline__ void ms_cmpx( float4 & a, float4 & b, bool up ) {
+  if( ( __float_as_int( a.w )>__float_as_int( b.w ) )==up ) { const float4 t = a; a = b; b = t; }
+}
+
+// mode 0: sort each chunk completely (k = 2..MS_CHUNK); mode 1: finish stage k
+// inside each chunk (j = MS_CHUNK/2..1).  Direction from the GLOBAL index.
+__global__ void __launch_bounds__(MS_T)
+k_movers_bitonic_local( float4 * __restrict__ d, int k_stage, int mode ) {
+  __shared__ float4 s[MS_CHUNK];
+  const int base = blockIdx.x*MS_CHUNK;
+  s[threadIdx.x] = d[base+threadIdx.x]; s[threadIdx.x+MS_T] = d[base+threadIdx.x+MS_T];
+  __syncthreads();
+  for( int k = mode==0 ? 2 : k_stage; k<=( mode==0 ? MS_CHUNK : k_stage ); k<<=1 ) {
+    for( int j = ( k>MS_CHUNK ? MS_CHUNK : k )>>1; j>0; j>>=1 ) {
+      const int t = threadIdx.x;
+      const int lo = ( ( t & ~(j-1) )<<1 ) | ( t & (j-1) ), hi = lo | j;
+      const bool up = ( ( base+lo ) & k )==0;
+      ms_cmpx( s[lo], s[hi], up );
+      __syncthreads();
+    }
+  }
+  d[base+threadIdx.x] = s[threadIdx.x]; d[base+threadIdx.x+MS_T] = s[threadIdx.x+MS_T];
+}
+
+__global__ void __launch_bounds__(256)
+k_movers_bitonic_global( float4 * __restrict__ d, int n2, int k, int j ) {
+  const int t = blockIdx.x*blockDim.x + threadIdx.x;
+  if( t>=n2/2 ) return;
+  const int lo = ( ( t & ~(j-1) )<<1 ) | ( t & (j-1) ), hi = lo | j;
+  float4 a = d[lo], b = d[hi];
+  const bool up = ( lo & k )==0;
+  if( ( __float_as_int( a.w )>__float_as_int( b.w ) )==up ) { d[lo] = b; d[hi] = a; }
+}
+
+__global__ void k_movers_pad( float4 * __restrict__ d, const float4 * __restrict__ src, int n, int n2 ) {
+  const int t = blockIdx.x*blockDim.x + threadIdx.x;
+  if( t<n2 ) d[t] = t<n ? src[t] : make_float4( 0.f, 0.f, 0.f, __int_as_float( 0x7fffffff ) );
+}
+
 void sort_movers_by_index( SpeciesMirror * m ) {
   Runtime & r = rt();
-  std::vector<vpb_particle_mover_t> h( (size_t)m->nm );
-  VPB_CUDA( cudaMemcpyAsync( h.data(), m->d_pm, sizeof(vpb_particle_mover_t)*h.size(), cudaMemcpyDeviceToHost, r.stream ) );
-  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-  std::sort( h.begin(), h.end(), []( const vpb_particle_mover_t & a, const vpb_particle_mover_t & b ) { return a.i<b.i; } );
-  VPB_CUDA( cudaMemcpyAsync( m->d_pm, h.data(), sizeof(vpb_particle_mover_t)*h.size(), cudaMemcpyHostToDevice, r.stream ) );
-  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  const int n = m->nm;
+  if( n<2 ) return;
+  int n2 = MS_CHUNK; while( n2<n ) n2 <<= 1;
+  float4 * d = (float4 *)scratch( sizeof(float4)*(size_t)n2 );
+  k_movers_pad<<< div_up( n2, 256 ), 256, 0, r.stream >>>( d, (const float4 *)m->d_pm, n, n2 );
+  k_movers_bitonic_local<<< n2/MS_CHUNK, MS_T, 0, r.stream >>>( d, 0, 0 );
+  r.launches += 2;
+  for( int k=2*MS_CHUNK; k<=n2; k<<=1 ) {
+    for( int j=k>>1; j>=MS_CHUNK; j>>=1 ) { k_movers_bitonic_global<<< div_up( n2/2, 256 ), 256, 0, r.stream >>>( d, n2, k, j ); r.launches++; }
+    k_movers_bitonic_local<<< n2/MS_CHUNK, MS_T, 0, r.stream >>>( d, k, 1 ); r.launches++;
+  }
+  VPB_CHECK_LAUNCH();
+  VPB_CUDA( cudaMemcpyAsync( m->d_pm, d, sizeof(float4)*(size_t)n, cudaMemcpyDeviceToDevice, r.stream ) );
 }
 
 } // namespace vpb
