@@ -86,6 +86,9 @@ int  vpic_b200_comm_ready( void );
 void vpic_b200_finalize( void );
 void vpic_b200_set_coherence( int mode );
 void vpic_b200_set_deposit_mode( int mode );
+/* PARITY only: the reference's pipeline count (--tpp) whose summation order the
+   energy diagnostics reproduce (advance_p takes it from aa->n_pipeline). Default 1. */
+void vpic_b200_set_reference_pipelines( int n_pipeline );
 int  vpic_b200_abi_check( int sizeof_interpolator, int sizeof_accumulator, int sizeof_field,
                           int sizeof_particle, int sizeof_grid, int sizeof_species ); /* 0 = ok */
 /* obj = any species_t / field_array_t / interpolator_array_t / accumulator_array_t */

@@ -186,3 +186,50 @@ def test_resident_mode_matches_strict(gpu):
         assert np.array_equal(sr.particles(b)["i"], sg.particles(a)["i"])
     for k in ("ex", "ey", "ez", "cbx", "cby", "cbz"):
         assert close(sr.fields()[k], sg.fields()[k], 5e-5)
+
+
+# ---- PARITY deposit mode: the reference's summation order, bit for bit --------
+
+@pytest.fixture()
+def parity_mode(gpu):
+    L = load_b200()
+    L.vpic_b200_set_deposit_mode(1)
+    yield gpu
+    L.vpic_b200_set_deposit_mode(0)
+    L.vpic_b200_set_reference_pipelines(1)
+
+
+@pytest.mark.parametrize("case", CASES[:5])
+@pytest.mark.parametrize("n_pipeline", [1, 3])
+def test_parity_mode_accumulators_bit_exact(parity_mode, case, n_pipeline):
+    so, sg = pair(parity_mode, n_pipeline=n_pipeline, **case)
+    nv = so.grid_struct(so.g).nv
+    for s in (so, sg):
+        s.be.load_interpolator_array(s.ia, s.fa)
+        s.be.clear_accumulator_array(s.aa)
+        for sp in s.species_in_list_order():
+            s.be.uncenter_p(sp, s.ia)
+            s.be.advance_p(sp, s.aa, s.ia)
+        s.be.reduce_accumulator_array(s.aa)
+        s.be.clear_jf(s.fa)
+        s.be.unload_accumulator_array(s.fa, s.aa)
+    assert same_bits(sg.accumulators()[:nv], so.accumulators()[:nv])
+    assert same_bits(sg.fields(), so.fields())
+    for a, b in zip(so.species, sg.species):
+        assert same_bits(sg.particles(b), so.particles(a))
+
+
+@pytest.mark.parametrize("case", CASES[:5])
+def test_parity_mode_free_running_steps_bit_exact(parity_mode, case):
+    """No re-synchronisation: 25 full steps, then every particle, every field
+    component and every energy must equal the oracle's exactly."""
+    so, sg = pair(parity_mode, sort_interval=4, **case)
+    for s in (so, sg):
+        s.initialize()
+    for step in range(25):
+        so.advance(); sg.advance()
+    assert same_bits(sg.fields(), so.fields())
+    assert same_bits(sg.interpolators(), so.interpolators())
+    for a, b in zip(so.species, sg.species):
+        assert same_bits(sg.particles(b), so.particles(a))
+    assert sg.energies() == so.energies()

@@ -446,6 +446,13 @@ void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ) {
   FieldMirror * m = mirror( const_cast<vpb_field_array_t *>( fa ) );
   to_device( m );
   const GridDev & g = m->grid->dev; const vpb_grid_t * hg = fa->g;
+  if( r.deposit_mode==VPB_DEPOSIT_PARITY ) {      // the reference's summation order, bit for bit
+    double loc[6];
+    energy_f_parity( loc, m );
+    if( g_world_size>1 ) comm_allsum_d( loc, 6 );
+    for( int c=0; c<6; c++ ) en[c] = loc[c];
+    return;
+  }
   const int ncell = g.nx*g.ny*g.nz;
   int nb = div_up( ncell, EN_BLOCK ); if( nb>r.sm_count*4 ) nb = r.sm_count*4;
   double * partial = (double *)scratch( sizeof(double)*6*(size_t)nb );

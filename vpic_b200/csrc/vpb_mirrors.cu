@@ -252,7 +252,7 @@ void vpic_b200_forget( void * obj ) {
   if( r.species.count( obj ) ) { auto m = r.species[obj]; cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
   if( r.fields.count( obj )  ) { auto m = r.fields[obj]; cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
   if( r.interps.count( obj ) ) { auto m = r.interps[obj]; cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
-  if( r.accs.count( obj )    ) { auto m = r.accs[obj]; cudaFree( m->d ); delete m; r.accs.erase( obj ); return; }
+  if( r.accs.count( obj )    ) { auto m = r.accs[obj]; cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }
   if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
 }
 
@@ -275,7 +275,7 @@ void vpic_b200_finalize( void ) {
   for( auto & kv : r.accs    ) keys.push_back( kv.first );
   for( auto & kv : r.grids   ) keys.push_back( kv.first );
   for( auto k : keys ) vpic_b200_forget( (void *)k );
-  release_boundary_buffers(); release_sort_buffers(); comm_shutdown();
+  release_boundary_buffers(); release_sort_buffers(); release_parity_buffers(); comm_shutdown();
   if( r.d_scratch ) cudaFree( r.d_scratch ); r.d_scratch = nullptr; r.scratch_bytes = 0;
   if( r.h_pinned ) cudaFreeHost( r.h_pinned ); r.h_pinned = nullptr; r.pinned_bytes = 0;
 }

@@ -177,6 +177,11 @@ double energy_p( const vpb_species_t * sp, const vpb_interpolator_array_t * ia )
   to_device( ms ); to_device( mi );
   const vpb_grid_t * hg = sp->g;
   const float qdt_2mc = (sp->q*hg->dt)/(2*sp->m*hg->cvac);
+  if( r.deposit_mode==VPB_DEPOSIT_PARITY ) {      // the reference's summation order, bit for bit
+    double loc = energy_p_parity( ms, mi, qdt_2mc, sp->m );
+    if( g_world_size>1 ) comm_allsum_d( &loc, 1 );
+    return loc*( (double)hg->cvac*(double)hg->cvac );
+  }
   int nb = div_up( ms->np>0 ? ms->np : 1, EP_BLOCK ); if( nb>r.sm_count*8 ) nb = r.sm_count*8;
   double * partial = (double *)scratch( sizeof(double)*( (size_t)nb + 8 ) );
   k_energy_p<<< nb, EP_BLOCK, 0, r.stream >>>( partial, ms->d_p, ms->np, mi->d, qdt_2mc, sp->m );

@@ -108,6 +108,8 @@ struct AccMirror {
   vpb_accumulator_array_t * host = nullptr;
   GridMirror * grid = nullptr;
   float * d = nullptr;             // nv * 12 floats == host copy 0
+  float * d_priv = nullptr;        // PARITY mode only: copies 1..n_priv (the reference's per-pipeline accumulators)
+  int n_priv = 0;
   bool dev_valid = false, host_valid = true;
 };
 
@@ -132,6 +134,7 @@ struct Runtime {
   cudaStream_t copy_stream[2] = { nullptr, nullptr };
   int coherence = VPB_COHERENCE_STRICT;
   int deposit_mode = VPB_DEPOSIT_FAST;
+  int ref_pipelines = 1;              // PARITY: the reference's N_PIPELINE (--tpp) whose summation order is reproduced
   int sm_count = 148;
   // scratch shared by all species (sort destination, keys, scan space)
   void * d_scratch = nullptr; size_t scratch_bytes = 0;
@@ -173,6 +176,13 @@ template<class M> inline void finish_write( M * m ) {
 // cross-file internals
 struct PushCoef;
 void advance_p_parity( SpeciesMirror *, AccMirror *, InterpMirror *, const PushCoef & );
+void reduce_accumulators_parity( AccMirror * );
+void energy_f_parity( double * en6, FieldMirror * m );           // local (pre-allreduce) energies, reference summation order
+double energy_p_parity( SpeciesMirror * ms, InterpMirror * mi, float qdt_2mc, float msp );
+// counting-sort front end shared by sort_p and the PARITY deposit: start[0..nbin] = first slot of each bin,
+// perm[0..n) = element indices grouped by bin (order inside a bin arbitrary)
+void bin_indices( const int * keys, int n, int nbin, int * start, int * perm );
+void release_parity_buffers();
 void sort_movers_by_index( SpeciesMirror * );
 void comm_exchange_faces( FieldMirror * m, int X, float * slo, float * shi, float * rlo, float * rhi, int nfloat );
 void comm_sendrecv( int rank_lo, int rank_hi, const void * slo, size_t nslo, const void * shi, size_t nshi,

@@ -108,6 +108,7 @@ void clear_accumulator_array( vpb_accumulator_array_t * aa ) {
   // One device copy; ghosts are never deposited into, so clearing the whole
   // array is equivalent to the reference's [VOXEL(1,1,1), VOXEL(nx,ny,nz)] range.
   VPB_CUDA( cudaMemsetAsync( m->d, 0, sizeof(float)*ACC_STRIDE*(size_t)m->grid->dev.nv, r.stream ) );
+  if( m->d_priv ) VPB_CUDA( cudaMemsetAsync( m->d_priv, 0, sizeof(float)*ACC_STRIDE*(size_t)m->grid->dev.nv*(size_t)m->n_priv, r.stream ) );
   r.launches++;
   mark_dev_written( m );
   if( r.coherence==VPB_COHERENCE_STRICT && aa->a ) {
@@ -124,8 +125,13 @@ void clear_accumulator_array( vpb_accumulator_array_t * aa ) {
 
 void reduce_accumulator_array( vpb_accumulator_array_t * aa ) {
   if( !aa ) VPB_ERROR( "Bad args" );
-  // All device deposits already land in the single device copy (= host copy 0).
-  (void)mirror( aa );
+  // FAST: all device deposits already land in the single device copy (= host
+  // copy 0).  PARITY: add the per-pipeline copies with the reference's tree.
+  AccMirror * m = mirror( aa );
+  if( rt().deposit_mode==VPB_DEPOSIT_PARITY && m->dev_valid ) {
+    reduce_accumulators_parity( m );
+    finish_write( m );
+  }
 }
 
 void unload_accumulator_array( vpb_field_array_t * fa, const vpb_accumulator_array_t * aa ) {

@@ -9,13 +9,14 @@
 //   2. exclusive scan of the histogram -> partition[],
 //   3. scatter the particle INDICES into their voxel's segment (atomic slots;
 //      order inside a segment is arbitrary at this point),
-//   4. sort every segment ascending (warp per voxel, bitonic) -> this is what
-//      makes the sort stable and run-to-run deterministic,
-//   5. gather the 32 B particles through the permutation into the spare buffer
-//      (coalesced 2 x 128-bit stores) and swap buffers.
+//   4. the warp that owns a voxel ranks its segment ascending (this is what
+//      makes the sort stable and run-to-run deterministic) and, in the same
+//      kernel, copies the 32 B particles to their final places in the spare
+//      buffer (2 x 128-bit loads / stores each); buffers are swapped.
 // Algorithmic traffic: 4 B key + 32 B read + 32 B write per particle (SURVEY
 // 8d: 68 B); this version moves ~120 B because of the index passes.
 #include "vpb_runtime.h"
+#include "vpb_sortutil.cuh"
 
 namespace vpb {
 
@@ -117,64 +118,79 @@ k_sort_scatter_idx( const int * __restrict__ keys, int np, int * __restrict__ ne
 // Segments <= 32: shuffle bitonic.  <= FIX_SMEM: bitonic in shared memory.
 // Larger: bitonic in global memory by the same warp (rare: > 2048 particles in
 // one voxel).
-constexpr int FIX_SMEM = 2048, FIX_WARPS = 4;
 
-__device__ __forceinline__ void bitonic_mem( int * a, int n2, int lane ) {   // n2 power of two, padded with INT_MAX
-  for( int k=2; k<=n2; k<<=1 ) for( int j=k>>1; j>0; j>>=1 ) {
-    for( int t=lane; t<n2/2; t+=32 ) {
-      const int lo = ( ( t & ~(j-1) )<<1 ) | ( t & (j-1) ), hi = lo | j;
-      const bool up = ( lo & k )==0;
-      const int x = a[lo], y = a[hi];
-      if( ( x>y )==up ) { a[lo] = y; a[hi] = x; }
-    }
-    __syncwarp();
-  }
+__device__ __forceinline__ void copy_particle( vpb_particle_t * __restrict__ out, int dst, const vpb_particle_t * __restrict__ in, int src ) {
+  const float4 * s = reinterpret_cast<const float4 *>( in + src );
+  const float4 a = __ldg( s ), b = __ldg( s+1 );
+  float4 * d = reinterpret_cast<float4 *>( out + dst );
+  d[0] = a; d[1] = b;
 }
 
+// Fix-up and gather fused: the warp that owns voxel v puts the particle
+// indices of its segment in ascending order (= original array order: that is
+// what makes the sort stable) and copies the particles to their final places.
+// Segments of <= 32*FIX_E indices are ranked in registers by counting
+// (rank = number of smaller indices; broadcast by shuffle), larger ones fall
+// back to the bitonic sorts.
+constexpr int FIX_E = 4;
+
 __global__ void __launch_bounds__(32*FIX_WARPS)
-k_sort_fix( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch ) {
+k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch,
+                   const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
   __shared__ int s[FIX_WARPS][FIX_SMEM];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int v = blockIdx.x*FIX_WARPS + w;
   if( v>=nv ) return;
   const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
-  if( n<=1 ) return;
-  if( n<=32 ) {
-    int x = lane<n ? perm[b+lane] : 0x7fffffff;
-    for( int k=2; k<=32; k<<=1 ) for( int j=k>>1; j>0; j>>=1 ) {
-      const int y = __shfl_xor_sync( 0xffffffffu, x, j );
-      const bool up = ( lane & k )==0, lower = ( lane & j )==0;
-      x = ( lower==up ) ? min( x, y ) : max( x, y );
+  if( n<=0 ) return;
+  if( n<=32*FIX_E ) {
+    int x[FIX_E], rank[FIX_E];
+#   pragma unroll
+    for( int k=0; k<FIX_E; k++ ) { x[k] = 32*k+lane<n ? perm[b+32*k+lane] : 0x7fffffff; rank[k] = 0; }
+#   pragma unroll
+    for( int k=0; k<FIX_E; k++ ) {
+      if( 32*k<n ) {
+        const int m = n-32*k<32 ? n-32*k : 32;
+        for( int l=0; l<m; l++ ) {
+          const int y = __shfl_sync( 0xffffffffu, x[k], l );
+#         pragma unroll
+          for( int q=0; q<FIX_E; q++ ) rank[q] += ( y<x[q] ) ? 1 : 0;
+        }
+      }
     }
-    if( lane<n ) perm[b+lane] = x;
+#   pragma unroll
+    for( int k=0; k<FIX_E; k++ ) if( 32*k+lane<n ) copy_particle( out, b+rank[k], in, x[k] );
     return;
   }
   int n2 = 64; while( n2<n ) n2 <<= 1;
-  if( n2<=FIX_SMEM ) {
-    int * a = s[w];
-    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
-    __syncwarp();
-    bitonic_mem( a, n2, lane );
-    for( int t=lane; t<n; t+=32 ) perm[b+t] = a[t];
-  } else {
-    // big_scratch holds 2*np ints: each huge segment uses the window starting
-    // at 2*b, which cannot overlap another segment's window of size n2 < 2n.
-    int * a = big_scratch + 2*(size_t)b;
-    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
-    __threadfence_block(); __syncwarp();
-    bitonic_mem( a, n2, lane );
-    for( int t=lane; t<n; t+=32 ) perm[b+t] = a[t];
-  }
+  int * a;
+  if( n2<=FIX_SMEM ) a = s[w];
+  else a = big_scratch + 2*(size_t)b;     // window of n2 < 2n ints starting at 2b: windows of different voxels are disjoint
+  for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+  __threadfence_block(); __syncwarp();
+  bitonic_mem( a, n2, lane );
+  for( int t=lane; t<n; t+=32 ) copy_particle( out, b+t, in, a[t] );
 }
 
 __global__ void __launch_bounds__(256)
-k_sort_gather( const vpb_particle_t * __restrict__ in, const int * __restrict__ perm, vpb_particle_t * __restrict__ out, int np ) {
+k_hist_keys( const int * __restrict__ keys, int n, int * __restrict__ count ) {
   const int i = blockIdx.x*blockDim.x + threadIdx.x;
-  if( i>=np ) return;
-  const float4 * src = reinterpret_cast<const float4 *>( in + perm[i] );
-  const float4 a = __ldg( src ), b = __ldg( src+1 );
-  float4 * dst = reinterpret_cast<float4 *>( out + i );
-  dst[0] = a; dst[1] = b;
+  const int key = i<n ? keys[i] : -1;
+  const unsigned m = __match_any_sync( 0xffffffffu, key );
+  if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+}
+
+void bin_indices( const int * keys, int n, int nbin, int * start, int * perm ) {
+  Runtime & r = rt();
+  const size_t nba = ( (size_t)nbin + 1 + 31 ) & ~(size_t)31;
+  const size_t ntile = (size_t)div_up( nbin+1, SCAN_TILE ) + 32;
+  int * base = (int *)scratch( sizeof(int)*( 2*nba + ntile + 64 ) );
+  int * count = base, * next = count + nba, * tiles = next + nba;
+  VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nbin+1 ), r.stream ) );
+  if( n>0 ) { k_hist_keys<<< div_up(n,256), 256, 0, r.stream >>>( keys, n, count ); r.launches++; }
+  exclusive_scan( count, start, next, tiles, nbin+1 );
+  if( n>0 ) { k_sort_scatter_idx<<< div_up(n,256), 256, 0, r.stream >>>( keys, n, next, perm ); r.launches++; }
+  VPB_CHECK_LAUNCH();
 }
 
 // spare particle buffer shared by all species (swapped with the sorted species)
@@ -212,9 +228,8 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   exclusive_scan( count, m->d_partition, next, tiles, nv+1 );
   if( np>0 ) {
     k_sort_scatter_idx<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, next, perm );
-    k_sort_fix<<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big );
-    k_sort_gather<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, perm, g_alt, np );
-    VPB_CHECK_LAUNCH(); r.launches += 3;
+    k_sort_fix_gather<<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt );
+    VPB_CHECK_LAUNCH(); r.launches += 2;
     // swap the species buffer with the spare
     vpb_particle_t * t = m->d_p; size_t tc = m->cap_p;
     m->d_p = g_alt; m->cap_p = g_alt_cap; g_alt = t; g_alt_cap = tc;

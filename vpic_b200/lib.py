@@ -40,6 +40,7 @@ def load_b200():
         "vpic_b200_set_world": (None, [i, i]), "vpic_b200_comm_unique_id": (i, [_P, i]),
         "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []),
         "vpic_b200_set_coherence": (None, [i]), "vpic_b200_set_deposit_mode": (None, [i]),
+        "vpic_b200_set_reference_pipelines": (None, [i]),
         "vpic_b200_abi_check": (i, [i] * 6),
         "vpic_b200_sync_to_host": (None, [_P]), "vpic_b200_sync_from_host": (None, [_P]),
         "vpic_b200_forget": (None, [_P]), "vpic_b200_device_synchronize": (None, []),
