@@ -97,6 +97,7 @@ void vpic_b200_sync_from_host( void * obj );   /* host struct arrays -> device  
 void vpic_b200_forget( void * obj );           /* drop the mirror (before free())    */
 void vpic_b200_device_synchronize( void );
 long long vpic_b200_launch_count( void );      /* kernels launched so far            */
+void vpic_b200_transfer_bytes( long long * h2d_d2h ); /* bytes copied host->device, device->host so far */
 void * vpic_b200_stream( void );               /* cudaStream_t the kernels run on    */
 /* Device pointers of a mirror, for tests/benchmarks: which = 0 particles,
    1 movers, 2 partition (species); 0 SoA planes (field); 0 coefficients

@@ -188,6 +188,24 @@ def test_resident_mode_matches_strict(gpu):
         assert close(sr.fields()[k], sg.fields()[k], 5e-5)
 
 
+def test_streamed_strict_advance_p_large(gpu):
+    """> 8M host-resident particles in STRICT mode take the chunk-pipelined path
+    (upload / push / download overlapped); it must give the same particles as the
+    oracle, bit for bit, and the same currents within the FAST tolerance."""
+    so, sg = pair(gpu, kind="periodic", n=(64, 64, 50), ppc=44, max_np_factor=1.05)
+    nv = so.grid_struct(so.g).nv
+    assert so.sp_struct(so.species[0]).np > 2 * (1 << 22)
+    for s in (so, sg):
+        s.be.load_interpolator_array(s.ia, s.fa)
+        s.be.clear_accumulator_array(s.aa)
+        for sp in s.species_in_list_order():
+            s.be.advance_p(sp, s.aa, s.ia)
+        s.be.reduce_accumulator_array(s.aa)
+    for a, b in zip(so.species, sg.species):
+        assert same_bits(sg.particles(b), so.particles(a))
+    assert close(sg.accumulators()[:nv], so.accumulators()[:nv], RTOL_J)
+
+
 # ---- PARITY deposit mode: the reference's summation order, bit for bit --------
 
 @pytest.fixture()

@@ -29,6 +29,7 @@
 // voxel, 80 B interpolator + 48 B accumulator read-modify-write (SURVEY 8d:
 // 64 + 176/ppc bytes per push).
 #include "vpb_push.cuh"
+#include <vector>
 
 namespace vpb {
 
@@ -41,7 +42,7 @@ constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 struct __align__(128) WarpTile {
   float4 tile[2*AP_TILE];               // the particles, array order (8 KB)
   // queue of particles that left their voxel (structure of arrays)
-  int   q_idx[AP_QCAP];                 // index in sp->p
+  int   q_idx[AP_QCAP];                 // index inside the tile
   float q_dx[AP_QCAP], q_dy[AP_QCAP], q_dz[AP_QCAP];
   int   q_i[AP_QCAP];
   float q_dispx[AP_QCAP], q_dispy[AP_QCAP], q_dispz[AP_QCAP];
@@ -54,13 +55,13 @@ __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_
 // Run move_p (move_p.cc:216-353) on up to 32 queued particles, one per lane.
 // The queue is emptied before its tile is written back, so every entry is
 // finished in the shared-memory copy of the tile.
-__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane, long long t0,
+__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane, long long idx0,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
                                                 int max_nm, int * __restrict__ counters, const GridDev & g ) {
   if( lane>=n ) return;
   const int e = base + lane;
-  const int idx = S.q_idx[e];
-  float4 * slot = &S.tile[ 2*(int)( idx-t0 ) ];
+  const int loc = S.q_idx[e];
+  float4 * slot = &S.tile[ 2*loc ];
   const float4 r1 = slot[1];
   MoveState ms;
   ms.dx = S.q_dx[e]; ms.dy = S.q_dy[e]; ms.dz = S.q_dz[e]; ms.i = S.q_i[e];
@@ -78,13 +79,15 @@ __device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, i
   slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );       // reflections flip a momentum component
   if( status==2 ) {
     const int k = atomicAdd( counters+0, 1 );
-    if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
+    if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( (int)( idx0 + loc ) ) );
     else atomicAdd( counters+1, 1 );
   }
 }
 
+// p points at the first particle of the range this launch owns (np particles,
+// ntile tiles); idx_base is that particle's index in sp->p (mover indices).
 __global__ void __launch_bounds__( 32*AP_WARPS, AP_MINBLK )
-k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
+k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
              const float * __restrict__ ip, float * __restrict__ acc,
              vpb_particle_mover_t * __restrict__ pm, int max_nm, int * __restrict__ counters,
              GridDev g, PushCoef c ) {
@@ -190,7 +193,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
       if( m ) {
         if( cross ) {
           const int e = qn + __popc( m & ( ( 1u<<lane )-1u ) );
-          S.q_idx[e] = (int)( t0 + loc );
+          S.q_idx[e] = loc;
           S.q_dx[e] = cdx; S.q_dy[e] = cdy; S.q_dz[e] = cdz; S.q_i[e] = ci;
           S.q_dispx[e] = cux; S.q_dispy[e] = cuy; S.q_dispz[e] = cuz; S.q_q[e] = cq;
         }
@@ -198,7 +201,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
         __syncwarp();
         if( qn>=32 ) {
           qn -= 32;
-          drain_crossers( S, qn, 32, lane, t0, acc, pm, max_nm, counters, g );
+          drain_crossers( S, qn, 32, lane, idx_base + t0, acc, pm, max_nm, counters, g );
           __syncwarp();
         }
       }
@@ -208,7 +211,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
     while( qn>0 ) {
       const int n = qn<32 ? qn : 32;
       qn -= n;
-      drain_crossers( S, qn, n, lane, t0, acc, pm, max_nm, counters, g );
+      drain_crossers( S, qn, n, lane, idx_base + t0, acc, pm, max_nm, counters, g );
       __syncwarp();
     }
     // write the tile back: generic-proxy writes -> async-proxy bulk store
@@ -230,13 +233,71 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile,
 
 using namespace vpb;
 
+namespace {
+
+int advance_p_blocks_per_sm() {
+  static int blocks_per_sm = 0;
+  if( !blocks_per_sm ) {
+    VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
+    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, k_advance_p, 32*AP_WARPS, 0 ) );
+    if( blocks_per_sm<1 ) VPB_ERROR( "k_advance_p does not fit on an SM" );
+  }
+  return blocks_per_sm;
+}
+
+void launch_advance_p( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, const PushCoef & c, int first, int count ) {
+  Runtime & r = rt();
+  const int ntile = div_up( count, AP_TILE );
+  int nblock = r.sm_count*advance_p_blocks_per_sm();
+  if( nblock>div_up( ntile, AP_WARPS ) ) nblock = div_up( ntile, AP_WARPS );
+  k_advance_p<<< nblock, 32*AP_WARPS, 0, r.stream >>>( ms->d_p + first, count, ntile, first, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
+                                                        ms->d_counters, ms->grid->dev, c );
+  VPB_CHECK_LAUNCH(); r.launches++;
+}
+
+// STRICT coherence with host-resident particles: stream the array through the
+// device in chunks -- upload chunk k+1, push chunk k, download chunk k-1 run
+// concurrently on three streams (PCIe is full duplex), so the call costs about
+// max(upload, download) instead of upload + push + download.
+constexpr int AP_CHUNK = 1<<22;       // particles per chunk (128 MB)
+
+bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, const PushCoef & c ) {
+  Runtime & r = rt();
+  vpb_species_t * sp = ms->host;
+  if( r.coherence!=VPB_COHERENCE_STRICT || !sp->p || sp->np<2*AP_CHUNK || r.deposit_mode!=VPB_DEPOSIT_FAST ) return false;
+  if( ms->dev_valid && !ms->host_valid ) return false;             // the device holds the only current copy
+  ms->np = sp->np;
+  pin_host( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
+  static std::vector<cudaEvent_t> ev;
+  const int nchunk = div_up( ms->np, AP_CHUNK );
+  while( (int)ev.size()<2*nchunk+1 ) { cudaEvent_t e; VPB_CUDA( cudaEventCreateWithFlags( &e, cudaEventDisableTiming ) ); ev.push_back( e ); }
+  VPB_CUDA( cudaEventRecord( ev[2*nchunk], r.stream ) );            // uploads must not overtake earlier work on the buffers
+  VPB_CUDA( cudaStreamWaitEvent( r.copy_stream[0], ev[2*nchunk], 0 ) );
+  for( int k=0; k<nchunk; k++ ) {
+    const int first = k*AP_CHUNK, count = ( ms->np-first<AP_CHUNK ) ? ms->np-first : AP_CHUNK;
+    const size_t bytes = sizeof(vpb_particle_t)*(size_t)count;
+    h2d( ms->d_p + first, sp->p + first, bytes, r.copy_stream[0] );
+    VPB_CUDA( cudaEventRecord( ev[2*k], r.copy_stream[0] ) );
+    VPB_CUDA( cudaStreamWaitEvent( r.stream, ev[2*k], 0 ) );
+    launch_advance_p( ms, ma, mi, c, first, count );
+    VPB_CUDA( cudaEventRecord( ev[2*k+1], r.stream ) );
+    VPB_CUDA( cudaStreamWaitEvent( r.copy_stream[1], ev[2*k+1], 0 ) );
+    d2h( sp->p + first, ms->d_p + first, bytes, r.copy_stream[1] );
+  }
+  VPB_CUDA( cudaStreamSynchronize( r.copy_stream[1] ) );
+  ms->dev_valid = true; ms->host_valid = true; ms->partition_dev_valid = false;
+  return true;
+}
+
+} // namespace
+
 extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, const vpb_interpolator_array_t * ia ) {
   if( !sp || !aa || !ia || sp->g!=aa->g || sp->g!=ia->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
   SpeciesMirror * ms = mirror( sp );
   AccMirror     * ma = mirror( aa );
   InterpMirror  * mi = mirror( const_cast<vpb_interpolator_array_t *>( ia ) );
-  to_device( ms ); to_device( ma ); to_device( mi );
+  to_device( ma ); to_device( mi );
   const vpb_grid_t * hg = sp->g;
   PushCoef c;
   c.qdt_2mc = (sp->q*hg->dt)/(2*sp->m*hg->cvac);      // advance_p_pipeline.cc:267-271
@@ -245,32 +306,24 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   c.cdt_dz  = hg->cvac*hg->dt*hg->rdz;
   c.qsp     = sp->q;
   VPB_CUDA( cudaMemsetAsync( ms->d_counters, 0, sizeof(int)*2, r.stream ) );
-  if( ms->np>0 ) {
-    if( r.deposit_mode==VPB_DEPOSIT_PARITY ) advance_p_parity( ms, ma, mi, c );
-    else {
-      static int blocks_per_sm = 0;
-      if( !blocks_per_sm ) {
-        VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
-        VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, k_advance_p, 32*AP_WARPS, 0 ) );
-        if( blocks_per_sm<1 ) VPB_ERROR( "k_advance_p does not fit on an SM" );
-      }
-      const int ntile = div_up( ms->np, AP_TILE );
-      int nblock = r.sm_count*blocks_per_sm;
-      if( nblock>div_up( ntile, AP_WARPS ) ) nblock = div_up( ntile, AP_WARPS );
-      k_advance_p<<< nblock, 32*AP_WARPS, 0, r.stream >>>( ms->d_p, ms->np, ntile, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
-                                                            ms->d_counters, ms->grid->dev, c );
-      VPB_CHECK_LAUNCH(); r.launches++;
+  const bool streamed = advance_p_streamed( ms, ma, mi, c );
+  if( !streamed ) {
+    to_device( ms );
+    if( ms->np>0 ) {
+      if( r.deposit_mode==VPB_DEPOSIT_PARITY ) advance_p_parity( ms, ma, mi, c );
+      else launch_advance_p( ms, ma, mi, c, 0, ms->np );
     }
   }
   // The mover count is what the host driver reads next (advance.cc:73-101).
   int cnt[2];
-  VPB_CUDA( cudaMemcpyAsync( cnt, ms->d_counters, sizeof(int)*2, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( cnt, ms->d_counters, sizeof(int)*2, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( cnt[1] ) VPB_WARNING( "Species \"%s\" ran out of storage for %i movers", sp->name, cnt[1] );   // advance_p_pipeline.cc:301-305
   ms->nm = cnt[0]<(int)ms->cap_pm ? cnt[0] : (int)ms->cap_pm;
   if( ms->nm>1 ) sort_movers_by_index( ms );
   ms->movers_sorted = true;
-  mark_dev_written( ms ); mark_dev_written( ma );
+  if( !streamed ) mark_dev_written( ms );
+  mark_dev_written( ma );
   movers_to_host( ms );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ms ); to_host( ma ); }
 }

@@ -270,6 +270,15 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   if( !sp_list ) return;                                        // boundary_p.cc:77
   if( !fa || !aa || sp_list->g!=aa->g || fa->g!=aa->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
+  {
+    // Nothing left the domain and no neighbour rank to talk to: return before
+    // touching the mirrors (in STRICT coherence that would re-upload every particle).
+    GridMirror * g0 = mirror( sp_list->g );
+    bool remote = false; long long pending = 0;
+    for( int f=0; f<6; f++ ) if( g0->pkind[f]==PK_REMOTE ) remote = true;
+    for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) pending += sp->nm;    // always current on the host (movers_to_host)
+    if( !remote && pending==0 ) return;
+  }
   std::vector<SpeciesMirror *> sps;
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
     SpeciesMirror * m = mirror( sp );
@@ -316,7 +325,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     mark_dev_written( m );
   }
   int h_int[32];
-  VPB_CUDA( cudaMemcpyAsync( h_int, B.d_int, sizeof(int)*32, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( h_int, B.d_int, sizeof(int)*32, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( h_int[16] ) VPB_WARNING( "Unknown boundary interaction ... dropping %d particles", h_int[16] );   // boundary_p.cc:259-260
   int n_send[6], n_recv[6] = { 0, 0, 0, 0, 0, 0 };
@@ -330,7 +339,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
       if( rank_lo<0 && rank_hi<0 ) continue;
       comm_sendrecv( rank_lo, rank_hi, B.d_int+lo, 4, B.d_int+hi, 4, B.d_int+8+lo, 4, B.d_int+8+hi, 4 );
     }
-    VPB_CUDA( cudaMemcpyAsync( n_recv, B.d_int+8, sizeof(int)*6, cudaMemcpyDeviceToHost, r.stream ) );
+    d2h( n_recv, B.d_int+8, sizeof(int)*6, r.stream );
     VPB_CUDA( cudaStreamSynchronize( r.stream ) );
     for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) grow( &B.recv[f], &B.recv_cap[f], (size_t)n_recv[f] ); else n_recv[f] = 0;
     const size_t S = sizeof(vpb_particle_injector_t);
@@ -361,7 +370,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
     VPB_CHECK_LAUNCH(); r.launches++;
     int h_cnt[4*BND_MAX_SP+1];
-    VPB_CUDA( cudaMemcpyAsync( h_cnt, B.d_int+32, sizeof(h_cnt), cudaMemcpyDeviceToHost, r.stream ) );
+    d2h( h_cnt, B.d_int+32, sizeof(h_cnt), r.stream );
     VPB_CUDA( cudaStreamSynchronize( r.stream ) );
     if( h_cnt[3*BND_MAX_SP] ) VPB_WARNING( "Dropped %d received particles of unknown species", h_cnt[3*BND_MAX_SP] );
     for( SpeciesMirror * m : sps ) {

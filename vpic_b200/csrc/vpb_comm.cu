@@ -96,9 +96,9 @@ void comm_allsum_d( double * v, int n ) {
   Runtime & r = rt();
   if( n>64 ) VPB_ERROR( "allreduce of %d doubles", n );
   if( !N.d_red ) VPB_CUDA( cudaMalloc( &N.d_red, sizeof(double)*64 ) );
-  VPB_CUDA( cudaMemcpyAsync( N.d_red, v, sizeof(double)*(size_t)n, cudaMemcpyHostToDevice, r.stream ) );
+  h2d( N.d_red, v, sizeof(double)*(size_t)n, r.stream );
   VPB_NCCL( N.AllReduce( N.d_red, N.d_red, (size_t)n, ncclFloat64, ncclSum, N.comm, r.stream ) );
-  VPB_CUDA( cudaMemcpyAsync( v, N.d_red, sizeof(double)*(size_t)n, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( v, N.d_red, sizeof(double)*(size_t)n, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   r.launches++;
 }

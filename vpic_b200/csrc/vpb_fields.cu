@@ -463,7 +463,7 @@ void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ) {
   k_sum_partials<<< 1, 32, 0, r.stream >>>( m->d_en, partial, nb, 6, v0 );
   VPB_CHECK_LAUNCH(); r.launches++;
   double local[6];
-  VPB_CUDA( cudaMemcpyAsync( local, m->d_en, sizeof(double)*6, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( local, m->d_en, sizeof(double)*6, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( g_world_size>1 ) comm_allsum_d( local, 6 );
   for( int c=0; c<6; c++ ) en[c] = local[c];

@@ -37,7 +37,8 @@ void to_device( InterpMirror * m ) {
   static_assert( sizeof(vpb_interpolator_t)==sizeof(float)*IP_HOST, "host interpolator layout" );
   const int nv = m->grid->dev.nv;
   if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(float)*IP_HOST*(size_t)nv ) );
-  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv, cudaMemcpyHostToDevice, r.stream ) );
+  pin_host( m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv );
+  h2d( m->d_stage, m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv, r.stream );
   k_interp_restride<<< div_up( 5LL*nv, 256 ), 256, 0, r.stream >>>( m->d, IP_STRIDE, m->d_stage, IP_HOST, nv );
   VPB_CHECK_LAUNCH(); r.launches++;
   m->dev_valid = true;
@@ -50,7 +51,7 @@ void to_host( InterpMirror * m ) {
   if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(float)*IP_HOST*(size_t)nv ) );
   k_interp_restride<<< div_up( 5LL*nv, 256 ), 256, 0, r.stream >>>( m->d_stage, IP_HOST, m->d, IP_STRIDE, nv );
   VPB_CHECK_LAUNCH(); r.launches++;
-  VPB_CUDA( cudaMemcpyAsync( m->host->i, m->d_stage, sizeof(vpb_interpolator_t)*(size_t)nv, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( m->host->i, m->d_stage, sizeof(vpb_interpolator_t)*(size_t)nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
 }
@@ -81,14 +82,15 @@ void to_device( AccMirror * m ) {
   if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
   if( !m->host->a ) { if( m->dev_valid ) return; VPB_ERROR( "accumulator array has neither host nor device data" ); }
   static_assert( sizeof(vpb_accumulator_t)==sizeof(float)*ACC_STRIDE, "device accumulator layout == host layout" );
-  VPB_CUDA( cudaMemcpyAsync( m->d, m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, cudaMemcpyHostToDevice, r.stream ) );
+  pin_host( m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv );
+  h2d( m->d, m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, r.stream );
   m->dev_valid = true;
 }
 
 void to_host( AccMirror * m ) {
   Runtime & r = rt();
   if( !m->dev_valid || m->host_valid || !m->host->a ) return;
-  VPB_CUDA( cudaMemcpyAsync( m->host->a, m->d, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( m->host->a, m->d, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
 }
@@ -136,13 +138,14 @@ void to_device( SpeciesMirror * m ) {
   if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
   if( !m->host->p ) { if( m->dev_valid ) return; VPB_ERROR( "species \"%s\" has neither host nor device particles", m->host->name ); }
   m->np = m->host->np; m->nm = m->host->nm;
+  pin_host( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np );
   if( m->np>0 )
-    VPB_CUDA( cudaMemcpyAsync( m->d_p, m->host->p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyHostToDevice, r.stream ) );
+    h2d( m->d_p, m->host->p, sizeof(vpb_particle_t)*(size_t)m->np, r.stream );
   // pending movers travel with the particles (the host may have added some:
   // inject_particle, emitters; src/vpic/misc.cc:86-99)
   if( m->nm>(int)m->cap_pm ) VPB_ERROR( "species \"%s\": nm=%d exceeds max_nm=%zu", m->host->name, m->nm, m->cap_pm );
   if( m->nm>0 && m->host->pm ) {
-    VPB_CUDA( cudaMemcpyAsync( m->d_pm, m->host->pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, cudaMemcpyHostToDevice, r.stream ) );
+    h2d( m->d_pm, m->host->pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, r.stream );
     m->movers_sorted = false;
     for( int k=1; k<m->nm; k++ ) if( m->host->pm[k].i<=m->host->pm[k-1].i ) goto unsorted;
     m->movers_sorted = true;
@@ -156,9 +159,9 @@ void to_host( SpeciesMirror * m ) {
   if( !m->dev_valid || m->host_valid ) return;
   m->host->np = m->np;
   if( m->host->p && m->np>0 )
-    VPB_CUDA( cudaMemcpyAsync( m->host->p, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyDeviceToHost, r.stream ) );
+    d2h( m->host->p, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, r.stream );
   if( m->host->partition && m->partition_dev_valid )
-    VPB_CUDA( cudaMemcpyAsync( m->host->partition, m->d_partition, sizeof(int)*(size_t)m->grid->dev.nv, cudaMemcpyDeviceToHost, r.stream ) );
+    d2h( m->host->partition, m->d_partition, sizeof(int)*(size_t)m->grid->dev.nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( m->host->p ) m->host_valid = true;
 }
@@ -169,7 +172,7 @@ void movers_to_host( SpeciesMirror * m ) {
   Runtime & r = rt();
   m->host->nm = m->nm;
   if( m->host->pm && m->nm>0 )
-    VPB_CUDA( cudaMemcpyAsync( m->host->pm, m->d_pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, cudaMemcpyDeviceToHost, r.stream ) );
+    d2h( m->host->pm, m->d_pm, sizeof(vpb_particle_mover_t)*(size_t)m->nm, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
 }
 
@@ -223,6 +226,7 @@ void vpic_b200_device_synchronize( void ) {
 }
 
 long long vpic_b200_launch_count( void ) { return rt().launches; }
+void vpic_b200_transfer_bytes( long long * h2d_d2h ) { if( h2d_d2h ) { h2d_d2h[0] = rt().h2d_bytes; h2d_d2h[1] = rt().d2h_bytes; } }
 void * vpic_b200_stream( void ) { ensure_init(); return (void *)rt().stream; }
 
 #define VPB_FIND( map, obj ) ( rt().map.find( obj )!=rt().map.end() ? rt().map[obj] : nullptr )
@@ -249,10 +253,10 @@ void vpic_b200_forget( void * obj ) {
   Runtime & r = rt();
   if( !r.initialised ) return;
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-  if( r.species.count( obj ) ) { auto m = r.species[obj]; cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
-  if( r.fields.count( obj )  ) { auto m = r.fields[obj]; cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
-  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
-  if( r.accs.count( obj )    ) { auto m = r.accs[obj]; cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }
+  if( r.species.count( obj ) ) { auto m = r.species[obj]; unpin_host( m->host->p ); cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
+  if( r.fields.count( obj )  ) { auto m = r.fields[obj]; unpin_host( m->host->f ); cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
+  if( r.interps.count( obj ) ) { auto m = r.interps[obj]; unpin_host( m->host->i ); cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
+  if( r.accs.count( obj )    ) { auto m = r.accs[obj]; unpin_host( m->host->a ); cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }
   if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
 }
 
@@ -275,7 +279,7 @@ void vpic_b200_finalize( void ) {
   for( auto & kv : r.accs    ) keys.push_back( kv.first );
   for( auto & kv : r.grids   ) keys.push_back( kv.first );
   for( auto k : keys ) vpic_b200_forget( (void *)k );
-  release_boundary_buffers(); release_sort_buffers(); release_parity_buffers(); comm_shutdown();
+  release_boundary_buffers(); release_sort_buffers(); release_parity_buffers(); comm_shutdown(); unpin_all();
   if( r.d_scratch ) cudaFree( r.d_scratch ); r.d_scratch = nullptr; r.scratch_bytes = 0;
   if( r.h_pinned ) cudaFreeHost( r.h_pinned ); r.h_pinned = nullptr; r.pinned_bytes = 0;
 }

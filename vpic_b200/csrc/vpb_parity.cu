@@ -276,8 +276,8 @@ void advance_p_parity( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, co
   exclusive_scan( cnt, off, nullptr, tiles, np );
   VPB_CHECK_LAUNCH(); r.launches++;
   int last[2];
-  VPB_CUDA( cudaMemcpyAsync( last+0, off+np-1, sizeof(int), cudaMemcpyDeviceToHost, r.stream ) );
-  VPB_CUDA( cudaMemcpyAsync( last+1, cnt+np-1, sizeof(int), cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( last+0, off+np-1, sizeof(int), r.stream );
+  d2h( last+1, cnt+np-1, sizeof(int), r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   const int nrec = last[0] + last[1];
   int   * rec_bin = (int *)need( B_bin, sizeof(int)*( (size_t)nrec+32 ) );
@@ -309,7 +309,7 @@ static void ordered_sum( double * host_out, const double * val, int n, int ncomp
   k_ordered_shares<<< div_up( ( P+1 )*ncomp, 32 ), 32, 0, r.stream >>>( share, val, n, ncomp, P );
   k_ordered_total<<< 1, 32, 0, r.stream >>>( share + ( P+1 )*ncomp, share, ncomp, P, scale );
   VPB_CHECK_LAUNCH(); r.launches += 2;
-  VPB_CUDA( cudaMemcpyAsync( host_out, share + ( P+1 )*ncomp, sizeof(double)*ncomp, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( host_out, share + ( P+1 )*ncomp, sizeof(double)*ncomp, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
 }
 

@@ -188,7 +188,7 @@ double energy_p( const vpb_species_t * sp, const vpb_interpolator_array_t * ia )
   k_sum_partials<<< 1, 32, 0, r.stream >>>( partial + nb, partial, nb, 1, 1.0 );
   VPB_CHECK_LAUNCH(); r.launches += 2;
   double local = 0;
-  VPB_CUDA( cudaMemcpyAsync( &local, partial + nb, sizeof(double), cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( &local, partial + nb, sizeof(double), r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( g_world_size>1 ) comm_allsum_d( &local, 1 );
   return local*( (double)hg->cvac*(double)hg->cvac );

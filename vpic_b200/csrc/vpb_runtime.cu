@@ -40,6 +40,33 @@ void ensure_init() {
   r.initialised = true;
 }
 
+// The reference allocates its arrays with posix_memalign (pageable).  Page-
+// locking them once lets every later cudaMemcpyAsync run at full PCIe rate and
+// overlap with kernels.  Arrays below 1 MB are not worth a registration.
+void pin_host( const void * ptr, size_t bytes ) {
+  Runtime & r = rt();
+  if( !ptr || bytes<( 1u<<20 ) ) return;
+  auto it = r.pinned_host.find( ptr );
+  if( it!=r.pinned_host.end() ) {
+    if( it->second>=bytes ) return;
+    cudaHostUnregister( const_cast<void *>( ptr ) ); r.pinned_host.erase( it );
+  }
+  if( cudaHostRegister( const_cast<void *>( ptr ), bytes, cudaHostRegisterDefault )==cudaSuccess ) r.pinned_host[ptr] = bytes;
+  else (void)cudaGetLastError();     // already registered by the host program, or not lockable: copies still work
+}
+void unpin_host( const void * ptr ) {
+  Runtime & r = rt();
+  auto it = r.pinned_host.find( ptr );
+  if( it==r.pinned_host.end() ) return;
+  if( cudaHostUnregister( const_cast<void *>( ptr ) )!=cudaSuccess ) (void)cudaGetLastError();
+  r.pinned_host.erase( it );
+}
+void unpin_all() {
+  Runtime & r = rt();
+  for( auto & kv : r.pinned_host ) if( cudaHostUnregister( const_cast<void *>( kv.first ) )!=cudaSuccess ) (void)cudaGetLastError();
+  r.pinned_host.clear();
+}
+
 void * scratch( size_t bytes ) {
   Runtime & r = rt();
   if( bytes>r.scratch_bytes ) {
@@ -211,10 +238,11 @@ void to_device( FieldMirror * m ) {
   if( !m->host->f ) { if( m->dev_valid ) return; VPB_ERROR( "field array has neither host nor device data" ); }
   const GridDev & d = m->grid->dev;
   if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv ) );
-  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyHostToDevice, r.stream ) );
+  pin_host( m->host->f, sizeof(vpb_field_t)*(size_t)d.nv );
+  h2d( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, r.stream );
   k_field_aos_to_soa<<< div_up(d.nv,256), 256, 0, r.stream >>>( (const vpb_field_t *)m->d_stage, m->d, m->d_mat, d.nv, d.nvp );
   VPB_CHECK_LAUNCH(); r.launches++;
-  m->dev_valid = true;
+  m->dev_valid = true; m->stage_has_ids = true;
 }
 
 void to_host( FieldMirror * m ) {
@@ -223,11 +251,16 @@ void to_host( FieldMirror * m ) {
   if( !m->host->f ) return;                         // device-only array
   const GridDev & d = m->grid->dev;
   if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv ) );
-  // keep the material ids of the host copy: stage starts from the host bytes
-  VPB_CUDA( cudaMemcpyAsync( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyHostToDevice, r.stream ) );
+  // keep the material ids of the host copy: the stage still holds the bytes of
+  // the last upload (only the 16 floats per voxel are rewritten below)
+  pin_host( m->host->f, sizeof(vpb_field_t)*(size_t)d.nv );
+  if( !m->stage_has_ids ) {
+    h2d( m->d_stage, m->host->f, sizeof(vpb_field_t)*(size_t)d.nv, r.stream );
+    m->stage_has_ids = true;
+  }
   k_field_soa_to_aos<<< div_up(d.nv,256), 256, 0, r.stream >>>( (vpb_field_t *)m->d_stage, m->d, d.nv, d.nvp );
   VPB_CHECK_LAUNCH(); r.launches++;
-  VPB_CUDA( cudaMemcpyAsync( m->host->f, m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv, cudaMemcpyDeviceToHost, r.stream ) );
+  d2h( m->host->f, m->d_stage, sizeof(vpb_field_t)*(size_t)d.nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
 }

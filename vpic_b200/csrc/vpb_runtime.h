@@ -88,6 +88,7 @@ struct FieldMirror {
   vpb_material_coefficient_t * d_mc = nullptr;
   int   n_mc = 0;
   float * d_stage = nullptr;       // AoS staging for host<->device conversion
+  bool stage_has_ids = false;      // d_stage holds the host's material-id bytes (kept across downloads)
   double * d_en = nullptr;         // 6 doubles + scratch for energy_f
   float * d_face = nullptr;        // packed face buffers for exchanges
   size_t face_floats = 0;
@@ -140,6 +141,8 @@ struct Runtime {
   void * d_scratch = nullptr; size_t scratch_bytes = 0;
   void * h_pinned = nullptr;  size_t pinned_bytes = 0;
   long long launches = 0;             // kernels launched (for bench's gpu_launches)
+  long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued by the entry points
+  std::unordered_map<const void *, size_t>          pinned_host;   // host arrays registered with cudaHostRegister
   std::unordered_map<const void *, GridMirror *>    grids;
   std::unordered_map<const void *, FieldMirror *>   fields;
   std::unordered_map<const void *, InterpMirror *>  interps;
@@ -149,6 +152,9 @@ struct Runtime {
 
 Runtime & rt();
 void ensure_init();
+void pin_host( const void * ptr, size_t bytes );   // page-lock a host array the host program owns (idempotent, best effort)
+void unpin_host( const void * ptr );
+void unpin_all();
 void * scratch( size_t bytes );        // grow-only device scratch
 void * pinned( size_t bytes );         // grow-only pinned host scratch
 
@@ -194,6 +200,14 @@ void release_boundary_buffers();
 void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
 void release_sort_buffers();
 __global__ void k_sum_partials( double * out, const double * partial, int nblock, int ncomp, double scale );
+
+// every host<->device copy of the library goes through these two (byte accounting for bench.py's e2e)
+inline void h2d( void * dst, const void * src, size_t bytes, cudaStream_t st ) {
+  VPB_CUDA( cudaMemcpyAsync( dst, src, bytes, cudaMemcpyHostToDevice, st ) ); rt().h2d_bytes += (long long)bytes;
+}
+inline void d2h( void * dst, const void * src, size_t bytes, cudaStream_t st ) {
+  VPB_CUDA( cudaMemcpyAsync( dst, src, bytes, cudaMemcpyDeviceToHost, st ) ); rt().d2h_bytes += (long long)bytes;
+}
 
 inline int div_up( long long a, long long b ) { return (int)( (a+b-1)/b ); }
 
