@@ -14,22 +14,34 @@ namespace vpb {
 // advance_b: 24 B read + 12 B written per cell = 36 B.
 // ---------------------------------------------------------------------------
 
+// Lattice point i (x fastest over the (nx+1)(ny+1)(nz+1) block) -> voxel.
+__device__ __forceinline__ int lattice_voxel( const GridDev & g, int i, int mx, int my, int & x, int & y, int & z ) {
+  x = i % mx; const int t = i / mx; y = t % my; z = t / my;
+  return (x+1) + g.sy*(y+1) + g.sz*(z+1);
+}
+
+// One thread per lattice point, blockIdx.y = z: one integer division per
+// thread, no grid-stride loop (tools/membench.cu: a flat grid streams 6R+3W
+// float planes at 6.5 TB/s, a persistent one at 6.0).  Out-of-range neighbours
+// are clamped instead of branched so all twelve loads issue together.
 __global__ void __launch_bounds__(256)
 k_advance_b( float * __restrict__ f, GridDev g, float px, float py, float pz ) {
-  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
-  const int n = mx*my*mz;
+  const int mx = g.nx+1, my = g.ny+1;
+  const int ixy = blockIdx.x*blockDim.x + threadIdx.x;
+  if( ixy>=mx*my ) return;
+  const int z = blockIdx.y, y = ixy / mx, x = ixy - y*mx;
+  const int w = (x+1) + g.sy*(y+1) + g.sz*(z+1);
   const size_t P = (size_t)g.nvp;
   const float * __restrict__ ex = f + F_EX*P, * __restrict__ ey = f + F_EY*P, * __restrict__ ez = f + F_EZ*P;
   float * __restrict__ cbx = f + F_CBX*P, * __restrict__ cby = f + F_CBY*P, * __restrict__ cbz = f + F_CBZ*P;
-  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
-    const int x = i % mx, t = i / mx, y = t % my, z = t / my;      // 0-based
-    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
-    const bool inx = x<g.nx, iny = y<g.ny, inz = z<g.nz;
-    const float ex0 = ex[v], ey0 = ey[v], ez0 = ez[v];
-    if( iny && inz ) cbx[v] -= ( py*( ez[v+g.sy]-ez0 ) - pz*( ey[v+g.sz]-ey0 ) );
-    if( inz && inx ) cby[v] -= ( pz*( ex[v+g.sz]-ex0 ) - px*( ez[v+1]   -ez0 ) );
-    if( inx && iny ) cbz[v] -= ( px*( ey[v+1]   -ey0 ) - py*( ex[v+g.sy]-ex0 ) );
-  }
+  const bool inx = x<g.nx, iny = y<g.ny, inz = z<g.nz;
+  const int wx = inx ? w+1 : w, wy = iny ? w+g.sy : w, wz = inz ? w+g.sz : w;
+  const float ex0 = ex[w], ey0 = ey[w], ez0 = ez[w];
+  const float ezy = ez[wy], eyz = ey[wz], exz = ex[wz], ezx = ez[wx], eyx = ey[wx], exy = ex[wy];
+  const float bx = cbx[w], by = cby[w], bz = cbz[w];
+  if( iny && inz ) cbx[w] = bx - ( py*( ezy-ez0 ) - pz*( eyz-ey0 ) );
+  if( inz && inx ) cby[w] = by - ( pz*( exz-ex0 ) - px*( ezx-ez0 ) );
+  if( inx && iny ) cbz[w] = bz - ( px*( eyx-ey0 ) - py*( exy-ex0 ) );
 }
 
 // advance_e, vacuum variant (one material): 48 B read + 24 B written per cell.
@@ -40,32 +52,34 @@ struct VacuumCoef {
 
 __global__ void __launch_bounds__(256)
 k_advance_e_vacuum( float * __restrict__ f, GridDev g, VacuumCoef c ) {
-  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
-  const int n = mx*my*mz;
+  const int mx = g.nx+1, my = g.ny+1;
+  const int ixy = blockIdx.x*blockDim.x + threadIdx.x;
+  if( ixy>=mx*my ) return;
+  const int z = blockIdx.y, y = ixy / mx, x = ixy - y*mx;
+  const int w = (x+1) + g.sy*(y+1) + g.sz*(z+1);
   const size_t P = (size_t)g.nvp;
   const float * __restrict__ cbx = f + F_CBX*P, * __restrict__ cby = f + F_CBY*P, * __restrict__ cbz = f + F_CBZ*P;
   const float * __restrict__ jfx = f + F_JFX*P, * __restrict__ jfy = f + F_JFY*P, * __restrict__ jfz = f + F_JFZ*P;
   float * __restrict__ ex = f + F_EX*P, * __restrict__ ey = f + F_EY*P, * __restrict__ ez = f + F_EZ*P;
   float * __restrict__ tx = f + F_TCAX*P, * __restrict__ ty = f + F_TCAY*P, * __restrict__ tz = f + F_TCAZ*P;
-  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
-    const int x = i % mx, t = i / mx, y = t % my, z = t / my;
-    const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
-    const float bx0 = cbx[v], by0 = cby[v], bz0 = cbz[v];
-    if( x<g.nx ) {
-      const float tca = ( c.py_muz*( bz0 - cbz[v-g.sy] ) - c.pz_muy*( by0 - cby[v-g.sz] ) ) - c.damp*tx[v];
-      tx[v] = tca;
-      ex[v] = c.decayx*ex[v] + c.drivex*( tca - c.cj*jfx[v] );
-    }
-    if( y<g.ny ) {
-      const float tca = ( c.pz_mux*( bx0 - cbx[v-g.sz] ) - c.px_muz*( bz0 - cbz[v-1] ) ) - c.damp*ty[v];
-      ty[v] = tca;
-      ey[v] = c.decayy*ey[v] + c.drivey*( tca - c.cj*jfy[v] );
-    }
-    if( z<g.nz ) {
-      const float tca = ( c.px_muy*( by0 - cby[v-1] ) - c.py_mux*( bx0 - cbx[v-g.sy] ) ) - c.damp*tz[v];
-      tz[v] = tca;
-      ez[v] = c.decayz*ez[v] + c.drivez*( tca - c.cj*jfz[v] );
-    }
+  // the -x,-y,-z neighbours always exist (ghost layer): all loads issue together
+  const float bx0 = cbx[w], by0 = cby[w], bz0 = cbz[w];
+  const float bzy = cbz[w-g.sy], byz = cby[w-g.sz], bxz = cbx[w-g.sz], bzx = cbz[w-1], byx = cby[w-1], bxy = cbx[w-g.sy];
+  const float e0 = ex[w], e1 = ey[w], e2 = ez[w], t0 = tx[w], t1 = ty[w], t2 = tz[w], j0 = jfx[w], j1 = jfy[w], j2 = jfz[w];
+  if( x<g.nx ) {
+    const float tca = ( c.py_muz*( bz0 - bzy ) - c.pz_muy*( by0 - byz ) ) - c.damp*t0;
+    tx[w] = tca;
+    ex[w] = c.decayx*e0 + c.drivex*( tca - c.cj*j0 );
+  }
+  if( y<g.ny ) {
+    const float tca = ( c.pz_mux*( bx0 - bxz ) - c.px_muz*( bz0 - bzx ) ) - c.damp*t1;
+    ty[w] = tca;
+    ey[w] = c.decayy*e1 + c.drivey*( tca - c.cj*j1 );
+  }
+  if( z<g.nz ) {
+    const float tca = ( c.px_muy*( by0 - byx ) - c.py_mux*( bx0 - bxy ) ) - c.damp*t2;
+    tz[w] = tca;
+    ez[w] = c.decayz*e2 + c.drivez*( tca - c.cj*j2 );
   }
 }
 
@@ -84,8 +98,11 @@ k_advance_e_material( float * __restrict__ f, const int16_t * __restrict__ mat,
   float * tx = f + F_TCAX*P, * ty = f + F_TCAY*P, * tz = f + F_TCAZ*P;
   const int16_t * emx = mat + 0*P, * emy = mat + 1*P, * emz = mat + 2*P;
   const int16_t * fmx = mat + 4*P, * fmy = mat + 5*P, * fmz = mat + 6*P;
-  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
-    const int x = i % mx, t = i / mx, y = t % my, z = t / my;
+  {
+    const int ixy = blockIdx.x*blockDim.x + threadIdx.x;
+    if( ixy>=mx*my ) return;
+    const int z = blockIdx.y, y = ixy / mx, x = ixy - y*mx;
+    (void)n; (void)mz;
     const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
     const int vx = v-1, vy = v-g.sy, vz = v-g.sz;
     if( x<g.nx ) {
@@ -362,10 +379,6 @@ static void fill_ghost_tang_b( FieldMirror * m ) {
 
 using namespace vpb;
 
-static int stencil_grid( long long n ) {
-  long long b = ( n + 255 )/256, cap = (long long)rt().sm_count*16;
-  return (int)( b>cap ? cap : ( b<1 ? 1 : b ) );
-}
 
 extern "C" {
 
@@ -379,7 +392,7 @@ void vpic_b200_advance_b( vpb_field_array_t * fa, float frac ) {
   const float px = (g.nx>1) ? frac*hg->cvac*hg->dt*hg->rdx : 0;
   const float py = (g.ny>1) ? frac*hg->cvac*hg->dt*hg->rdy : 0;
   const float pz = (g.nz>1) ? frac*hg->cvac*hg->dt*hg->rdz : 0;
-  k_advance_b<<< stencil_grid( (long long)(g.nx+1)*(g.ny+1)*(g.nz+1) ), 256, 0, r.stream >>>( m->d, g, px, py, pz );
+  k_advance_b<<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( m->d, g, px, py, pz );
   VPB_CHECK_LAUNCH(); r.launches++;
   const int n3[3] = { g.nx, g.ny, g.nz };
   for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
@@ -405,7 +418,6 @@ void vpic_b200_advance_e( vpb_field_array_t * fa, float frac ) {
   const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
   const float damp = prm->damp;
   fill_ghost_tang_b( m );
-  const long long n = (long long)(g.nx+1)*(g.ny+1)*(g.nz+1);
   if( m->n_mc==1 ) {
     const vpb_material_coefficient_t * mc = prm->mc;
     VacuumCoef c;
@@ -418,12 +430,12 @@ void vpic_b200_advance_e( vpb_field_array_t * fa, float frac ) {
     c.pz_muy = ((g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0)*mc->rmuy;
     c.pz_mux = ((g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0)*mc->rmux;
     c.damp = damp; c.cj = hg->dt/hg->eps0;
-    k_advance_e_vacuum<<< stencil_grid( n ), 256, 0, r.stream >>>( m->d, g, c );
+    k_advance_e_vacuum<<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( m->d, g, c );
   } else {
     const float px = (g.nx>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdx : 0;
     const float py = (g.ny>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdy : 0;
     const float pz = (g.nz>1) ? (1+damp)*hg->cvac*hg->dt*hg->rdz : 0;
-    k_advance_e_material<<< stencil_grid( n ), 256, 0, r.stream >>>( m->d, m->d_mat, m->d_mc, g, px, py, pz, damp, hg->dt/hg->eps0 );
+    k_advance_e_material<<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( m->d, m->d_mat, m->d_mc, g, px, py, pz, damp, hg->dt/hg->eps0 );
   }
   VPB_CHECK_LAUNCH(); r.launches++;
   // local_adjust_tang_e (local.c:224-264)

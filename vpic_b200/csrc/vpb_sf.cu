@@ -14,9 +14,11 @@ namespace vpb {
 // are unit-stride and the +y/+z neighbours come out of L1/L2.
 __global__ void __launch_bounds__(256)
 k_load_interpolator( float * __restrict__ ip, const float * __restrict__ f, GridDev g ) {
-  const int ncell = g.nx*g.ny*g.nz;
-  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<ncell; i += gridDim.x*blockDim.x ) {
-    const int x = i % g.nx, t = i / g.nx, y = t % g.ny, z = t / g.ny;
+  // flat grid, blockIdx.y = z (see k_advance_b): blocks walk the planes in order
+  {
+    const int ixy = blockIdx.x*blockDim.x + threadIdx.x;
+    if( ixy>=g.nx*g.ny ) return;
+    const int z = blockIdx.y, y = ixy / g.nx, x = ixy - y*g.nx;
     const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
     const size_t P = (size_t)g.nvp;
     const float * ex = f + F_EX*P, * ey = f + F_EY*P, * ez = f + F_EZ*P;
@@ -53,12 +55,13 @@ k_load_interpolator( float * __restrict__ ip, const float * __restrict__ f, Grid
 template<bool CLEAR_FIRST>
 __global__ void __launch_bounds__(256)
 k_unload_accumulator( float * __restrict__ f, const float * __restrict__ a, GridDev g, float cx, float cy, float cz ) {
-  const int mx = g.nx+1, my = g.ny+1, mz = g.nz+1;
-  const int n = mx*my*mz;
+  const int mx = g.nx+1, my = g.ny+1;
   const size_t P = (size_t)g.nvp;
   float * jfx = f + F_JFX*P, * jfy = f + F_JFY*P, * jfz = f + F_JFZ*P;
-  for( int i = blockIdx.x*blockDim.x + threadIdx.x; i<n; i += gridDim.x*blockDim.x ) {
-    const int x = i % mx, t = i / mx, y = t % my, z = t / my;
+  {
+    const int ixy = blockIdx.x*blockDim.x + threadIdx.x;
+    if( ixy>=mx*my ) return;
+    const int z = blockIdx.y, y = ixy / mx, x = ixy - y*mx;
     const int v = (x+1) + g.sy*(y+1) + g.sz*(z+1);
     const float * a0  = a + (size_t)v*ACC_STRIDE;
     const float * ax  = a + (size_t)(v-1)*ACC_STRIDE;
@@ -75,13 +78,6 @@ k_unload_accumulator( float * __restrict__ f, const float * __restrict__ a, Grid
   }
 }
 
-static int grid_for( long long n, int threads ) {
-  long long b = ( n + threads - 1 )/threads;
-  long long cap = (long long)rt().sm_count*16;
-  if( b>cap ) b = cap;
-  if( b<1 ) b = 1;
-  return (int)b;
-}
 
 } // namespace vpb
 
@@ -96,7 +92,7 @@ void load_interpolator_array( vpb_interpolator_array_t * ia, const vpb_field_arr
   FieldMirror  * mf = mirror( const_cast<vpb_field_array_t *>( fa ) );
   to_device( mf );
   const GridDev & g = mi->grid->dev;
-  k_load_interpolator<<< grid_for( (long long)g.nx*g.ny*g.nz, 256 ), 256, 0, r.stream >>>( mi->d, mf->d, g );
+  k_load_interpolator<<< dim3( div_up( (long long)g.nx*g.ny, 256 ), g.nz ), 256, 0, r.stream >>>( mi->d, mf->d, g );
   VPB_CHECK_LAUNCH(); r.launches++;
   finish_write( mi );
 }
@@ -146,8 +142,7 @@ void unload_accumulator_array( vpb_field_array_t * fa, const vpb_accumulator_arr
   const float cy = 0.25 * hg->rdz * hg->rdx / hg->dt;
   const float cz = 0.25 * hg->rdx * hg->rdy / hg->dt;
   const GridDev & g = mf->grid->dev;
-  long long n = (long long)(g.nx+1)*(g.ny+1)*(g.nz+1);
-  k_unload_accumulator<false><<< grid_for( n, 256 ), 256, 0, r.stream >>>( mf->d, ma->d, g, cx, cy, cz );
+  k_unload_accumulator<false><<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( mf->d, ma->d, g, cx, cy, cz );
   VPB_CHECK_LAUNCH(); r.launches++;
   finish_write( mf );
 }
