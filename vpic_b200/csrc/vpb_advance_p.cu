@@ -42,7 +42,7 @@ constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 struct __align__(128) WarpTile {
   float4 tile[2*AP_TILE];               // the particles, array order (8 KB)
   // queue of particles that left their voxel (structure of arrays)
-  int   q_idx[AP_QCAP];                 // index inside the tile
+  int   q_idx[AP_QCAP];                 // particle index relative to the launch's first particle
   float q_dx[AP_QCAP], q_dy[AP_QCAP], q_dz[AP_QCAP];
   int   q_i[AP_QCAP];
   float q_dispx[AP_QCAP], q_dispy[AP_QCAP], q_dispz[AP_QCAP];
@@ -53,15 +53,18 @@ struct __align__(128) WarpTile {
 __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_t)__cvta_generic_to_shared( p ); }
 
 // Run move_p (move_p.cc:216-353) on up to 32 queued particles, one per lane.
-// The queue is emptied before its tile is written back, so every entry is
-// finished in the shared-memory copy of the tile.
-__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane, long long idx0,
+// Entries of the tile that is still in shared memory are finished there;
+// entries carried over from tiles already written back are finished in global
+// memory (the caller has waited for those bulk stores to complete).
+__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane,
+                                                vpb_particle_t * __restrict__ p, int idx_base, long long t0, int cnt,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
                                                 int max_nm, int * __restrict__ counters, const GridDev & g ) {
   if( lane>=n ) return;
   const int e = base + lane;
-  const int loc = S.q_idx[e];
-  float4 * slot = &S.tile[ 2*loc ];
+  const int rel = S.q_idx[e];
+  const bool in_tile = rel>=t0 && rel<t0+cnt;
+  float4 * slot = in_tile ? &S.tile[ 2*(int)( rel-t0 ) ] : reinterpret_cast<float4 *>( p + rel );
   const float4 r1 = slot[1];
   MoveState ms;
   ms.dx = S.q_dx[e]; ms.dy = S.q_dy[e]; ms.dz = S.q_dz[e]; ms.i = S.q_i[e];
@@ -79,10 +82,12 @@ __device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, i
   slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );       // reflections flip a momentum component
   if( status==2 ) {
     const int k = atomicAdd( counters+0, 1 );
-    if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( (int)( idx0 + loc ) ) );
+    if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx_base + rel ) );
     else atomicAdd( counters+1, 1 );
   }
 }
+
+constexpr int AP_DRAIN_MIN = 24;        // fewer crossers than this wait for the next tile's
 
 // p points at the first particle of the range this launch owns (np particles,
 // ntile tiles); idx_base is that particle's index in sp->p (mover indices).
@@ -107,6 +112,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
 
   uint32_t phase = 0;
   int qn = 0;                                  // queued crossers (warp uniform)
+  int n_carry = 0;                             // of which: from tiles whose bulk store may still be in flight
   int cur = -1;                                // voxel whose current sums this lane holds in run[]
   int fvox = -1;                               // voxel whose coefficients this lane holds in f
   float run[12];
@@ -193,7 +199,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       if( m ) {
         if( cross ) {
           const int e = qn + __popc( m & ( ( 1u<<lane )-1u ) );
-          S.q_idx[e] = loc;
+          S.q_idx[e] = (int)t0 + loc;
           S.q_dx[e] = cdx; S.q_dy[e] = cdy; S.q_dz[e] = cdz; S.q_i[e] = ci;
           S.q_dispx[e] = cux; S.q_dispy[e] = cuy; S.q_dispz[e] = cuz; S.q_q[e] = cq;
         }
@@ -201,19 +207,32 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         __syncwarp();
         if( qn>=32 ) {
           qn -= 32;
-          drain_crossers( S, qn, 32, lane, idx_base + t0, acc, pm, max_nm, counters, g );
+          if( qn<n_carry ) {       // this batch reaches entries of tiles already written back: their stores must have landed
+            if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
+            __syncwarp();
+            n_carry = qn;
+          }
+          drain_crossers( S, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g );
           __syncwarp();
         }
       }
     }
 
-    // finish the remaining crossers of this tile while it is still on chip
-    while( qn>0 ) {
-      const int n = qn<32 ? qn : 32;
-      qn -= n;
-      drain_crossers( S, qn, n, lane, idx_base + t0, acc, pm, max_nm, counters, g );
-      __syncwarp();
+    // finish the queued crossers while the tile is still on chip -- unless there are only a few
+    if( qn>=AP_DRAIN_MIN ) {
+      if( n_carry>0 ) {
+        if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
+        __syncwarp();
+        n_carry = 0;
+      }
+      while( qn>0 ) {
+        const int n = qn<32 ? qn : 32;
+        qn -= n;
+        drain_crossers( S, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g );
+        __syncwarp();
+      }
     }
+    n_carry = qn;              // whatever is left rides along; its tile is written back now
     // write the tile back: generic-proxy writes -> async-proxy bulk store
     asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
     __syncwarp();
@@ -226,6 +245,11 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     __syncwarp();
   }
 
+  if( qn>0 ) {                 // all tiles are stored: finish the stragglers in global memory
+    if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
+    __syncwarp();
+    drain_crossers( S, 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g );
+  }
   if( cur>=0 ) commit_currents( acc, cur, run );
 }
 
