@@ -41,12 +41,9 @@ constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 
 struct __align__(128) WarpTile {
   float4 tile[2*AP_TILE];               // the particles, array order (8 KB)
-  // queue of particles that left their voxel (structure of arrays)
-  int   q_idx[AP_QCAP];                 // particle index relative to the launch's first particle
-  float q_dx[AP_QCAP], q_dy[AP_QCAP], q_dz[AP_QCAP];
-  int   q_i[AP_QCAP];
-  float q_dispx[AP_QCAP], q_dispy[AP_QCAP], q_dispz[AP_QCAP];
-  float q_q[AP_QCAP];
+  // queue of particles that left their voxel: remaining displacement + index
+  // (position, voxel, momentum and weight are still in the particle's slot)
+  float4 q[AP_QCAP];                    // dispx, dispy, dispz, index relative to the launch's first particle
   unsigned long long bar;               // mbarrier of the tile load
 };
 
@@ -59,18 +56,19 @@ __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_
 __device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane,
                                                 vpb_particle_t * __restrict__ p, int idx_base, long long t0, int cnt,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
-                                                int max_nm, int * __restrict__ counters, const GridDev & g ) {
+                                                int max_nm, int * __restrict__ counters, const GridDev & g, float qsp ) {
   if( lane>=n ) return;
   const int e = base + lane;
-  const int rel = S.q_idx[e];
+  const float4 qe = S.q[e];
+  const int rel = __float_as_int( qe.w );
   const bool in_tile = rel>=t0 && rel<t0+cnt;
   float4 * slot = in_tile ? &S.tile[ 2*(int)( rel-t0 ) ] : reinterpret_cast<float4 *>( p + rel );
-  const float4 r1 = slot[1];
+  const float4 r0 = slot[0], r1 = slot[1];
   MoveState ms;
-  ms.dx = S.q_dx[e]; ms.dy = S.q_dy[e]; ms.dz = S.q_dz[e]; ms.i = S.q_i[e];
+  ms.dx = r0.x; ms.dy = r0.y; ms.dz = r0.z; ms.i = __float_as_int( r0.w );
   ms.ux = r1.x; ms.uy = r1.y; ms.uz = r1.z;
-  ms.dispx = S.q_dispx[e]; ms.dispy = S.q_dispy[e]; ms.dispz = S.q_dispz[e];
-  const float q = S.q_q[e];
+  ms.dispx = qe.x; ms.dispy = qe.y; ms.dispz = qe.z;
+  const float q = r1.w*qsp;
   float j[12];
   int status;
   do {
@@ -150,7 +148,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       // quarter warp spread over the banks
       const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
       bool cross = false;
-      float cdx = 0, cdy = 0, cdz = 0, cux = 0, cuy = 0, cuz = 0, cq = 0; int ci = 0;
+      float cux = 0, cuy = 0, cuz = 0;
       if( loc<cnt ) {
         const float4 r0 = S.tile[2*loc], r1 = S.tile[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
@@ -192,16 +190,14 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
           } else commit_currents( acc, ii, j );
         } else {
           cross = true;
-          cdx = dx; cdy = dy; cdz = dz; ci = ii; cux = ux; cuy = uy; cuz = uz; cq = q;
+          cux = ux; cuy = uy; cuz = uz;
         }
       }
       const unsigned m = __ballot_sync( 0xffffffffu, cross );
       if( m ) {
         if( cross ) {
           const int e = qn + __popc( m & ( ( 1u<<lane )-1u ) );
-          S.q_idx[e] = (int)t0 + loc;
-          S.q_dx[e] = cdx; S.q_dy[e] = cdy; S.q_dz[e] = cdz; S.q_i[e] = ci;
-          S.q_dispx[e] = cux; S.q_dispy[e] = cuy; S.q_dispz[e] = cuz; S.q_q[e] = cq;
+          S.q[e] = make_float4( cux, cuy, cuz, __int_as_float( (int)t0 + loc ) );
         }
         qn += __popc( m );
         __syncwarp();
@@ -212,7 +208,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             __syncwarp();
             n_carry = qn;
           }
-          drain_crossers( S, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g );
+          drain_crossers( S, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
           __syncwarp();
         }
       }
@@ -228,7 +224,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       while( qn>0 ) {
         const int n = qn<32 ? qn : 32;
         qn -= n;
-        drain_crossers( S, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g );
+        drain_crossers( S, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
         __syncwarp();
       }
     }
@@ -248,7 +244,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   if( qn>0 ) {                 // all tiles are stored: finish the stragglers in global memory
     if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
     __syncwarp();
-    drain_crossers( S, 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g );
+    drain_crossers( S, 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g, c.qsp );
   }
   if( cur>=0 ) commit_currents( acc, cur, run );
 }
