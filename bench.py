@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", default="512x256x256", help="cells per GPU")
     ap.add_argument("--ppc", type=int, default=32, help="particles per cell per species")
-    ap.add_argument("--sort-interval", type=int, default=4)
+    ap.add_argument("--sort-interval", type=int, default=8)
     ap.add_argument("--e2e-cells", default="256x128x128")
     ap.add_argument("--cpu-cells", default="64x64x32")
     ap.add_argument("--no-cpu", action="store_true")
@@ -182,14 +182,17 @@ def run_b200(args):
     np_total = sum(sim.sp_struct(sp).np for sp, _, _ in sps)
     tm = EventTimer(torch, L.vpic_b200_stream(), local)
     be.advance_p = tm.wrap(be.advance_p)
+    tm_sort = EventTimer(torch, L.vpic_b200_stream(), local)
+    be.sort_p = tm_sort.wrap(be.sort_p)
 
     for _ in range(args.warmup):
         sim.advance()
-    tm.total_ms()
+    tm.total_ms(); tm_sort.total_ms()
     sampler = ClockSampler(local); sampler.start()
     ms, launches = timed_steps(torch, sim, L, stream, args.steps, barrier)
     sampler.stop_flag = True; sampler.join(timeout=2)
     ap_ms, ap_calls = tm.total_ms()
+    sort_ms, sort_calls = tm_sort.total_ms()
     if dist is not None:
         t = torch.tensor([ms, ap_ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms, ap_ms = t.tolist()
     pushes = np_total * world * args.steps
@@ -212,7 +215,10 @@ def run_b200(args):
                       "particles_per_gpu": np_total, "l2": "inputs (particles, fields) far larger than the 126 MB L2",
                       "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, slab decomposition ({world},1,1): ghost-B / jf face exchange and "
                                                                           f"particle migration over NCCL every step"},
-           "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary()}
+           "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary(),
+           "sort_p": {"ms_per_call": sort_ms / max(sort_calls, 1), "calls": sort_calls, "share_of_step": round(sort_ms / ms, 4),
+                      "GB/s": (np_total / 2 * 68.0 / (sort_ms / max(sort_calls, 1) * 1e-3) / 1e9) if sort_calls else None,
+                      "bytes_per_particle": 68.0}}
     free_sim(L, sim)
 
     if rank == 0 and not args.no_yee:

@@ -129,10 +129,49 @@ __device__ __forceinline__ void copy_particle( vpb_particle_t * __restrict__ out
 // Fix-up and gather fused: the warp that owns voxel v puts the particle
 // indices of its segment in ascending order (= original array order: that is
 // what makes the sort stable) and copies the particles to their final places.
-// Segments of <= 32*FIX_E indices are ranked in registers by counting
-// (rank = number of smaller indices; broadcast by shuffle), larger ones fall
-// back to the bitonic sorts.
+// Segments of <= 32*FIX_E indices sort in registers (a bitonic network of 32,
+// 64 or 128 elements, chosen per segment), larger ones fall back to the
+// bitonic sorts in shared or global memory.
 constexpr int FIX_E = 4;
+
+// Bitonic sort of 32*E ints held E per lane (element index 32k+lane): strides
+// of 32 and up exchange registers of one lane, shorter strides use shuffles.
+template<int E> __device__ __forceinline__ void warp_bitonic_regs( int (&x)[E], int lane ) {
+# pragma unroll
+  for( int sz=2; sz<=32*E; sz<<=1 ) {
+#   pragma unroll
+    for( int j=sz>>1; j>0; j>>=1 ) {
+      if( j>=32 ) {
+        const int dk = j>>5;
+#       pragma unroll
+        for( int k=0; k<E; k++ ) if( ( k & dk )==0 ) {
+          const bool up = ( ( 32*k ) & sz )==0;
+          const int lo = min( x[k], x[k|dk] ), hi = max( x[k], x[k|dk] );
+          x[k] = up ? lo : hi; x[k|dk] = up ? hi : lo;
+        }
+      } else {
+        const bool lower = ( lane & j )==0;
+#       pragma unroll
+        for( int k=0; k<E; k++ ) {
+          const bool up = ( ( 32*k+lane ) & sz )==0;
+          const int y = __shfl_xor_sync( 0xffffffffu, x[k], j );
+          x[k] = ( lower==up ) ? min( x[k], y ) : max( x[k], y );
+        }
+      }
+    }
+  }
+}
+
+template<int E> __device__ __forceinline__ void
+fix_gather_regs( const int * __restrict__ perm, int b, int n, int lane,
+                 const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
+  int x[E];
+# pragma unroll
+  for( int k=0; k<E; k++ ) x[k] = 32*k+lane<n ? perm[b+32*k+lane] : 0x7fffffff;
+  warp_bitonic_regs<E>( x, lane );
+# pragma unroll
+  for( int k=0; k<E; k++ ) if( 32*k+lane<n ) copy_particle( out, b+32*k+lane, in, x[k] );
+}
 
 __global__ void __launch_bounds__(32*FIX_WARPS)
 k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch,
@@ -143,25 +182,11 @@ k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __r
   if( v>=nv ) return;
   const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
   if( n<=0 ) return;
-  if( n<=32*FIX_E ) {
-    int x[FIX_E], rank[FIX_E];
-#   pragma unroll
-    for( int k=0; k<FIX_E; k++ ) { x[k] = 32*k+lane<n ? perm[b+32*k+lane] : 0x7fffffff; rank[k] = 0; }
-#   pragma unroll
-    for( int k=0; k<FIX_E; k++ ) {
-      if( 32*k<n ) {
-        const int m = n-32*k<32 ? n-32*k : 32;
-        for( int l=0; l<m; l++ ) {
-          const int y = __shfl_sync( 0xffffffffu, x[k], l );
-#         pragma unroll
-          for( int q=0; q<FIX_E; q++ ) rank[q] += ( y<x[q] ) ? 1 : 0;
-        }
-      }
-    }
-#   pragma unroll
-    for( int k=0; k<FIX_E; k++ ) if( 32*k+lane<n ) copy_particle( out, b+rank[k], in, x[k] );
-    return;
-  }
+  // Segments up to 32*FIX_E indices sort in registers, with a network sized for
+  // the segment (ne is warp uniform); lane l of slot k then holds rank 32k+l.
+  if( n<=32 )       { fix_gather_regs<1>( perm, b, n, lane, in, out ); return; }
+  if( n<=64 )       { fix_gather_regs<2>( perm, b, n, lane, in, out ); return; }
+  if( n<=32*FIX_E ) { fix_gather_regs<FIX_E>( perm, b, n, lane, in, out ); return; }
   int n2 = 64; while( n2<n ) n2 <<= 1;
   int * a;
   if( n2<=FIX_SMEM ) a = s[w];

@@ -4,7 +4,9 @@
 
 namespace vpb {
 
-constexpr int FIX_SMEM = 2048, FIX_WARPS = 4;
+// FIX_SMEM ints of shared memory per warp for segments too long for registers;
+// kept small so that 16 blocks fit on an SM (longer segments sort in global memory)
+constexpr int FIX_SMEM = 512, FIX_WARPS = 4;
 
 __device__ __forceinline__ void bitonic_mem( int * a, int n2, int lane ) {   // n2 power of two, padded with INT_MAX
   for( int k=2; k<=n2; k<<=1 ) for( int j=k>>1; j>0; j>>=1 ) {
