@@ -251,3 +251,28 @@ def test_parity_mode_free_running_steps_bit_exact(parity_mode, case):
     for a, b in zip(so.species, sg.species):
         assert same_bits(sg.particles(b), so.particles(a))
     assert sg.energies() == so.energies()
+
+
+def test_resident_absorbing_boundary_p_bit_exact(parity_mode):
+    """boundary_p with the particle arrays resident on the device (no sparse
+    host transfers): 8 free-running steps in an absorbing box, PARITY deposit,
+    must leave the reference's particles bit for bit."""
+    L = load_b200()
+    so, sg = pair(parity_mode, sort_interval=3, vth=0.3, max_nm=2000, **CASES[5])
+    for s in (so, sg):
+        s.initialize()
+    n0 = [so.sp_struct(a).np for a in so.species]
+    L.vpic_b200_set_coherence(1)
+    try:
+        for step in range(8):
+            so.advance(); sg.advance()
+        for obj in [sg.fa, sg.ia, sg.aa] + sg.species:
+            L.vpic_b200_sync_to_host(obj)
+    finally:
+        L.vpic_b200_set_coherence(0)
+    for a, b, n in zip(so.species, sg.species, n0):
+        assert so.sp_struct(a).np == sg.sp_struct(b).np < n
+        assert same_bits(sg.particles(b), so.particles(a))
+    for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "jfx", "jfy", "jfz"):
+        assert same_bits(sg.fields()[k], so.fields()[k]), k
+    assert close(sg.fields()["rhob"], so.fields()["rhob"], 5e-5)     # atomics: order of the absorbed charges is free

@@ -216,6 +216,25 @@ k_bnd_inject( BndInject a, float * __restrict__ acc, GridDev g ) {
   if( threadIdx.x<BND_MAX_SP ) a.counters[threadIdx.x] = s_base[threadIdx.x];
 }
 
+// STRICT coherence, sparse transfers: rows of the particle array named by an
+// index list, device <-> a compact staging buffer.
+__global__ void __launch_bounds__(256)
+k_rows_scatter( vpb_particle_t * __restrict__ p, const int * __restrict__ idx, const vpb_particle_t * __restrict__ rows, int n ) {
+  const int k = blockIdx.x*blockDim.x + threadIdx.x;
+  if( k>=n ) return;
+  const float4 * s = reinterpret_cast<const float4 *>( rows + k );
+  float4 * d = reinterpret_cast<float4 *>( p + idx[k] );
+  d[0] = s[0]; d[1] = s[1];
+}
+__global__ void __launch_bounds__(256)
+k_rows_gather( vpb_particle_t * __restrict__ rows, const int * __restrict__ idx, const vpb_particle_t * __restrict__ p, int n ) {
+  const int k = blockIdx.x*blockDim.x + threadIdx.x;
+  if( k>=n ) return;
+  const float4 * s = reinterpret_cast<const float4 *>( p + idx[k] );
+  float4 * d = reinterpret_cast<float4 *>( rows + k );
+  d[0] = s[0]; d[1] = s[1];
+}
+
 } // namespace vpb
 
 using namespace vpb;
@@ -226,6 +245,8 @@ struct BndBuffers {
   vpb_particle_injector_t * send[6] = {}, * recv[6] = {};
   size_t send_cap[6] = {}, recv_cap[6] = {};
   int * d_int = nullptr;     // [0..6) face_count  [8..14) recv counts  [16] n_unknown  [32..32+4*MAX_SP] inject counters
+  // sparse STRICT transfers: page-locked host staging and its device twin (rows, then indices)
+  char * h_rows = nullptr, * d_rows = nullptr; size_t rows_cap = 0;
 } B;
 
 void grow( vpb_particle_injector_t ** buf, size_t * cap, size_t want ) {
@@ -263,13 +284,118 @@ namespace vpb {
 void release_boundary_buffers() {
   for( int f=0; f<6; f++ ) { cudaFree( B.send[f] ); cudaFree( B.recv[f] ); B.send[f] = B.recv[f] = nullptr; B.send_cap[f] = B.recv_cap[f] = 0; }
   cudaFree( B.d_int ); B.d_int = nullptr;
+  cudaFree( B.d_rows ); if( B.h_rows ) cudaFreeHost( B.h_rows ); B.d_rows = B.h_rows = nullptr; B.rows_cap = 0;
 }
+}
+
+// ---- STRICT coherence with host arrays: sparse transfers ---------------------
+// boundary_p reads the particles its movers name and the tail of the array
+// that back-fills their holes, and writes those holes plus what it appends.
+// With the particle arrays living in host memory (STRICT) only those rows
+// travel; the rest of the device copy is left stale and marked invalid.
+struct SparseSpecies { SpeciesMirror * m; int np0, nm0; size_t off; };
+
+static void sparse_reserve( size_t rows ) {
+  const size_t bytes = rows*( sizeof(vpb_particle_t) + sizeof(int) ) + 256;
+  if( bytes<=B.rows_cap ) return;
+  VPB_CUDA( cudaStreamSynchronize( rt().stream ) );
+  if( B.h_rows ) cudaFreeHost( B.h_rows ); cudaFree( B.d_rows );
+  B.rows_cap = bytes + bytes/2;
+  VPB_CUDA( cudaMallocHost( &B.h_rows, B.rows_cap ) );
+  VPB_CUDA( cudaMalloc( &B.d_rows, B.rows_cap ) );
+}
+
+// rows of all species first, then their index lists
+static inline vpb_particle_t * rows_at( char * base, size_t off ) { return reinterpret_cast<vpb_particle_t *>( base ) + off; }
+static inline int * idx_at( char * base, size_t total, size_t off ) { return reinterpret_cast<int *>( base + total*sizeof(vpb_particle_t) ) + off; }
+
+static void sparse_upload( std::vector<SparseSpecies> & ss ) {
+  Runtime & r = rt();
+  size_t total = 0;
+  for( SparseSpecies & s : ss ) {
+    SpeciesMirror * m = s.m; const vpb_species_t * sp = m->host;
+    m->np = sp->np; m->nm = sp->nm; s.np0 = sp->np; s.nm0 = sp->nm; s.off = total; total += (size_t)sp->nm;
+    if( m->nm>(int)m->cap_pm ) VPB_ERROR( "species \"%s\": nm=%d exceeds max_nm=%zu", sp->name, m->nm, m->cap_pm );
+    if( m->nm>0 && !sp->pm ) VPB_ERROR( "species \"%s\" has movers but no mover array", sp->name );
+  }
+  sparse_reserve( total );
+  for( SparseSpecies & s : ss ) {
+    SpeciesMirror * m = s.m; const vpb_species_t * sp = m->host;
+    vpb_particle_t * hr = rows_at( B.h_rows, s.off ); int * hi = idx_at( B.h_rows, total, s.off );
+    bool sorted = true;
+    for( int k=0; k<s.nm0; k++ ) {
+      const int i = sp->pm[k].i;
+      if( i<0 || i>=s.np0 ) VPB_ERROR( "species \"%s\": mover %d names particle %d of %d", sp->name, k, i, s.np0 );
+      if( k && i<=sp->pm[k-1].i ) sorted = false;
+      hi[k] = i; hr[k] = sp->p[i];
+    }
+    m->movers_sorted = sorted;
+  }
+  if( total ) {
+    h2d( B.d_rows, B.h_rows, total*sizeof(vpb_particle_t), r.stream );
+    h2d( idx_at( B.d_rows, total, 0 ), idx_at( B.h_rows, total, 0 ), total*sizeof(int), r.stream );
+  }
+  for( SparseSpecies & s : ss ) {
+    SpeciesMirror * m = s.m; const vpb_species_t * sp = m->host;
+    if( s.nm0>0 ) {
+      h2d( m->d_pm, sp->pm, sizeof(vpb_particle_mover_t)*(size_t)s.nm0, r.stream );
+      k_rows_scatter<<< div_up( s.nm0, 256 ), 256, 0, r.stream >>>( m->d_p, idx_at( B.d_rows, total, s.off ), rows_at( B.d_rows, s.off ), s.nm0 );
+      r.launches++;
+      const int t0 = s.np0-s.nm0>0 ? s.np0-s.nm0 : 0;         // the tail that back-fills the holes
+      pin_host( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
+      h2d( m->d_p + t0, sp->p + t0, sizeof(vpb_particle_t)*(size_t)( s.np0-t0 ), r.stream );
+    }
+    m->dev_valid = true; m->partition_dev_valid = false;
+  }
+  VPB_CHECK_LAUNCH();
+}
+
+static void sparse_download( std::vector<SparseSpecies> & ss ) {
+  Runtime & r = rt();
+  size_t total = 0;
+  for( SparseSpecies & s : ss ) total += (size_t)s.nm0;
+  for( SparseSpecies & s : ss ) {
+    SpeciesMirror * m = s.m; vpb_species_t * sp = m->host;
+    if( s.nm0>0 ) {           // the holes (the index list is still in the device staging buffer)
+      k_rows_gather<<< div_up( s.nm0, 256 ), 256, 0, r.stream >>>( rows_at( B.d_rows, s.off ), idx_at( B.d_rows, total, s.off ), m->d_p, s.nm0 );
+      r.launches++;
+    }
+    const int kept = s.np0 - s.nm0;                            // particles appended by the injection
+    if( m->np>kept ) d2h( sp->p + kept, m->d_p + kept, sizeof(vpb_particle_t)*(size_t)( m->np-kept ), r.stream );
+  }
+  VPB_CHECK_LAUNCH();
+  if( total ) d2h( B.h_rows, B.d_rows, total*sizeof(vpb_particle_t), r.stream );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  for( SparseSpecies & s : ss ) {
+    SpeciesMirror * m = s.m; vpb_species_t * sp = m->host;
+    const vpb_particle_t * hr = rows_at( B.h_rows, s.off ); const int * hi = idx_at( B.h_rows, total, s.off );
+    const int kept = s.np0 - s.nm0;
+    for( int k=0; k<s.nm0; k++ ) if( hi[k]<kept ) sp->p[hi[k]] = hr[k];
+    sp->np = m->np;
+    // only the rows above are current on the device: the host copy is the valid one
+    m->host_valid = true; m->dev_valid = false; m->partition_dev_valid = false;
+  }
+}
+
+// Count phase of the migration (boundary_p.cc:285-300): per axis, our two
+// send counts (B.d_int[face]) against the neighbours' (B.d_int[8+face]).
+static void exchange_counts( const GridMirror * gm, int * n_recv ) {
+  Runtime & r = rt();
+  for( int X=0; X<3; X++ ) {
+    const int lo = X, hi = X+3;
+    const int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
+    if( rank_lo<0 && rank_hi<0 ) continue;
+    comm_sendrecv( rank_lo, rank_hi, B.d_int+lo, 4, B.d_int+hi, 4, B.d_int+8+lo, 4, B.d_int+8+hi, 4 );
+  }
+  d2h( n_recv, B.d_int+8, sizeof(int)*6, r.stream );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
 }
 
 extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa ) {
   if( !sp_list ) return;                                        // boundary_p.cc:77
   if( !fa || !aa || sp_list->g!=aa->g || fa->g!=aa->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
+  bool counts_done = false; int pre_recv[6] = { 0, 0, 0, 0, 0, 0 };
   {
     // Nothing left the domain and no neighbour rank to talk to: return before
     // touching the mirrors (in STRICT coherence that would re-upload every particle).
@@ -278,28 +404,50 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     for( int f=0; f<6; f++ ) if( g0->pkind[f]==PK_REMOTE ) remote = true;
     for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) pending += sp->nm;    // always current on the host (movers_to_host)
     if( !remote && pending==0 ) return;
+    // Nothing of ours is pending but a neighbour may send: run the count phase
+    // of the exchange on its own (all our counts are zero) and stop there when
+    // nothing arrives either.  This is what rounds 2 and 3 of a step's
+    // num_comm_round look like, and it keeps them from touching any mirror.
+    if( pending==0 ) {
+      if( !B.d_int ) VPB_CUDA( cudaMalloc( &B.d_int, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ) ) );
+      VPB_CUDA( cudaMemsetAsync( B.d_int, 0, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ), r.stream ) );
+      exchange_counts( g0, pre_recv );
+      counts_done = true;
+      int tot = 0; for( int f=0; f<6; f++ ) tot += pre_recv[f];
+      if( tot==0 ) return;
+    }
   }
   std::vector<SpeciesMirror *> sps;
+  bool sparse = r.coherence==VPB_COHERENCE_STRICT;
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
     SpeciesMirror * m = mirror( sp );
-    to_device( m );
+    if( !sp->p || ( m->dev_valid && !m->host_valid ) ) sparse = false;   // no host array, or the device copy is the current one
+  }
+  std::vector<SparseSpecies> ss;
+  for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
+    SpeciesMirror * m = mirror( sp );
+    if( sparse ) { SparseSpecies s = { m, 0, 0, 0 }; ss.push_back( s ); } else to_device( m );
     sps.push_back( m );
     if( sp->id<0 || sp->id>=BND_MAX_SP ) VPB_ERROR( "species id %d is outside the device boundary handler's range", sp->id );
   }
+  if( sparse ) sparse_upload( ss );
   GridMirror * gm = sps[0]->grid;
   const GridDev & g = gm->dev;
   bool any_remote = false;
   for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) any_remote = true;
   long long nm_tot = 0;
   for( SpeciesMirror * m : sps ) nm_tot += m->nm;
-  if( !any_remote && nm_tot==0 ) return;                        // nothing left the domain and nobody to talk to
+  if( !any_remote && nm_tot==0 ) { if( sparse ) sparse_download( ss ); return; }   // nothing left the domain and nobody to talk to
   if( nm_tot>0 && pbc_list ) {
     for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_CUSTOM )
       VPB_ERROR( "custom particle boundary handlers (host callbacks) are not available on the device yet" );
   }
   FieldMirror * mf = mirror( fa );
   AccMirror   * ma = mirror( aa );
-  to_device( mf ); to_device( ma );
+  bool any_absorb = false;
+  for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_ABSORB ) any_absorb = true;
+  if( any_absorb || !sparse ) to_device( mf );      // rhob is only touched by absorbed particles
+  if( !sparse ) to_device( ma );                    // (sparse: uploaded when something arrives)
   if( !B.d_int ) VPB_CUDA( cudaMalloc( &B.d_int, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ) ) );
   VPB_CUDA( cudaMemsetAsync( B.d_int, 0, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ), r.stream ) );
 
@@ -333,14 +481,8 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
 
   // ---- exchange counts, then injectors (boundary_p.cc:285-316) ----
   if( any_remote ) {
-    for( int X=0; X<3; X++ ) {
-      const int lo = X, hi = X+3;
-      const int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
-      if( rank_lo<0 && rank_hi<0 ) continue;
-      comm_sendrecv( rank_lo, rank_hi, B.d_int+lo, 4, B.d_int+hi, 4, B.d_int+8+lo, 4, B.d_int+8+hi, 4 );
-    }
-    d2h( n_recv, B.d_int+8, sizeof(int)*6, r.stream );
-    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( counts_done ) for( int f=0; f<6; f++ ) n_recv[f] = pre_recv[f];
+    else exchange_counts( gm, n_recv );
     for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) grow( &B.recv[f], &B.recv_cap[f], (size_t)n_recv[f] ); else n_recv[f] = 0;
     const size_t S = sizeof(vpb_particle_injector_t);
     for( int X=0; X<3; X++ ) {
@@ -357,6 +499,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   int max_inj = 0;
   for( int f=0; f<6; f++ ) max_inj += n_recv[f];
   if( max_inj>0 ) {
+    if( sparse ) to_device( ma );
     BndInject bi = {};
     bi.start[0] = 0;
     for( int f=0; f<6; f++ ) { bi.recv[f] = B.recv[f]; bi.start[f+1] = bi.start[f] + n_recv[f]; }
@@ -390,7 +533,8 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     m->host->np = m->np;
     if( m->nm>1 && !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     movers_to_host( m );
-    if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
+    if( r.coherence==VPB_COHERENCE_STRICT && !sparse ) to_host( m );
   }
+  if( sparse ) sparse_download( ss );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ma ); to_host( mf ); }
 }

@@ -108,12 +108,15 @@ void clear_accumulator_array( vpb_accumulator_array_t * aa ) {
   r.launches++;
   mark_dev_written( m );
   if( r.coherence==VPB_COHERENCE_STRICT && aa->a ) {
-    // keep the host's private copies coherent with "all clear" as well
+    // keep the host's copies (shared + one per pipeline) coherent with "all
+    // clear" as well: the zeros come down from the device copy by DMA, which
+    // is several times faster than one host thread's memset
     const int nx = aa->g->nx, ny = aa->g->ny, nz = aa->g->nz;
     int i0 = ( VPB_VOXEL(1,1,1,nx,ny,nz)/2 )*2;
     int n  = ( ( ( VPB_VOXEL(nx,ny,nz,nx,ny,nz) - i0 + 1 ) + 1 )/2 )*2;
+    pin_host( aa->a, sizeof(vpb_accumulator_t)*( (size_t)aa->n_pipeline*aa->stride + (size_t)m->grid->dev.nv ) );
     for( int c=0; c<=aa->n_pipeline; c++ )
-      memset( aa->a + (size_t)c*aa->stride + i0, 0, sizeof(vpb_accumulator_t)*(size_t)n );
+      d2h( aa->a + (size_t)c*aa->stride + i0, m->d + (size_t)ACC_STRIDE*i0, sizeof(vpb_accumulator_t)*(size_t)n, r.stream );
     VPB_CUDA( cudaStreamSynchronize( r.stream ) );
     m->host_valid = true;
   }
