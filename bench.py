@@ -85,6 +85,9 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+NCU_DRAM_BYTES_PER_PUSH = 71.4   # measured, profiles/r1h_summary.md
+
+
 def dims(s):
     return tuple(int(x) for x in s.lower().split("x"))
 
@@ -204,7 +207,11 @@ def run_b200(args):
     bytes_per_push = 64.0 + 176.0 / args.ppc
     ach = np_total * args.steps * bytes_per_push / (ap_ms * 1e-3) / 1e9
     roofline = {"kernel": "k_advance_p", "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
+                "frac": round(ach / peak, 4),
+                # ncu dram__bytes_read.sum + dram__bytes_write.sum of k_advance_p (profiles/r1h_summary.md:
+                # 71.4 B/push averaged over the ion and electron launches at 128^3), scaled to this launch size
+                "traffic": round(NCU_DRAM_BYTES_PER_PUSH * np_total / 2 / 1e9, 3), "traffic_unit": "GB per launch",
+                "achieved_unit_per_launch_GB": round(bytes_per_push * np_total / 2 / 1e9, 3), "peak_source": peak_src,
                 "bytes_per_push": bytes_per_push, "ms_per_launch": ap_ms / max(ap_calls, 1),
                 "pushes_per_s_kernel_only": np_total * args.steps / (ap_ms * 1e-3),
                 "share_of_step": round(ap_ms / ms, 4)}

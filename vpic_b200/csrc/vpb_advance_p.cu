@@ -10,8 +10,7 @@
 //
 //  * A warp owns a TILE of 32*AP_K consecutive particles (8 KB).  One elected
 //    lane brings the tile into shared memory with a single bulk asynchronous
-//    copy (cp.async.bulk, completion on an mbarrier), prefetches the warp's
-//    NEXT tile into L2 (cp.async.bulk.prefetch.L2), and after the push writes
+//    copy (cp.async.bulk, completion on an mbarrier) and after the push writes
 //    the tile back with one bulk store.  No per-particle LDG/STG at all.
 //  * Each LANE walks AP_K CONSECUTIVE particles of the tile (its own 256 B run
 //    of the array).  With cell-sorted particles a lane stays in one voxel for
@@ -126,12 +125,6 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
       asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                     :: "r"(tile_s), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
-      const int nt = tile + total_warps;
-      if( nt<ntile ) {
-        const long long n0 = (long long)nt*AP_TILE;
-        const uint32_t nb = (uint32_t)( ( np - n0 < AP_TILE ) ? ( np - n0 ) : AP_TILE )*32u;
-        asm volatile( "cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p + n0), "r"(nb) : "memory" );
-      }
     }
     {
       uint32_t ok;

@@ -15,7 +15,8 @@ from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-B200_LIB = os.path.join(_HERE, "libvpic_b200.so")
+# VPIC_B200_LIB: an experimental build of the same library (kernel A/B tests)
+B200_LIB = os.environ.get("VPIC_B200_LIB") or os.path.join(_HERE, "libvpic_b200.so")
 
 _P = C.c_void_p
 _cache = {}
