@@ -64,6 +64,21 @@ void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ); /* energy_
 void vpic_b200_clear_jf( vpb_field_array_t * fa );                    /* sfa.c:231-237          */
 void vpic_b200_synchronize_jf( vpb_field_array_t * fa );              /* remote.c:417-508       */
 void vpic_b200_clear_rhof( vpb_field_array_t * fa );                  /* sfa.c:239-245          */
+void vpic_b200_synchronize_rho( vpb_field_array_t * fa );             /* remote.c:534-624       */
+void vpic_b200_compute_rhob( vpb_field_array_t * fa );                /* {vacuum_,}compute_rhob.c:10-21 */
+void vpic_b200_compute_curl_b( vpb_field_array_t * fa );              /* {vacuum_,}compute_curl_b.cc:10-19 */
+double vpic_b200_synchronize_tang_e_norm_b( vpb_field_array_t * fa ); /* remote.c:298-415       */
+void vpic_b200_compute_div_e_err( vpb_field_array_t * fa );           /* {vacuum_,}compute_div_e_err.c:10-21 */
+double vpic_b200_compute_rms_div_e_err( const vpb_field_array_t * fa ); /* compute_rms_div_e_err.c:12-23 */
+void vpic_b200_clean_div_e( vpb_field_array_t * fa );                 /* {vacuum_,}clean_div_e.c:10-19 */
+void vpic_b200_compute_div_b_err( vpb_field_array_t * fa );           /* compute_div_b_err.cc:10-19 */
+double vpic_b200_compute_rms_div_b_err( const vpb_field_array_t * fa ); /* compute_rms_div_b_err.c:12-23 */
+void vpic_b200_clean_div_b( vpb_field_array_t * fa );                 /* clean_div_b.cc:10-19   */
+
+/* Charge density of a species onto rhof (reference symbol, called by the
+   driver between clear_rhof and synchronize_rho, src/vpic/advance.cc:144-146;
+   src/species_advance/standard/rho_p.cc:22-112). */
+void accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp );
 
 /* ======================= Part 2: control surface ========================== */
 

@@ -431,3 +431,488 @@ int orc_material_coefficients( vpb_material_coefficient_t * mc, int max_mc,
   }
   return n_mc;
 }
+
+/* ===========================================================================
+ * N1: divergence cleaning family, charge-density synchronisation, shared-face
+ * synchronisation, and the initialisation kernels compute_rhob /
+ * compute_curl_b.  Reference: sfa_private.h:256-373 and the files cited at
+ * each function.
+ * ======================================================================== */
+
+#define ORC_FOR_LOCAL_FACES( g, n, X, side, bc )                                  \
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ )                   \
+    for( int bc = orc_face_bc( g, X, side ), once_ = orc_bc_is_local( bc ); once_; once_ = 0 )
+
+/* sfa.c:239-245 */
+void orc_clear_rhof( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  for( int v=0; v<fa->g->nv; v++ ) fa->f[v].rhof = 0;
+}
+
+/* rho_p.cc:22-112: trilinear charge of every particle onto the 8 nodes of its
+   cell, in particle order (separate multiply and add, as compiled). */
+void orc_accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp ) {
+  if( !fa || !sp || fa->g!=sp->g ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_particle_t * p = sp->p;
+  const float q_8V = sp->q*sp->g->r8V;
+  const int np = sp->np, sy = sp->g->sy, sz = sp->g->sz;
+  for( int n=0; n<np; n++ ) {
+    float w0 = p[n].dx, w1 = p[n].dy, w2, w3, w4, w5, w6, w7, dz = p[n].dz;
+    const int v = p[n].i;
+    w7 = p[n].w*q_8V;
+    w6 = w7 - w0*w7; w7 = w7 + w0*w7;
+    w4 = w6 - w1*w6; w5 = w7 - w1*w7;
+    w6 = w6 + w1*w6; w7 = w7 + w1*w7;
+    w0 = w4 - dz*w4; w1 = w5 - dz*w5; w2 = w6 - dz*w6; w3 = w7 - dz*w7;
+    w4 = w4 + dz*w4; w5 = w5 + dz*w5; w6 = w6 + dz*w6; w7 = w7 + dz*w7;
+    f[v      ].rhof += w0; f[v      +1].rhof += w1;
+    f[v   +sy].rhof += w2; f[v   +sy+1].rhof += w3;
+    f[v+sz   ].rhof += w4; f[v+sz   +1].rhof += w5;
+    f[v+sz+sy].rhof += w6; f[v+sz+sy+1].rhof += w7;
+  }
+}
+
+/* local.c:376-445 */
+static void orc_local_adjust_rho( vpb_field_t * f, const vpb_grid_t * g, int which /*0 rhof, 1 rhob*/ ) {
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  ORC_FOR_LOCAL_FACES( g, n, X, side, bc ) {
+    orc_box_t b = orc_plane( g, X, side<0 ? 1 : n[X]+1, ORC_NODE );
+    switch( bc ) {
+    case VPB_PEC_FIELDS:
+      ORC_BOX_LOOP(b) { if( which ) f[ORC_VOX(x,y,z)].rhob = 0; else f[ORC_VOX(x,y,z)].rhof = 0; }
+      break;
+    case VPB_SYMMETRIC_FIELDS: case VPB_PMC_FIELDS: case VPB_ABSORB_FIELDS:
+      if( !which ) ORC_BOX_LOOP(b) f[ORC_VOX(x,y,z)].rhof *= 2;
+      break;
+    default: ORC_FAIL( "Bad boundary condition encountered." );
+    }
+  }
+}
+
+/* remote.c:534-624: axis by axis, node planes 1 and nX+1 of rhof and rhob are
+   folded with the neighbour's (rhof summed, rhob averaged, for equal cells). */
+void orc_synchronize_rho( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  const float d[3] = { g->dx, g->dy, g->dz };
+  orc_local_adjust_rho( f, g, 0 );
+  orc_local_adjust_rho( f, g, 1 );
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    int nf = 1 + 2*(n[Y]+1)*(n[Z]+1);
+    float * buf = (float *)malloc( 4*sizeof(float)*(size_t)nf );
+    float * s[2] = { buf, buf+nf }, * r[2] = { buf+2*nf, buf+3*nf };
+    for( int k=0; k<2; k++ ) {
+      float * p = s[k];
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X]+1, ORC_NODE );
+      *(p++) = d[X];
+      ORC_BOX_LOOP(b) { const vpb_field_t * f0 = f+ORC_VOX(x,y,z); *(p++) = f0->rhof; *(p++) = f0->rhob; }
+    }
+    int got[2];
+    orc_face_exchange( g, X, s[0], s[1], r[0], r[1], nf, &got[0], &got[1] );
+    for( int k=0; k<2; k++ ) {
+      if( !got[k] ) continue;
+      const float * p = r[k];
+      float hrw = *(p++), hlw = hrw + d[X], lw, rw;
+      hrw /= hlw; hlw = d[X]/hlw; lw = hlw + hlw; rw = hrw + hrw;
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X]+1, ORC_NODE );
+      ORC_BOX_LOOP(b) {
+        vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+        f0->rhof =  lw*f0->rhof +  rw*(*(p++));
+        f0->rhob = hlw*f0->rhob + hrw*(*(p++));
+      }
+    }
+    free( buf );
+  }
+}
+
+/* local.c:128-179: normal-E (and its tca) ghost nodes of locally handled faces */
+static void orc_local_ghost_norm_e( vpb_field_t * f, const vpb_grid_t * g ) {
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  ORC_FOR_LOCAL_FACES( g, n, X, side, bc ) {
+    int off[3] = {0,0,0}; off[X] = side;
+    orc_box_t b = orc_plane( g, X, side<0 ? 0 : n[X]+1, ORC_NODE );
+    ORC_BOX_LOOP(b) {
+      vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+      const vpb_field_t * f1 = f+ORC_VOX(x-off[0],y-off[1],z-off[2]), * f2 = f+ORC_VOX(x-2*off[0],y-2*off[1],z-2*off[2]);
+      switch( bc ) {
+      case VPB_PEC_FIELDS:       E_(f0,X) =  E_(f1,X); TCA_(f0,X) =  TCA_(f1,X); break;
+      case VPB_SYMMETRIC_FIELDS:
+      case VPB_PMC_FIELDS:       E_(f0,X) = -E_(f1,X); TCA_(f0,X) = -TCA_(f1,X); break;
+      case VPB_ABSORB_FIELDS:    E_(f0,X) = 2*E_(f1,X) - E_(f2,X); TCA_(f0,X) = 2*TCA_(f1,X) - TCA_(f2,X); break;
+      default: ORC_FAIL( "Bad boundary condition encountered." );
+      }
+    }
+  }
+}
+
+/* remote.c:137-206: the -X port carries eX of node plane 1, the +X port of
+   plane nX; arrivals land in ghost planes 0 / nX+1 (tca is not exchanged). */
+static void orc_remote_ghost_norm_e( vpb_field_t * f, const vpb_grid_t * g ) {
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  const float d[3] = { g->dx, g->dy, g->dz };
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    int nf = 1 + (n[Y]+1)*(n[Z]+1);
+    float * buf = (float *)malloc( 4*sizeof(float)*(size_t)nf );
+    float * s[2] = { buf, buf+nf }, * r[2] = { buf+2*nf, buf+3*nf };
+    for( int k=0; k<2; k++ ) {
+      float * p = s[k];
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X], ORC_NODE );
+      *(p++) = d[X];
+      ORC_BOX_LOOP(b) *(p++) = E_( f+ORC_VOX(x,y,z), X );
+    }
+    int got[2];
+    orc_face_exchange( g, X, s[0], s[1], r[0], r[1], nf, &got[0], &got[1] );
+    for( int k=0; k<2; k++ ) {
+      if( !got[k] ) continue;
+      const float * p = r[k];
+      int off[3] = {0,0,0}; off[X] = k==0 ? 1 : -1;   /* towards the interior */
+      float lw = *(p++);
+      float rw = (2.*d[X])/(lw+d[X]);
+      lw = (lw-d[X])/(lw+d[X]);
+      orc_box_t b = orc_plane( g, X, k==0 ? 0 : n[X]+1, ORC_NODE );
+      ORC_BOX_LOOP(b) E_( f+ORC_VOX(x,y,z), X ) = rw*(*(p++)) + lw*E_( f+ORC_VOX(x+off[0],y+off[1],z+off[2]), X );
+    }
+    free( buf );
+  }
+}
+
+/* compute_div_e_err / compute_rhob and their vacuum variants
+   ({vacuum_,}compute_{div_e_err,rhob}_pipeline.{h,c}): every node
+   (1:nx+1,1:ny+1,1:nz+1) once; the variants differ in how the constants are
+   folded, which changes the rounding and is kept. */
+static void orc_div_e_stencil( vpb_field_array_t * fa, int want_rhob ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
+  const vpb_material_coefficient_t * m = prm->mc;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  orc_local_ghost_norm_e( f, g );
+  orc_remote_ghost_norm_e( f, g );
+  const int vacuum = prm->n_mc==1;
+  const float nc = m->nonconductive;
+  float px, py, pz; const float cj = 1./g->eps0;
+  if( want_rhob ) {
+    if( vacuum ) {
+      px = (nx>1) ? g->eps0*m->epsx*g->rdx : 0; py = (ny>1) ? g->eps0*m->epsy*g->rdy : 0; pz = (nz>1) ? g->eps0*m->epsz*g->rdz : 0;
+    } else {
+      px = (nx>1) ? g->eps0*g->rdx : 0; py = (ny>1) ? g->eps0*g->rdy : 0; pz = (nz>1) ? g->eps0*g->rdz : 0;
+    }
+  } else {
+    if( vacuum ) {
+      px = ((nx>1) ? g->rdx : 0)*m->epsx; py = ((ny>1) ? g->rdy : 0)*m->epsy; pz = ((nz>1) ? g->rdz : 0)*m->epsz;
+    } else {
+      px = (nx>1) ? g->rdx : 0; py = (ny>1) ? g->rdy : 0; pz = (nz>1) ? g->rdz : 0;
+    }
+  }
+  for( int z=1; z<=nz+1; z++ ) for( int y=1; y<=ny+1; y++ ) for( int x=1; x<=nx+1; x++ ) {
+    vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+    const vpb_field_t * fx = f+ORC_VOX(x-1,y,z), * fy = f+ORC_VOX(x,y-1,z), * fz = f+ORC_VOX(x,y,z-1);
+    if( vacuum ) {
+      if( want_rhob ) f0->rhob = nc*( px*( f0->ex - fx->ex ) + py*( f0->ey - fy->ey ) + pz*( f0->ez - fz->ez ) - f0->rhof );
+      else f0->div_e_err = nc*( px*( f0->ex - fx->ex ) + py*( f0->ey - fy->ey ) + pz*( f0->ez - fz->ez ) - cj*( f0->rhof + f0->rhob ) );
+    } else {
+      if( want_rhob ) f0->rhob = m[f0->nmat].nonconductive *
+        ( px*( m[f0->ematx].epsx*f0->ex - m[fx->ematx].epsx*fx->ex ) +
+          py*( m[f0->ematy].epsy*f0->ey - m[fy->ematy].epsy*fy->ey ) +
+          pz*( m[f0->ematz].epsz*f0->ez - m[fz->ematz].epsz*fz->ez ) - f0->rhof );
+      else f0->div_e_err = m[f0->nmat].nonconductive *
+        ( px*( m[f0->ematx].epsx*f0->ex - m[fx->ematx].epsx*fx->ex ) +
+          py*( m[f0->ematy].epsy*f0->ey - m[fy->ematy].epsy*fy->ey ) +
+          pz*( m[f0->ematz].epsz*f0->ez - m[fz->ematz].epsz*fz->ez ) - cj*( f0->rhof + f0->rhob ) );
+    }
+  }
+}
+
+/* compute_div_e_err_pipeline.c:43-190 + local.c:298-333 */
+void orc_compute_div_e_err( vpb_field_array_t * fa ) {
+  orc_div_e_stencil( fa, 0 );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  ORC_FOR_LOCAL_FACES( g, n, X, side, bc ) {
+    orc_box_t b = orc_plane( g, X, side<0 ? 1 : n[X]+1, ORC_NODE );
+    switch( bc ) {
+    case VPB_PEC_FIELDS: case VPB_ABSORB_FIELDS: ORC_BOX_LOOP(b) f[ORC_VOX(x,y,z)].div_e_err = 0; break;
+    case VPB_SYMMETRIC_FIELDS: case VPB_PMC_FIELDS: break;
+    default: ORC_FAIL( "Bad boundary condition encountered." );
+    }
+  }
+}
+
+/* compute_rhob_pipeline.c:43-175 + local_adjust_rhob */
+void orc_compute_rhob( vpb_field_array_t * fa ) {
+  orc_div_e_stencil( fa, 1 );
+  orc_local_adjust_rho( fa->f, fa->g, 1 );
+}
+
+/* Sum of doubles across ranks through the face transport's sibling: tests
+   install orc_allsum for multi-rank runs; single rank is the identity. */
+void (*orc_allsum)( double * v, int n ) = 0;
+void orc_set_allsum( void (*fn)( double *, int ) ) { orc_allsum = fn; }
+
+/* compute_rms_div_e_err_pipeline.c:53-166: interior nodes as FLOAT squares
+   added to a double, boundary nodes with weights 1/2, 1/4, 1/8 as double
+   products.  Order: the exterior first (host), then the pipelines' shares. */
+double orc_compute_rms_div_e_err( const vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  const vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  double err = 0;
+# define ORC_SQ(x,y,z,w) do { const vpb_field_t * f0 = f+ORC_VOX(x,y,z); err += (w)*(double)f0->div_e_err*(double)f0->div_e_err; } while(0)
+  for( int y=2; y<=ny; y++ ) for( int z=2; z<=nz; z++ ) { ORC_SQ(1,y,z,0.5); ORC_SQ(nx+1,y,z,0.5); }
+  for( int z=2; z<=nz; z++ ) for( int x=2; x<=nx; x++ ) { ORC_SQ(x,1,z,0.5); ORC_SQ(x,ny+1,z,0.5); }
+  for( int x=2; x<=nx; x++ ) for( int y=2; y<=ny; y++ ) { ORC_SQ(x,y,1,0.5); ORC_SQ(x,y,nz+1,0.5); }
+  for( int x=2; x<=nx; x++ ) { ORC_SQ(x,1,1,0.25); ORC_SQ(x,ny+1,1,0.25); ORC_SQ(x,1,nz+1,0.25); ORC_SQ(x,ny+1,nz+1,0.25); }
+  for( int y=2; y<=ny; y++ ) { ORC_SQ(1,y,1,0.25); ORC_SQ(1,y,nz+1,0.25); ORC_SQ(nx+1,y,1,0.25); ORC_SQ(nx+1,y,nz+1,0.25); }
+  for( int z=2; z<=nz; z++ ) { ORC_SQ(1,1,z,0.25); ORC_SQ(nx+1,1,z,0.25); ORC_SQ(1,ny+1,z,0.25); ORC_SQ(nx+1,ny+1,z,0.25); }
+  ORC_SQ(1,1,1,0.125); ORC_SQ(nx+1,1,1,0.125); ORC_SQ(1,ny+1,1,0.125); ORC_SQ(nx+1,ny+1,1,0.125);
+  ORC_SQ(1,1,nz+1,0.125); ORC_SQ(nx+1,1,nz+1,0.125); ORC_SQ(1,ny+1,nz+1,0.125); ORC_SQ(nx+1,ny+1,nz+1,0.125);
+# undef ORC_SQ
+  /* interior: the pipelines' shares (blocks of 16 voxels) and the host's
+     straggler share, each summed on its own, added in pipeline order */
+  {
+    const int bx = nx-1, by = ny-1, bz = nz-1, P = orc_energy_pipelines;
+    const int nvox = ( bx>0 && by>0 && bz>0 ) ? bx*by*bz : 0;
+    for( int r=0; r<=P; r++ ) {
+      double t = (double)( nvox/16 )/(double)P;
+      int i0 = 16*(int)( t*(double)r + 0.5 ), i1 = nvox;
+      if( r<P ) i1 = 16*(int)( t*(double)(r+1) + 0.5 );
+      double part = 0;
+      for( int i=i0; i<i1; i++ ) {
+        const vpb_field_t * f0 = f+ORC_VOX( 2 + i%bx, 2 + (i/bx)%by, 2 + i/(bx*by) );
+        part += f0->div_e_err*f0->div_e_err;
+      }
+      err += part;
+    }
+  }
+  double local[2] = { err*g->dV, ( g->nx*g->ny*g->nz )*g->dV };
+  if( orc_allsum ) orc_allsum( local, 2 );
+  return g->eps0*sqrt( local[0]/local[1] );
+}
+
+/* {vacuum_,}clean_div_e_pipeline.{h,c} + local_adjust_tang_e: Marder pass on
+   ex (1:nx,1:ny+1,1:nz+1), ey (1:nx+1,1:ny,1:nz+1), ez (1:nx+1,1:ny+1,1:nz). */
+void orc_clean_div_e( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
+  const vpb_material_coefficient_t * m = prm->mc;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  const int vacuum = prm->n_mc==1;
+  const float _rdx = (nx>1) ? g->rdx : 0, _rdy = (ny>1) ? g->rdy : 0, _rdz = (nz>1) ? g->rdz : 0;
+  const float alphadt = 0.3888889/( _rdx*_rdx + _rdy*_rdy + _rdz*_rdz );
+  float px, py, pz;
+  if( vacuum ) { px = (alphadt*_rdx)*m->drivex; py = (alphadt*_rdy)*m->drivey; pz = (alphadt*_rdz)*m->drivez; }
+  else         { px = alphadt*_rdx; py = alphadt*_rdy; pz = alphadt*_rdz; }
+  for( int z=1; z<=nz+1; z++ ) for( int y=1; y<=ny+1; y++ ) for( int x=1; x<=nx+1; x++ ) {
+    vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+    const vpb_field_t * fx = f+ORC_VOX(x+1,y,z), * fy = f+ORC_VOX(x,y+1,z), * fz = f+ORC_VOX(x,y,z+1);
+    if( vacuum ) {
+      if( x<=nx ) f0->ex += px*( fx->div_e_err - f0->div_e_err );
+      if( y<=ny ) f0->ey += py*( fy->div_e_err - f0->div_e_err );
+      if( z<=nz ) f0->ez += pz*( fz->div_e_err - f0->div_e_err );
+    } else {
+      if( x<=nx ) f0->ex += m[f0->ematx].drivex*px*( fx->div_e_err - f0->div_e_err );
+      if( y<=ny ) f0->ey += m[f0->ematy].drivey*py*( fy->div_e_err - f0->div_e_err );
+      if( z<=nz ) f0->ez += m[f0->ematz].drivez*pz*( fz->div_e_err - f0->div_e_err );
+    }
+  }
+  orc_local_adjust_tang_e( f, g );
+}
+
+/* compute_div_b_err_pipeline.cc:7-53: cells (1:nx,1:ny,1:nz) */
+void orc_compute_div_b_err( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  const float px = (nx>1) ? g->rdx : 0, py = (ny>1) ? g->rdy : 0, pz = (nz>1) ? g->rdz : 0;
+  for( int z=1; z<=nz; z++ ) for( int y=1; y<=ny; y++ ) for( int x=1; x<=nx; x++ ) {
+    vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+    const vpb_field_t * fx = f+ORC_VOX(x+1,y,z), * fy = f+ORC_VOX(x,y+1,z), * fz = f+ORC_VOX(x,y,z+1);
+    f0->div_b_err = px*( fx->cbx - f0->cbx ) + py*( fy->cby - f0->cby ) + pz*( fz->cbz - f0->cbz );
+  }
+}
+
+/* compute_rms_div_b_err_pipeline.c:7-103 */
+double orc_compute_rms_div_b_err( const vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  const vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz, P = orc_energy_pipelines;
+  const int nvox = nx*ny*nz;
+  double err = 0;
+  for( int r=0; r<=P; r++ ) {
+    double t = (double)( nvox/16 )/(double)P;
+    int i0 = 16*(int)( t*(double)r + 0.5 ), i1 = nvox;
+    if( r<P ) i1 = 16*(int)( t*(double)(r+1) + 0.5 );
+    double part = 0;
+    for( int i=i0; i<i1; i++ ) {
+      const vpb_field_t * f0 = f+ORC_VOX( 1 + i%nx, 1 + (i/nx)%ny, 1 + i/(nx*ny) );
+      part += f0->div_b_err*f0->div_b_err;
+    }
+    err += part;
+  }
+  double local[2] = { err*g->dV, ( g->nx*g->ny*g->nz )*g->dV };
+  if( orc_allsum ) orc_allsum( local, 2 );
+  return g->eps0*sqrt( local[0]/local[1] );
+}
+
+/* local.c:181-222 */
+static void orc_local_ghost_div_b( vpb_field_t * f, const vpb_grid_t * g ) {
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  ORC_FOR_LOCAL_FACES( g, n, X, side, bc ) {
+    int off[3] = {0,0,0}; off[X] = side;
+    orc_box_t b = orc_plane( g, X, side<0 ? 0 : n[X]+1, ORC_FACE );
+    ORC_BOX_LOOP(b) {
+      vpb_field_t * f0 = f+ORC_VOX(x,y,z); const vpb_field_t * f1 = f+ORC_VOX(x-off[0],y-off[1],z-off[2]);
+      switch( bc ) {
+      case VPB_PEC_FIELDS:       f0->div_b_err =  f1->div_b_err; break;
+      case VPB_SYMMETRIC_FIELDS:
+      case VPB_PMC_FIELDS:       f0->div_b_err = -f1->div_b_err; break;
+      case VPB_ABSORB_FIELDS:    f0->div_b_err = 0; break;
+      default: ORC_FAIL( "Bad boundary condition encountered." );
+      }
+    }
+  }
+}
+
+/* remote.c:208-296 */
+static void orc_remote_ghost_div_b( vpb_field_t * f, const vpb_grid_t * g ) {
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  const float d[3] = { g->dx, g->dy, g->dz };
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    int nf = 1 + n[Y]*n[Z];
+    float * buf = (float *)malloc( 4*sizeof(float)*(size_t)nf );
+    float * s[2] = { buf, buf+nf }, * r[2] = { buf+2*nf, buf+3*nf };
+    for( int k=0; k<2; k++ ) {
+      float * p = s[k];
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X], ORC_FACE );
+      *(p++) = d[X];
+      ORC_BOX_LOOP(b) *(p++) = f[ORC_VOX(x,y,z)].div_b_err;
+    }
+    int got[2];
+    orc_face_exchange( g, X, s[0], s[1], r[0], r[1], nf, &got[0], &got[1] );
+    for( int k=0; k<2; k++ ) {
+      if( !got[k] ) continue;
+      const float * p = r[k];
+      int off[3] = {0,0,0}; off[X] = k==0 ? 1 : -1;
+      float lw = *(p++);
+      float rw = (2.*d[X])/(lw+d[X]);
+      lw = (lw-d[X])/(lw+d[X]);
+      orc_box_t b = orc_plane( g, X, k==0 ? 0 : n[X]+1, ORC_FACE );
+      ORC_BOX_LOOP(b) f[ORC_VOX(x,y,z)].div_b_err = rw*(*(p++)) + lw*f[ORC_VOX(x+off[0],y+off[1],z+off[2])].div_b_err;
+    }
+    free( buf );
+  }
+}
+
+/* clean_div_b_pipeline.cc:17-307 + local_adjust_norm_b: cbx on
+   (1:nx+1,1:ny,1:nz), cby on (1:nx,1:ny+1,1:nz), cbz on (1:nx,1:ny,1:nz+1). */
+void orc_clean_div_b( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  float px = (nx>1) ? g->rdx : 0, py = (ny>1) ? g->rdy : 0, pz = (nz>1) ? g->rdz : 0;
+  const float alphadt = 0.3888889/( px*px + py*py + pz*pz );
+  px *= alphadt; py *= alphadt; pz *= alphadt;
+  orc_local_ghost_div_b( f, g );
+  orc_remote_ghost_div_b( f, g );
+  for( int z=1; z<=nz+1; z++ ) for( int y=1; y<=ny+1; y++ ) for( int x=1; x<=nx+1; x++ ) {
+    vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+    const vpb_field_t * fx = f+ORC_VOX(x-1,y,z), * fy = f+ORC_VOX(x,y-1,z), * fz = f+ORC_VOX(x,y,z-1);
+    if( y<=ny && z<=nz ) f0->cbx += px*( f0->div_b_err - fx->div_b_err );
+    if( z<=nz && x<=nx ) f0->cby += py*( f0->div_b_err - fy->div_b_err );
+    if( x<=nx && y<=ny ) f0->cbz += pz*( f0->div_b_err - fz->div_b_err );
+  }
+  orc_local_adjust_norm_b( f, g );
+}
+
+/* {vacuum_,}compute_curl_b_pipeline.{h,cc}: tca = curl( cB/mu_r ) on the same
+   edge sets as advance_e, with the same ghost / adjust steps around it. */
+void orc_compute_curl_b( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const vpb_sfa_params_t * prm = (const vpb_sfa_params_t *)fa->params;
+  const vpb_material_coefficient_t * m = prm->mc;
+  const int nx = g->nx, ny = g->ny, nz = g->nz;
+  orc_local_ghost_tang_b( f, g );
+  orc_remote_ghost_tang_b( f, g );
+  if( prm->n_mc==1 ) {
+    const float px_muz = ((nx>1) ? g->cvac*g->dt*g->rdx : 0)*m->rmuz;
+    const float px_muy = ((nx>1) ? g->cvac*g->dt*g->rdx : 0)*m->rmuy;
+    const float py_mux = ((ny>1) ? g->cvac*g->dt*g->rdy : 0)*m->rmux;
+    const float py_muz = ((ny>1) ? g->cvac*g->dt*g->rdy : 0)*m->rmuz;
+    const float pz_muy = ((nz>1) ? g->cvac*g->dt*g->rdz : 0)*m->rmuy;
+    const float pz_mux = ((nz>1) ? g->cvac*g->dt*g->rdz : 0)*m->rmux;
+    for( int z=1; z<=nz+1; z++ ) for( int y=1; y<=ny+1; y++ ) for( int x=1; x<=nx+1; x++ ) {
+      vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+      const vpb_field_t * fx = f+ORC_VOX(x-1,y,z), * fy = f+ORC_VOX(x,y-1,z), * fz = f+ORC_VOX(x,y,z-1);
+      if( x<=nx ) f0->tcax = ( py_muz*( f0->cbz - fy->cbz ) - pz_muy*( f0->cby - fz->cby ) );
+      if( y<=ny ) f0->tcay = ( pz_mux*( f0->cbx - fz->cbx ) - px_muz*( f0->cbz - fx->cbz ) );
+      if( z<=nz ) f0->tcaz = ( px_muy*( f0->cby - fx->cby ) - py_mux*( f0->cbx - fy->cbx ) );
+    }
+  } else {
+    const float px = (nx>1) ? g->cvac*g->dt*g->rdx : 0;
+    const float py = (ny>1) ? g->cvac*g->dt*g->rdy : 0;
+    const float pz = (nz>1) ? g->cvac*g->dt*g->rdz : 0;
+    for( int z=1; z<=nz+1; z++ ) for( int y=1; y<=ny+1; y++ ) for( int x=1; x<=nx+1; x++ ) {
+      vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+      const vpb_field_t * fx = f+ORC_VOX(x-1,y,z), * fy = f+ORC_VOX(x,y-1,z), * fz = f+ORC_VOX(x,y,z-1);
+      if( x<=nx ) f0->tcax = ( py*( f0->cbz*m[f0->fmatz].rmuz - fy->cbz*m[fy->fmatz].rmuz ) -
+                               pz*( f0->cby*m[f0->fmaty].rmuy - fz->cby*m[fz->fmaty].rmuy ) );
+      if( y<=ny ) f0->tcay = ( pz*( f0->cbx*m[f0->fmatx].rmux - fz->cbx*m[fz->fmatx].rmux ) -
+                               px*( f0->cbz*m[f0->fmatz].rmuz - fx->cbz*m[fx->fmatz].rmuz ) );
+      if( z<=nz ) f0->tcaz = ( px*( f0->cby*m[f0->fmaty].rmuy - fx->cby*m[fx->fmaty].rmuy ) -
+                               py*( f0->cbx*m[f0->fmatx].rmux - fy->cbx*m[fy->fmatx].rmux ) );
+    }
+  }
+  orc_local_adjust_tang_e( f, g );
+}
+
+/* remote.c:298-415: average the doubly owned face values (cbX on faces, eY/eZ
+   and tcaY/tcaZ on edges of planes 1 and nX+1) with the neighbour's, axis by
+   axis, and return the summed squared mismatch (cb and e only). */
+double orc_synchronize_tang_e_norm_b( vpb_field_array_t * fa ) {
+  if( !fa ) ORC_FAIL( "Bad args" );
+  vpb_field_t * f = fa->f; const vpb_grid_t * g = fa->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  double err = 0;
+  orc_local_adjust_tang_e( f, g );
+  orc_local_adjust_norm_b( f, g );
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    int nf = 2*n[Y]*(n[Z]+1) + 2*n[Z]*(n[Y]+1) + n[Y]*n[Z];
+    float * buf = (float *)malloc( 4*sizeof(float)*(size_t)nf );
+    float * s[2] = { buf, buf+nf }, * r[2] = { buf+2*nf, buf+3*nf };
+    for( int k=0; k<2; k++ ) {
+      float * p = s[k]; int face = k==0 ? 1 : n[X]+1;
+      orc_box_t bf = orc_plane( g, X, face, ORC_FACE ), by = orc_plane( g, X, face, ORC_YZ_EDGE ), bz = orc_plane( g, X, face, ORC_ZY_EDGE );
+      ORC_BOX_LOOP(bf) *(p++) = CB_( f+ORC_VOX(x,y,z), X );
+      ORC_BOX_LOOP(by) { const vpb_field_t * f0 = f+ORC_VOX(x,y,z); *(p++) = E_(f0,Y); *(p++) = TCA_(f0,Y); }
+      ORC_BOX_LOOP(bz) { const vpb_field_t * f0 = f+ORC_VOX(x,y,z); *(p++) = E_(f0,Z); *(p++) = TCA_(f0,Z); }
+    }
+    int got[2];
+    orc_face_exchange( g, X, s[0], s[1], r[0], r[1], nf, &got[0], &got[1] );
+    /* END_RECV(-1,0,0) comes first in the reference and names the message by
+       the SENDER's port (see orc_synchronize_jf): it is the +X neighbour's
+       plane 1 and updates our face nX+1 ("face = (i+j+k)<0 ? nX+1 : 1"). */
+    for( int k=1; k>=0; k-- ) {          /* face nX+1 first: fixes the order of the double sum */
+      if( !got[k] ) continue;
+      const float * p = r[k]; int face = k==0 ? 1 : n[X]+1;
+      double w1, w2;
+      orc_box_t bf = orc_plane( g, X, face, ORC_FACE ), by = orc_plane( g, X, face, ORC_YZ_EDGE ), bz = orc_plane( g, X, face, ORC_ZY_EDGE );
+      ORC_BOX_LOOP(bf) { vpb_field_t * f0 = f+ORC_VOX(x,y,z); w1 = *(p++); w2 = CB_(f0,X); CB_(f0,X) = 0.5*( w1+w2 ); err += (w1-w2)*(w1-w2); }
+      ORC_BOX_LOOP(by) { vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+        w1 = *(p++); w2 = E_(f0,Y);   E_(f0,Y)   = 0.5*( w1+w2 ); err += (w1-w2)*(w1-w2);
+        w1 = *(p++); w2 = TCA_(f0,Y); TCA_(f0,Y) = 0.5*( w1+w2 ); }
+      ORC_BOX_LOOP(bz) { vpb_field_t * f0 = f+ORC_VOX(x,y,z);
+        w1 = *(p++); w2 = E_(f0,Z);   E_(f0,Z)   = 0.5*( w1+w2 ); err += (w1-w2)*(w1-w2);
+        w1 = *(p++); w2 = TCA_(f0,Z); TCA_(f0,Z) = 0.5*( w1+w2 ); }
+    }
+    free( buf );
+  }
+  if( orc_allsum ) orc_allsum( &err, 1 );
+  return err;
+}

@@ -82,6 +82,24 @@ void orc_advance_e( vpb_field_array_t * fa, float frac );
 /* F12 src/field_advance/standard/pipeline/{vacuum_,}energy_f_pipeline.{h,c} */
 void orc_energy_f( double * en /*[6]*/, const vpb_field_array_t * fa );
 
+/* N1: divergence cleaning, charge synchronisation, shared-face synchronisation
+   (sfa_private.h:256-373; local.c; remote.c:137-415,534-624; rho_p.cc:22-112)
+   and N2's field initialisation kernels. */
+void   orc_clear_rhof( vpb_field_array_t * fa );                                  /* sfa.c:239-245 */
+void   orc_accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp );   /* rho_p.cc:22-112 */
+void   orc_synchronize_rho( vpb_field_array_t * fa );                             /* remote.c:534-624 */
+void   orc_compute_rhob( vpb_field_array_t * fa );                                /* {vacuum_,}compute_rhob_pipeline */
+void   orc_compute_curl_b( vpb_field_array_t * fa );                              /* {vacuum_,}compute_curl_b_pipeline */
+double orc_synchronize_tang_e_norm_b( vpb_field_array_t * fa );                   /* remote.c:298-415 */
+void   orc_compute_div_e_err( vpb_field_array_t * fa );                           /* {vacuum_,}compute_div_e_err_pipeline */
+double orc_compute_rms_div_e_err( const vpb_field_array_t * fa );                 /* compute_rms_div_e_err_pipeline.c */
+void   orc_clean_div_e( vpb_field_array_t * fa );                                 /* {vacuum_,}clean_div_e_pipeline */
+void   orc_compute_div_b_err( vpb_field_array_t * fa );                           /* compute_div_b_err_pipeline.cc */
+double orc_compute_rms_div_b_err( const vpb_field_array_t * fa );                 /* compute_rms_div_b_err_pipeline.c */
+void   orc_clean_div_b( vpb_field_array_t * fa );                                 /* clean_div_b_pipeline.cc */
+/* allreduce hook for the rms / mismatch diagnostics of multi-rank tests */
+void   orc_set_allsum( void (*fn)( double * v, int n ) );
+
 /* F14 src/boundary/boundary_p.cc:36-518 (absorb/reflect/periodic/remote; no
        custom handlers) and F15 src/species_advance/standard/rho_p.cc:125-171 */
 void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa );

@@ -83,3 +83,49 @@ def test_whole_steps(case):
         so.advance(); sr.advance()
         compare(so, sr, f"step {step}")
     assert so.energies() == sr.energies()
+
+
+def _seed_charges(so, sr, seed=11):
+    """Non-trivial rhob / div errors in both states (random_fields leaves them 0)."""
+    rng = np.random.default_rng(seed)
+    nv = so.grid_struct(so.g).nv
+    for k in ("rhob", "rhof", "div_e_err", "div_b_err"):
+        v = (0.05 * rng.standard_normal(nv)).astype(np.float32)
+        so.fields()[k] = v
+        sr.fields()[k] = v
+
+
+DIVCLEAN_CASES = CASES + [dict(kind="periodic", n=(7, 1, 5)), dict(kind="metal", n=(1, 6, 5))]
+
+
+@pytest.mark.parametrize("case", DIVCLEAN_CASES)
+def test_divergence_cleaning_family(case):
+    """N1: clear_rhof / accumulate_rho_p / synchronize_rho, the div-E and div-B
+    error + rms + Marder passes, compute_rhob / compute_curl_b and
+    synchronize_tang_e_norm_b, oracle against the compiled reference, bit for
+    bit including the double diagnostics."""
+    so, sr = pair(**case)
+    _seed_charges(so, sr)
+    out = []
+    for s in (so, sr):
+        be, fa = s.be, s.fa
+        res = []
+        be.clear_rhof(fa)
+        for sp in s.species_in_list_order():
+            be.accumulate_rho_p(fa, sp)
+        be.synchronize_rho(fa)
+        for _ in range(2):
+            be.compute_div_e_err(fa)
+            res.append(be.compute_rms_div_e_err(fa))
+            be.clean_div_e(fa)
+        for _ in range(2):
+            be.compute_div_b_err(fa)
+            res.append(be.compute_rms_div_b_err(fa))
+            be.clean_div_b(fa)
+        res.append(be.synchronize_tang_e_norm_b(fa))
+        be.compute_rhob(fa)
+        be.compute_curl_b(fa)
+        out.append(res)
+    assert same_bits(so.fields(), sr.fields())
+    assert out[0] == out[1], (out[0], out[1])
+    assert all(np.isfinite(v) and v > 0 for v in out[0][:4])

@@ -298,18 +298,18 @@ static void launch_plane( FieldMirror * m, PlaneArgs a ) {
   VPB_CHECK_LAUNCH(); r.launches++;
 }
 
-static inline bool face_is_remote( const GridMirror * gm, int X, int side ) {
+bool face_is_remote( const GridMirror * gm, int X, int side ) {
   int bc = gm->fbc[ X + ( side>0 ? 3 : 0 ) ];
   return bc>=0 && bc<g_world_size;
 }
-static inline int face_bc( const GridMirror * gm, int X, int side ) { return gm->fbc[ X + ( side>0 ? 3 : 0 ) ]; }
+int face_bc( const GridMirror * gm, int X, int side ) { return gm->fbc[ X + ( side>0 ? 3 : 0 ) ]; }
 
 // Face transport.  Single-GPU: what leaves through -X arrives on our own +X
 // port (the reference self-sends through MPI, grid_comm.c:20-23), i.e. the
 // receive buffer IS the opposite send buffer.  Multi-GPU: vpb_comm.cu.
 
 // Device layout of m->d_face: [send_lo | send_hi | recv_lo | recv_hi], each face_floats long.
-static void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi ) {
+void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi ) {
   float * slo = m->d_face, * shi = m->d_face + m->face_floats;
   float * rlo = m->d_face + 2*m->face_floats, * rhi = m->d_face + 3*m->face_floats;
   const GridMirror * gm = m->grid;
@@ -330,7 +330,7 @@ static void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo,
 }
 
 // remote.c:61-134 + local.c:50-122: fill every tangential-B ghost plane.
-static void fill_ghost_tang_b( FieldMirror * m ) {
+void fill_ghost_tang_b( FieldMirror * m ) {
   const GridMirror * gm = m->grid; const GridDev & g = gm->dev; const vpb_grid_t * hg = gm->host;
   const int n3[3] = { g.nx, g.ny, g.nz };
   const float d3[3] = { hg->dx, hg->dy, hg->dz };
@@ -375,6 +375,35 @@ static void fill_ghost_tang_b( FieldMirror * m ) {
   }
 }
 
+// local.c:267-296
+void local_adjust_norm_b( FieldMirror * m ) {
+  const GridDev & g = m->grid->dev;
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
+    const int bc = face_bc( m->grid, X, side );
+    if( !( bc<0 || bc>=g_world_size ) ) continue;
+    if( bc==VPB_SYMMETRIC_FIELDS ) {
+      PlaneArgs a{}; a.op = OP_NORM_B_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
+      launch_plane( m, a );
+    } else if( bc!=VPB_PEC_FIELDS && bc!=VPB_PMC_FIELDS && bc!=VPB_ABSORB_FIELDS )
+      VPB_ERROR( "Bad boundary condition encountered." );
+  }
+}
+
+// local.c:224-264
+void local_adjust_tang_e( FieldMirror * m ) {
+  const GridDev & g = m->grid->dev;
+  const int n3[3] = { g.nx, g.ny, g.nz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
+    const int bc = face_bc( m->grid, X, side );
+    if( !( bc<0 || bc>=g_world_size ) ) continue;
+    if( bc==VPB_PEC_FIELDS ) {
+      PlaneArgs a{}; a.op = OP_TANG_E_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
+      launch_plane( m, a );
+    }
+  }
+}
+
 } // namespace vpb
 
 using namespace vpb;
@@ -394,16 +423,7 @@ void vpic_b200_advance_b( vpb_field_array_t * fa, float frac ) {
   const float pz = (g.nz>1) ? frac*hg->cvac*hg->dt*hg->rdz : 0;
   k_advance_b<<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( m->d, g, px, py, pz );
   VPB_CHECK_LAUNCH(); r.launches++;
-  const int n3[3] = { g.nx, g.ny, g.nz };
-  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
-    const int bc = face_bc( m->grid, X, side );
-    if( !( bc<0 || bc>=g_world_size ) ) continue;
-    if( bc==VPB_SYMMETRIC_FIELDS ) {
-      PlaneArgs a{}; a.op = OP_NORM_B_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
-      launch_plane( m, a );
-    } else if( bc!=VPB_PEC_FIELDS && bc!=VPB_PMC_FIELDS && bc!=VPB_ABSORB_FIELDS )
-      VPB_ERROR( "Bad boundary condition encountered." );
-  }
+  local_adjust_norm_b( m );
   finish_write( m );
 }
 
@@ -438,16 +458,7 @@ void vpic_b200_advance_e( vpb_field_array_t * fa, float frac ) {
     k_advance_e_material<<< dim3( div_up( (long long)(g.nx+1)*(g.ny+1), 256 ), g.nz+1 ), 256, 0, r.stream >>>( m->d, m->d_mat, m->d_mc, g, px, py, pz, damp, hg->dt/hg->eps0 );
   }
   VPB_CHECK_LAUNCH(); r.launches++;
-  // local_adjust_tang_e (local.c:224-264)
-  const int n3[3] = { g.nx, g.ny, g.nz };
-  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {
-    const int bc = face_bc( m->grid, X, side );
-    if( !( bc<0 || bc>=g_world_size ) ) continue;
-    if( bc==VPB_PEC_FIELDS ) {
-      PlaneArgs a{}; a.op = OP_TANG_E_ZERO; a.X = X; a.side = side; a.plane = side<0 ? 1 : n3[X]+1;
-      launch_plane( m, a );
-    }
-  }
+  local_adjust_tang_e( m );
   finish_write( m );
 }
 

@@ -296,6 +296,16 @@ vpb_field_array_t * new_standard_field_array( vpb_grid_t * g, const vpb_material
   fa->kernel->clear_jf       = vpic_b200_clear_jf;
   fa->kernel->synchronize_jf = vpic_b200_synchronize_jf;
   fa->kernel->clear_rhof     = vpic_b200_clear_rhof;
+  fa->kernel->synchronize_rho           = vpic_b200_synchronize_rho;
+  fa->kernel->compute_rhob              = vpic_b200_compute_rhob;
+  fa->kernel->compute_curl_b            = vpic_b200_compute_curl_b;
+  fa->kernel->synchronize_tang_e_norm_b = vpic_b200_synchronize_tang_e_norm_b;
+  fa->kernel->compute_div_e_err         = vpic_b200_compute_div_e_err;
+  fa->kernel->compute_rms_div_e_err     = vpic_b200_compute_rms_div_e_err;
+  fa->kernel->clean_div_e               = vpic_b200_clean_div_e;
+  fa->kernel->compute_div_b_err         = vpic_b200_compute_div_b_err;
+  fa->kernel->compute_rms_div_b_err     = vpic_b200_compute_rms_div_b_err;
+  fa->kernel->clean_div_b               = vpic_b200_clean_div_b;
   return fa;
 }
 

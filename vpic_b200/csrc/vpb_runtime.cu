@@ -221,10 +221,11 @@ FieldMirror * mirror( vpb_field_array_t * fa ) {
   VPB_CUDA( cudaMalloc( &m->d_mc, sizeof(vpb_material_coefficient_t)*(size_t)m->n_mc ) );
   VPB_CUDA( cudaMemcpy( m->d_mc, prm->mc, sizeof(vpb_material_coefficient_t)*(size_t)m->n_mc, cudaMemcpyHostToDevice ) );
   if( m->n_mc>1 ) VPB_CUDA( cudaMalloc( &m->d_mat, sizeof(int16_t)*8*(size_t)d.nvp ) );
-  // packed faces: 2 faces x (send+recv) of the largest plane, 3 comps worth
+  // packed faces: 2 faces x (send+recv) of the largest plane; the largest message
+  // (synchronize_tang_e_norm_b) carries 5 values per plane point
   size_t a = (size_t)(d.nx+2)*(d.ny+2), b = (size_t)(d.ny+2)*(d.nz+2), c = (size_t)(d.nz+2)*(d.nx+2);
   size_t mx = a>b ? a : b; if( c>mx ) mx = c;
-  m->face_floats = 2*mx + 32;
+  m->face_floats = 5*mx + 32;
   VPB_CUDA( cudaMalloc( &m->d_face, sizeof(float)*4*m->face_floats ) );
   m->dev_valid = false; m->host_valid = true;
   r.fields[fa] = m;

@@ -198,6 +198,13 @@ bool comm_ready();
 void comm_shutdown();
 void release_boundary_buffers();
 void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
+// field boundary machinery shared by vpb_fields.cu and vpb_divclean.cu
+bool face_is_remote( const GridMirror * gm, int X, int side );
+int  face_bc( const GridMirror * gm, int X, int side );
+void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi );   // packed faces in m->d_face
+void fill_ghost_tang_b( FieldMirror * m );
+void local_adjust_norm_b( FieldMirror * m );
+void local_adjust_tang_e( FieldMirror * m );
 void release_sort_buffers();
 __global__ void k_sum_partials( double * out, const double * partial, int nblock, int ncomp, double scale );
 

@@ -73,10 +73,16 @@ _SPECIES_FUNCS = {
     "center_p": (None, [_P, _P]), "uncenter_p": (None, [_P, _P]),
     "load_interpolator_array": (None, [_P, _P]), "clear_accumulator_array": (None, [_P]),
     "reduce_accumulator_array": (None, [_P]), "unload_accumulator_array": (None, [_P, _P]),
+    "accumulate_rho_p": (None, [_P, _P]),
 }
 _FIELD_FUNCS = {
     "advance_b": (None, [_P, C.c_float]), "advance_e": (None, [_P, C.c_float]),
     "energy_f": (None, [C.POINTER(C.c_double), _P]), "clear_jf": (None, [_P]), "synchronize_jf": (None, [_P]),
+    # interval-gated entries of the kernel table (src/vpic/advance.cc:141-179, initialize.cc:17-31)
+    "clear_rhof": (None, [_P]), "synchronize_rho": (None, [_P]), "compute_rhob": (None, [_P]),
+    "compute_curl_b": (None, [_P]), "synchronize_tang_e_norm_b": (C.c_double, [_P]),
+    "compute_div_e_err": (None, [_P]), "compute_rms_div_e_err": (C.c_double, [_P]), "clean_div_e": (None, [_P]),
+    "compute_div_b_err": (None, [_P]), "compute_rms_div_b_err": (C.c_double, [_P]), "clean_div_b": (None, [_P]),
 }
 
 
