@@ -133,6 +133,7 @@ def ref_facts(L):
 # ---- multi-rank transport for the oracle (tests only) -------------------------
 
 _EXCH_PROTO = C.CFUNCTYPE(None, _P, C.c_int, _P, _P, _P, _P, C.POINTER(C.c_int64), C.POINTER(C.c_int64))
+_ALLSUM_PROTO = C.CFUNCTYPE(None, C.POINTER(C.c_double), C.c_int)
 _exch_keepalive = []
 
 
@@ -186,6 +187,27 @@ def install_gloo_exchange(sim):
     L.orc_set_exchange.argtypes = [_EXCH_PROTO, _P]
     L.orc_set_exchange.restype = None
     L.orc_set_exchange(cb, None)
+
+    def allsum(v, n):                                   # mp_allsum_d of the rms / mismatch diagnostics
+        t = torch.from_numpy(np.ctypeslib.as_array(v, shape=(n,)).copy())
+        dist.all_reduce(t)
+        for k in range(n):
+            v[k] = float(t[k])
+
+    cb2 = _ALLSUM_PROTO(allsum)
+    _exch_keepalive.append(cb2)
+    L.orc_set_allsum.argtypes = [_ALLSUM_PROTO]
+    L.orc_set_allsum.restype = None
+    L.orc_set_allsum(cb2)
+
+
+def remove_exchange():
+    """Back to the single-rank loop-back transport."""
+    L = _load(ORACLE_LIB)
+    L.orc_set_exchange.argtypes = [_EXCH_PROTO, _P]
+    L.orc_set_exchange(_EXCH_PROTO(0), None)
+    L.orc_set_allsum.argtypes = [_ALLSUM_PROTO]
+    L.orc_set_allsum(_ALLSUM_PROTO(0))
 
 
 def set_world(rank, size):

@@ -129,3 +129,20 @@ def test_divergence_cleaning_family(case):
     assert same_bits(so.fields(), sr.fields())
     assert out[0] == out[1], (out[0], out[1])
     assert all(np.isfinite(v) and v > 0 for v in out[0][:4])
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_whole_steps_with_full_initialize_and_cleaning(case):
+    """The reference's complete initialize() sequence and its interval-gated
+    cleaning / synchronisation blocks (advance.cc:141-179) in the step loop."""
+    so, sr = pair(sort_interval=3, **case)
+    for s in (so, sr):
+        s.clean_div_e_interval, s.clean_div_b_interval, s.sync_shared_interval = 2, 3, 2
+        s.initialize(full=True)
+    compare(so, sr, "after initialize")
+    assert so.init_report == sr.init_report
+    for step in range(7):
+        so.advance(); sr.advance()
+        compare(so, sr, f"step {step}")
+        assert (so.last_div_e_err, so.last_div_b_err, so.last_sync_err) == (sr.last_div_e_err, sr.last_div_b_err, sr.last_sync_err)
+    assert so.energies() == sr.energies()

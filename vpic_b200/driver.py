@@ -64,6 +64,10 @@ class Simulation:
         self.n_pipeline = n_pipeline
         self.species = []          # definition order; the reference's list head is the LAST one
         self.num_comm_round = 3    # src/vpic/vpic.cc:79
+        # divergence cleaning / shared-face synchronisation cadence (vpic.cc:72-78: off by default)
+        self.clean_div_e_interval = self.clean_div_b_interval = self.sync_shared_interval = 0
+        self.num_div_e_round = self.num_div_b_round = 2
+        self.last_div_e_err = self.last_div_b_err = self.last_sync_err = None
         self.g = self.fa = self.ia = self.aa = None
 
     # ---- setup (deck-like helpers, src/vpic/vpic.h:326-653) ----
@@ -149,9 +153,29 @@ class Simulation:
         s = self.sp_struct(sp)
         return abi.as_array(s.pm, s.nm, abi.mover_dtype)
 
-    # ---- initialize(): the tail of src/vpic/initialize.cc:33-54 ----
-    def initialize(self, uncenter=True):
+    # ---- initialize(): src/vpic/initialize.cc:14-54 ----
+    def initialize(self, uncenter=True, full=False):
+        """full=True runs the reference's whole post-deck sequence (shared-face
+        check, div B clean, tca and rhob initialisation, div E clean); the
+        default is its tail, which is all a deck with consistent fields needs."""
         be = self.be
+        if full:
+            fa = self.fa
+            self.init_report = rep = {}
+            rep["sync0"] = be.synchronize_tang_e_norm_b(fa)            # :16
+            be.compute_div_b_err(fa)                                    # :20-23
+            rep["div_b"] = be.compute_rms_div_b_err(fa)
+            be.clean_div_b(fa)
+            be.compute_curl_b(fa)                                       # :28
+            be.clear_rhof(fa)                                           # :31-34
+            for sp in self.species_in_list_order():
+                be.accumulate_rho_p(fa, sp)
+            be.synchronize_rho(fa)
+            be.compute_rhob(fa)
+            be.compute_div_e_err(fa)                                    # :40-43
+            rep["div_e"] = be.compute_rms_div_e_err(fa)
+            be.clean_div_e(fa)
+            rep["sync1"] = be.synchronize_tang_e_norm_b(fa)            # :46
         be.load_interpolator_array(self.ia, self.fa)
         if uncenter:
             for sp in self.species_in_list_order():
@@ -179,6 +203,25 @@ class Simulation:
         be.advance_b(self.fa, 0.5)                                    # :123
         be.advance_e(self.fa, 1.0)                                    # :127
         be.advance_b(self.fa, 0.5)                                    # :137
+        step = g.step
+        if self.clean_div_e_interval > 0 and step % self.clean_div_e_interval == 0:      # :141-157
+            be.clear_rhof(self.fa)
+            for sp in self.species_in_list_order():
+                be.accumulate_rho_p(self.fa, sp)
+            be.synchronize_rho(self.fa)
+            for rnd in range(self.num_div_e_round):
+                be.compute_div_e_err(self.fa)
+                if rnd == 0 or rnd == self.num_div_e_round - 1:
+                    self.last_div_e_err = be.compute_rms_div_e_err(self.fa)
+                be.clean_div_e(self.fa)
+        if self.clean_div_b_interval > 0 and step % self.clean_div_b_interval == 0:      # :161-171
+            for rnd in range(self.num_div_b_round):
+                be.compute_div_b_err(self.fa)
+                if rnd == 0 or rnd == self.num_div_b_round - 1:
+                    self.last_div_b_err = be.compute_rms_div_b_err(self.fa)
+                be.clean_div_b(self.fa)
+        if self.sync_shared_interval > 0 and step % self.sync_shared_interval == 0:      # :175-179
+            self.last_sync_err = be.synchronize_tang_e_norm_b(self.fa)
         be.load_interpolator_array(self.ia, self.fa)                  # :185
         g.step += 1                                                   # :187
 
