@@ -152,6 +152,7 @@ vpb_accumulator_array_t * vpic_b200_new_accumulator_array( vpb_grid_t * g, int n
 void vpic_b200_delete_accumulator_array( vpb_accumulator_array_t * aa );
 /* one-material list helper: src/material/material.c */
 vpb_material_t * vpic_b200_new_material( const char * name, float eps, float mu, float sigma );
+vpb_material_t * vpic_b200_append_material( vpb_material_t * m, vpb_material_t ** m_list );   /* material.c:69-86 */
 
 #ifdef __cplusplus
 }

@@ -105,10 +105,11 @@ class RefHost:
     def set_pbc(self, g, boundary, pbc):
         self.L.set_pbc(g, boundary, pbc)
 
-    def material_list(self, eps=1.0, mu=1.0, sigma=0.0):
-        m = self.L.material(b"vacuum", eps, eps, eps, mu, mu, mu, sigma, sigma, sigma, 0.0, 0.0, 0.0)
+    def material_list(self, eps=1.0, mu=1.0, sigma=0.0, more=()):
         head = _P(None)
-        self.L.append_material(m, C.byref(head))
+        for name, e, m_, sg in (("vacuum", eps, mu, sigma),) + tuple(more):
+            m = self.L.material(name.encode(), e, e, e, m_, m_, m_, sg, sg, sg, 0.0, 0.0, 0.0)
+            self.L.append_material(m, C.byref(head))
         return head.value
 
     def field_array(self, g, m_list, damp):

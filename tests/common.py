@@ -6,7 +6,7 @@ from vpic_b200 import Simulation, abi
 
 def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0.95, damp=0.0,
              species=(("electron", -1.0, 1.0), ("ion", 1.0, 100.0)), ppc=8, max_np_factor=1.5,
-             sort_interval=0, n_pipeline=1, topo=(1, 1, 1), max_nm=None):
+             sort_interval=0, n_pipeline=1, topo=(1, 1, 1), max_nm=None, materials=()):
     nx, ny, nz = n
     L = length if length is not None else tuple(0.5 * k for k in n)
     dx = [L[a] / n[a] for a in range(3)]
@@ -14,7 +14,7 @@ def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0
     dt = dt_frac / np.sqrt(inv) if inv > 0 else dt_frac * dx[0]
     s = Simulation(be, host, n_pipeline=n_pipeline)
     s.define_grid(kind, (0, 0, 0), L, n, topo=topo, dt=float(np.float32(dt)))
-    s.define_fields(damp=damp)
+    s.define_fields(damp=damp, materials=materials)
     ncell = nx * ny * nz
     for name, q, m in species:
         s.define_species(name, q, m, int(max_np_factor * ppc * ncell) + 64, max_nm=max_nm, sort_interval=sort_interval)
@@ -46,6 +46,17 @@ def random_fields(sim, seed, amp=0.05):
     for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "tcax", "tcay", "tcaz", "jfx", "jfy", "jfz"):
         f[k] = (amp * rng.standard_normal(g.nv)).astype(np.float32)
     return f
+
+
+def random_material_ids(sim, n_mat, seed):
+    """Random material ids 0..n_mat-1 on every edge / node / face / cell of the field array."""
+    rng = np.random.default_rng(seed)
+    f = sim.fields()
+    ids = {k: rng.integers(0, n_mat, len(f)).astype(np.int16)
+           for k in ("ematx", "ematy", "ematz", "nmat", "fmatx", "fmaty", "fmatz", "cmat")}
+    for k, v in ids.items():
+        f[k] = v
+    return ids
 
 
 def same_bits(a, b):

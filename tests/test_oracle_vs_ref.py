@@ -4,7 +4,7 @@ function and over whole steps, bit for bit.  Needs oracle/_ref (only built where
 import numpy as np
 import pytest
 from oracle import harness as H
-from common import make_sim, random_particles, random_fields, same_bits
+from common import make_sim, random_particles, random_fields, random_material_ids, same_bits
 
 pytestmark = [pytest.mark.ref, pytest.mark.skipif(not H.have_ref(), reason="oracle/_ref not built")]
 
@@ -146,3 +146,30 @@ def test_whole_steps_with_full_initialize_and_cleaning(case):
         compare(so, sr, f"step {step}")
         assert (so.last_div_e_err, so.last_div_b_err, so.last_sync_err) == (sr.last_div_e_err, sr.last_div_b_err, sr.last_sync_err)
     assert so.energies() == sr.energies()
+
+
+MATERIALS = (("dielectric", 2.0, 1.5, 0.0), ("conductor", 1.0, 1.25, 0.3))
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[2], CASES[3], CASES[4]])
+def test_material_variants(case):
+    """More than one material: the per-point material kernels (advance_e,
+    energy_f, compute_div_e_err, compute_rhob, clean_div_e, compute_curl_b)
+    replace the vacuum ones (sfa.c:202-211)."""
+    so, sr = pair(materials=MATERIALS, **case)
+    ids = random_material_ids(so, 3, 5)
+    for k, v in ids.items():
+        sr.fields()[k] = v
+    _seed_charges(so, sr)
+    out = []
+    for s in (so, sr):
+        be, fa, res = s.be, s.fa, []
+        be.advance_b(fa, 0.5); be.advance_e(fa, 1.0); be.advance_b(fa, 0.5)
+        res += be.energy_f6(fa)
+        be.compute_div_e_err(fa); res.append(be.compute_rms_div_e_err(fa)); be.clean_div_e(fa)
+        be.compute_div_b_err(fa); res.append(be.compute_rms_div_b_err(fa)); be.clean_div_b(fa)
+        be.compute_rhob(fa); be.compute_curl_b(fa)
+        be.advance_e(fa, 1.0)
+        out.append(res)
+    assert same_bits(so.fields(), sr.fields())
+    assert out[0] == out[1]

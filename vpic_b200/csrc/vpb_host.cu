@@ -258,6 +258,20 @@ vpb_material_t * vpic_b200_new_material( const char * name, float eps, float mu,
   return m;
 }
 
+// material.c:69-86: ids count up from 0, the newest material is the list head
+vpb_material_t * vpic_b200_append_material( vpb_material_t * m, vpb_material_t ** m_list ) {
+  if( !m || !m_list ) VPB_ERROR( "Bad args" );
+  if( m->next ) VPB_ERROR( "Material \"%s\" already in a list", m->name );
+  for( const vpb_material_t * k=*m_list; k; k=k->next )
+    if( strcmp( k->name, m->name )==0 ) VPB_ERROR( "There is already a material named \"%s\" in list", m->name );
+  const int id = *m_list ? (*m_list)->id+1 : 0;
+  if( id>=32767 ) VPB_ERROR( "Too many materials in list to append material \"%s\"", m->name );
+  m->id = (vpb_material_id)id;
+  m->next = *m_list;
+  *m_list = m;
+  return m;
+}
+
 // sfa.c:55-151 (coefficients) and :191-216 (constructor)
 vpb_field_array_t * new_standard_field_array( vpb_grid_t * g, const vpb_material_t * m_list, float damp ) {
   if( !g || !m_list || damp<0 ) VPB_ERROR( "Bad args" );

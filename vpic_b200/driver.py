@@ -38,8 +38,12 @@ class B200Host:
     def set_pbc(self, g, boundary, pbc):
         self.L.vpic_b200_set_pbc(g, boundary, pbc)
 
-    def material_list(self, eps=1.0, mu=1.0, sigma=0.0):
-        return self.L.vpic_b200_new_material(b"vacuum", eps, mu, sigma)
+    def material_list(self, eps=1.0, mu=1.0, sigma=0.0, more=()):
+        """"vacuum" (id 0) plus the (name, eps, mu, sigma) materials of `more` (ids 1..)."""
+        head = _P(None)
+        for name, e, m, sg in (("vacuum", eps, mu, sigma),) + tuple(more):
+            self.L.vpic_b200_append_material(self.L.vpic_b200_new_material(name.encode(), e, m, sg), C.byref(head))
+        return head.value
 
     def field_array(self, g, m_list, damp):
         return self.L.new_standard_field_array(g, m_list, damp)
@@ -91,8 +95,8 @@ class Simulation:
     def grid_struct(g):
         return C.cast(g, C.POINTER(abi.Grid)).contents
 
-    def define_fields(self, damp=0.0, eps=1.0, mu=1.0, sigma=0.0):
-        self.m_list = self.host.material_list(eps, mu, sigma)
+    def define_fields(self, damp=0.0, eps=1.0, mu=1.0, sigma=0.0, materials=()):
+        self.m_list = self.host.material_list(eps, mu, sigma, materials)
         self.fa = self.host.field_array(self.g, self.m_list, damp)
         self.ia = self.host.interpolator_array(self.g)
         self.aa = self.host.accumulator_array(self.g, self.n_pipeline)

@@ -58,6 +58,7 @@ def load_b200():
         "vpic_b200_new_interpolator_array": (_P, [_P]), "vpic_b200_delete_interpolator_array": (None, [_P]),
         "vpic_b200_new_accumulator_array": (_P, [_P, i]), "vpic_b200_delete_accumulator_array": (None, [_P]),
         "vpic_b200_new_material": (_P, [C.c_char_p, f, f, f]),
+        "vpic_b200_append_material": (_P, [_P, C.POINTER(_P)]),
         "new_standard_field_array": (_P, [_P, _P, f]), "delete_field_array": (None, [_P]),
     }
     for name, (res, args) in sig.items():
