@@ -1,0 +1,65 @@
+"""Drop-in check on a B200: the UNMODIFIED reference driver (vpic_simulation,
+src/vpic/*.cc) and the reference's own Weibel test deck
+(test/unit/energy_comparison/weibel_driver.cc), linked with libvpic_b200.so
+ahead of the reference library (oracle/Makefile: deckrun_weibel_b200), so that
+every hot-path entry point and the field kernel table resolve to the CUDA
+implementation.  The executable is built where /root/reference exists and
+travels to the GPU box; nothing here reads /root/reference at run time."""
+import os
+import subprocess
+import numpy as np
+import pytest
+from weibel import gold_lines
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "oracle", "_ref", "deckrun_weibel_b200")
+
+
+def run_deck(tmp_path, **env):
+    if not os.path.exists(EXE):
+        pytest.skip("oracle/_ref/deckrun_weibel_b200 not built (needs /root/reference at build time)")
+    e = dict(os.environ)
+    e.update(env)
+    cuda_rt = []
+    try:
+        import nvidia.cuda_runtime as rt_pkg
+        cuda_rt.append(os.path.join(list(rt_pkg.__path__)[0], "lib"))
+    except Exception:
+        pass
+    e["LD_LIBRARY_PATH"] = ":".join(cuda_rt + ["/usr/local/cuda/lib64", e.get("LD_LIBRARY_PATH", "")])
+    e["VPIC_B200_REPORT"] = "1"
+    r = subprocess.run([EXE, "dropin", "0"], cwd=tmp_path, env=e, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    # the library's exit line: the 700 steps really ran as CUDA kernels
+    rep = [l for l in r.stderr.splitlines() if l.startswith("[vpic_b200]")]
+    assert rep, r.stderr[-2000:]
+    assert int(rep[-1].split(":")[1].split()[0]) > 700 * 20, rep[-1]
+    print(rep[-1])
+    return open(os.path.join(tmp_path, "energies")).read().splitlines(keepends=True)
+
+
+def body(lines):
+    return [l for l in lines if l and not l.startswith("%")]
+
+
+def test_reference_driver_and_deck_on_the_device_reproduce_energies_gold(tmp_path):
+    """PARITY deposit, STRICT coherence (the defaults a host program that never
+    calls the control surface gets, plus VPIC_B200_DEPOSIT): the reference's
+    700-step golden energy history, byte for byte."""
+    got = run_deck(tmp_path, VPIC_B200_DEPOSIT="parity", VPIC_B200_COHERENCE="strict")
+    assert body(got) == body(gold_lines())
+
+
+def test_reference_driver_fast_deposit_meets_the_reference_criteria(tmp_path):
+    got = np.array([[float(x) for x in l.split()] for l in body(run_deck(tmp_path, VPIC_B200_DEPOSIT="fast"))])
+    gold = np.array([[float(x) for x in l.split()] for l in body(gold_lines())])
+    assert got.shape == gold.shape
+    early = slice(0, 101)                       # weibel_driver.cc:328-352 bands on the deterministic part of the run
+    e_g, e_r = got[early, 1:4].sum(1), gold[early, 1:4].sum(1)
+    b_g, b_r = got[early, 4:7].sum(1), gold[early, 4:7].sum(1)
+    nz = e_r > 0
+    assert np.all(np.abs(e_g[nz] - e_r[nz]) <= 0.3 * e_r[nz])
+    nz = b_r > 0
+    assert np.all(np.abs(b_g[nz] - b_r[nz]) <= 0.03 * b_r[nz])
+    assert np.all(np.abs(got[:, 7:9] - gold[:, 7:9]) <= 2e-3 * gold[:, 7:9])

@@ -451,7 +451,8 @@ void accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp ) {
   SpeciesMirror * ms = mirror( const_cast<vpb_species_t *>( sp ) );
   to_device( ms );
   const GridDev & g = m->grid->dev;
-  if( ms->np>0 ) {
+  if( ms->np>0 && r.deposit_mode==VPB_DEPOSIT_PARITY ) accumulate_rho_p_parity( m, ms, sp->q*sp->g->r8V );
+  else if( ms->np>0 ) {
     const long long nthread = ( (long long)ms->np + RP_K - 1 )/RP_K;
     k_accumulate_rho_p<<< div_up( nthread, 256 ), 256, 0, r.stream >>>( m->comp( F_RHOF ), ms->d_p, ms->np, g.sy, g.sz, sp->q*sp->g->r8V );
     VPB_CHECK_LAUNCH(); r.launches++;

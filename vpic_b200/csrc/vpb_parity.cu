@@ -294,6 +294,70 @@ void advance_p_parity( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, co
   VPB_CHECK_LAUNCH(); r.launches++;
 }
 
+// ---- accumulate_rho_p in the reference's order (rho_p.cc:22-112) -------------
+// The reference adds each particle's eight node charges in particle order, so
+// per node the sum runs over contributing (particle, corner) records in
+// ascending record index.  Records of a chunk of particles are binned by node,
+// each node's list is put in order by one warp and added sequentially; chunks
+// follow one another in particle order, so the result is bit-identical.
+__global__ void __launch_bounds__(256)
+k_rho_records( int * __restrict__ key, float * __restrict__ val, const vpb_particle_t * __restrict__ p, int n,
+               int sy, int sz, float q_8V ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if( i>=n ) return;
+  float w0 = p[i].dx, w1 = p[i].dy, w2, w3, w4, w5, w6, w7 = p[i].w*q_8V; const float dz = p[i].dz;
+  const int v = p[i].i;
+  w6 = w7 - w0*w7; w7 = w7 + w0*w7;
+  w4 = w6 - w1*w6; w5 = w7 - w1*w7;
+  w6 = w6 + w1*w6; w7 = w7 + w1*w7;
+  w0 = w4 - dz*w4; w1 = w5 - dz*w5; w2 = w6 - dz*w6; w3 = w7 - dz*w7;
+  w4 = w4 + dz*w4; w5 = w5 + dz*w5; w6 = w6 + dz*w6; w7 = w7 + dz*w7;
+  int * k = key + 8*(size_t)i; float * o = val + 8*(size_t)i;
+  k[0] = v;    k[1] = v+1;    k[2] = v+sy;    k[3] = v+sy+1;
+  k[4] = v+sz; k[5] = v+sz+1; k[6] = v+sz+sy; k[7] = v+sz+sy+1;
+  o[0] = w0; o[1] = w1; o[2] = w2; o[3] = w3; o[4] = w4; o[5] = w5; o[6] = w6; o[7] = w7;
+}
+
+__global__ void __launch_bounds__(32*FIX_WARPS)
+k_rho_sum( const int * __restrict__ start, int nbin, int nrec, int * __restrict__ perm, int * __restrict__ big_scratch,
+           const float * __restrict__ rec_val, float * __restrict__ rhof ) {
+  __shared__ int s[FIX_WARPS][FIX_SMEM];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int bin = blockIdx.x*FIX_WARPS + w;
+  if( bin>=nbin ) return;
+  const int b = start[bin], e = bin+1<nbin ? start[bin+1] : nrec, n = e-b;
+  if( n<=0 ) return;
+  int n2 = 32; while( n2<n ) n2 <<= 1;
+  int * a = n2<=FIX_SMEM ? s[w] : big_scratch + 2*(size_t)b;
+  for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+  __threadfence_block(); __syncwarp();
+  bitonic_mem( a, n2, lane );
+  if( lane==0 ) {
+    float v = rhof[bin];
+    for( int t=0; t<n; t++ ) v = v + rec_val[ a[t] ];
+    rhof[bin] = v;
+  }
+}
+
+void accumulate_rho_p_parity( FieldMirror * mf, SpeciesMirror * ms, float q_8V ) {
+  Runtime & r = rt();
+  const GridDev & g = mf->grid->dev;
+  const int CHUNK = 1<<22;                            // particles per pass (32 M records)
+  for( long long first=0; first<ms->np; first+=CHUNK ) {
+    const int n = ms->np-first<CHUNK ? (int)( ms->np-first ) : CHUNK, nrec = 8*n;
+    int   * key = (int *)need( B_bin, sizeof(int)*( (size_t)nrec+32 ) );
+    float * val = (float *)need( B_val, sizeof(float)*( (size_t)nrec+32 ) );
+    k_rho_records<<< div_up( n, 256 ), 256, 0, r.stream >>>( key, val, ms->d_p + first, n, g.sy, g.sz, q_8V );
+    VPB_CHECK_LAUNCH(); r.launches++;
+    int * start = (int *)need( B_start, sizeof(int)*( (size_t)g.nv+64 ) );
+    int * perm  = (int *)need( B_perm, sizeof(int)*( (size_t)nrec+32 ) );
+    int * big   = (int *)need( B_big, sizeof(int)*( 2*(size_t)nrec+64 ) );
+    bin_indices( key, nrec, g.nv, start, perm );
+    k_rho_sum<<< div_up( g.nv, FIX_WARPS ), 32*FIX_WARPS, 0, r.stream >>>( start, g.nv, nrec, perm, big, val, mf->comp( F_RHOF ) );
+    VPB_CHECK_LAUNCH(); r.launches++;
+  }
+}
+
 void reduce_accumulators_parity( AccMirror * ma ) {
   Runtime & r = rt();
   if( !ma->d_priv || ma->n_priv<1 ) return;

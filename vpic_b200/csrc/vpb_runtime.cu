@@ -37,6 +37,25 @@ void ensure_init() {
   VPB_CUDA( cudaStreamCreateWithFlags( &r.stream, cudaStreamNonBlocking ) );
   VPB_CUDA( cudaStreamCreateWithFlags( &r.copy_stream[0], cudaStreamNonBlocking ) );
   VPB_CUDA( cudaStreamCreateWithFlags( &r.copy_stream[1], cudaStreamNonBlocking ) );
+  // A host program that links the library in place of the reference's own
+  // kernels never calls the control surface: the same switches as environment
+  // variables.
+  if( const char * e = getenv( "VPIC_B200_COHERENCE" ) ) {
+    if( !strcmp( e, "resident" ) ) r.coherence = VPB_COHERENCE_RESIDENT;
+    else if( !strcmp( e, "strict" ) ) r.coherence = VPB_COHERENCE_STRICT;
+    else VPB_ERROR( "VPIC_B200_COHERENCE must be strict or resident, not \"%s\"", e );
+  }
+  if( const char * e = getenv( "VPIC_B200_DEPOSIT" ) ) {
+    if( !strcmp( e, "parity" ) ) r.deposit_mode = VPB_DEPOSIT_PARITY;
+    else if( !strcmp( e, "fast" ) ) r.deposit_mode = VPB_DEPOSIT_FAST;
+    else VPB_ERROR( "VPIC_B200_DEPOSIT must be fast or parity, not \"%s\"", e );
+  }
+  if( getenv( "VPIC_B200_REPORT" ) )      // one line at exit: proof of where the work ran
+    atexit( [](){ Runtime & q = rt();
+                  fprintf( stderr, "[vpic_b200] device %d: %lld kernel launches, %lld bytes host->device, %lld bytes device->host, coherence %s, deposit %s\n",
+                           q.device, q.launches, q.h2d_bytes, q.d2h_bytes,
+                           q.coherence==VPB_COHERENCE_STRICT ? "strict" : "resident",
+                           q.deposit_mode==VPB_DEPOSIT_PARITY ? "parity" : "fast" ); } );
   r.initialised = true;
 }
 

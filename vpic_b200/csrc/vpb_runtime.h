@@ -183,6 +183,7 @@ template<class M> inline void finish_write( M * m ) {
 struct PushCoef;
 void advance_p_parity( SpeciesMirror *, AccMirror *, InterpMirror *, const PushCoef & );
 void reduce_accumulators_parity( AccMirror * );
+void accumulate_rho_p_parity( FieldMirror * mf, SpeciesMirror * ms, float q_8V );   // reference summation order
 void energy_f_parity( double * en6, FieldMirror * m );           // local (pre-allreduce) energies, reference summation order
 double energy_p_parity( SpeciesMirror * ms, InterpMirror * mi, float qdt_2mc, float msp );
 // counting-sort front end shared by sort_p and the PARITY deposit: start[0..nbin] = first slot of each bin,
