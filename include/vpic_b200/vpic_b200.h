@@ -58,6 +58,10 @@ void delete_field_array( vpb_field_array_t * fa );
 /* The kernel-table entries themselves (global symbols: the reference
    checkpoints function pointers by name, src/field_advance/field_advance.c:17-58). */
 void vpic_b200_delete_fa( vpb_field_array_t * fa );
+/* checkpoint / restore hooks registered with the reference's checkpt service when the
+   host program has one (sfa.c:161-188; src/util/checkpt/checkpt.h:150-175) */
+void   vpic_b200_checkpt_fa( const void * fa );
+void * vpic_b200_restore_fa( void );
 void vpic_b200_advance_b( vpb_field_array_t * fa, float frac );       /* advance_b.cc:10-19     */
 void vpic_b200_advance_e( vpb_field_array_t * fa, float frac );       /* advance_e.cc:10-25     */
 void vpic_b200_energy_f( double * en, const vpb_field_array_t * fa ); /* energy_f.c:12-23       */

@@ -16,9 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 EXE = os.path.join(ROOT, "oracle", "_ref", "deckrun_weibel_b200")
 
 
-def run_deck(tmp_path, **env):
-    if not os.path.exists(EXE):
-        pytest.skip("oracle/_ref/deckrun_weibel_b200 not built (needs /root/reference at build time)")
+def deck_env(**env):
     e = dict(os.environ)
     e.update(env)
     cuda_rt = []
@@ -29,13 +27,23 @@ def run_deck(tmp_path, **env):
         pass
     e["LD_LIBRARY_PATH"] = ":".join(cuda_rt + ["/usr/local/cuda/lib64", e.get("LD_LIBRARY_PATH", "")])
     e["VPIC_B200_REPORT"] = "1"
-    r = subprocess.run([EXE, "dropin", "0"], cwd=tmp_path, env=e, capture_output=True, text=True, timeout=900)
-    assert r.returncode == 0, r.stderr[-3000:]
-    # the library's exit line: the 700 steps really ran as CUDA kernels
-    rep = [l for l in r.stderr.splitlines() if l.startswith("[vpic_b200]")]
-    assert rep, r.stderr[-2000:]
-    assert int(rep[-1].split(":")[1].split()[0]) > 700 * 20, rep[-1]
+    return e
+
+
+def launches(stderr, at_least):
+    """The library's exit line: the steps really ran as CUDA kernels."""
+    rep = [l for l in stderr.splitlines() if l.startswith("[vpic_b200]")]
+    assert rep, stderr[-2000:]
+    assert int(rep[-1].split(":")[1].split()[0]) > at_least, rep[-1]
     print(rep[-1])
+
+
+def run_deck(tmp_path, **env):
+    if not os.path.exists(EXE):
+        pytest.skip("oracle/_ref/deckrun_weibel_b200 not built (needs /root/reference at build time)")
+    r = subprocess.run([EXE, "dropin", "0"], cwd=tmp_path, env=deck_env(**env), capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-3000:]
+    launches(r.stderr, 700 * 20)
     return open(os.path.join(tmp_path, "energies")).read().splitlines(keepends=True)
 
 
@@ -63,3 +71,29 @@ def test_reference_driver_fast_deposit_meets_the_reference_criteria(tmp_path):
     nz = b_r > 0
     assert np.all(np.abs(b_g[nz] - b_r[nz]) <= 0.03 * b_r[nz])
     assert np.all(np.abs(got[:, 7:9] - gold[:, 7:9]) <= 2e-3 * gold[:, 7:9])
+
+
+def test_reference_harris_deck_every_output_file_identical(tmp_path):
+    """The reference's sample/harris deck, built from the unmodified reference
+    program (deck/main.cc + deck/wrapper.cc + src/vpic) with libvpic_b200.so
+    ahead of the reference library: PEC + reflecting walls, divergence cleaning
+    and shared-face synchronisation every 24 steps, 480 steps.  With the PARITY
+    deposit every diagnostic file the reference's own host code writes from the
+    host arrays (energies, 21 field dumps, 42 hydro dumps, 42 particle dumps)
+    has the SHA-256 of the pure-CPU reference run (tests/golden/harris_outputs.json,
+    made by make_harris_golden.py)."""
+    import hashlib
+    import json
+    exe = os.path.join(ROOT, "oracle", "_ref", "deckrun_harris_b200")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/deckrun_harris_b200 not built (needs /root/reference at build time)")
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "harris_outputs.json")))
+    r = subprocess.run([exe, "--tpp", "1"], cwd=tmp_path, env=deck_env(VPIC_B200_DEPOSIT="parity", VPIC_B200_COHERENCE="strict"),
+                       capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
+    launches(r.stderr, 480 * 20)
+    assert open(os.path.join(tmp_path, "energies")).read() == gold["energies"]
+    bad = [n for n, h in gold["files"].items()
+           if hashlib.sha256(open(os.path.join(tmp_path, n), "rb").read()).hexdigest() != h]
+    assert not bad, bad
+    assert len(gold["files"]) == 106

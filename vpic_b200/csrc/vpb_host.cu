@@ -11,6 +11,25 @@
 #include <cmath>
 #include <climits>
 
+// The reference's checkpoint service (src/util/checkpt/checkpt.h:150-260).  A
+// host program built from the reference carries these symbols and expects every
+// object its simulation points at to be registered with them (a deck's
+// checkpt() call fails on "a pointer to an unregistered object" otherwise);
+// they are weak so that the library also loads on its own.
+extern "C" {
+typedef void   (*vpb_checkpt_func_t)( const void * obj );
+typedef void * (*vpb_restore_func_t)( void );
+typedef void   (*vpb_reanimate_func_t)( void * obj );
+void   register_object( void * obj, vpb_checkpt_func_t, vpb_restore_func_t, vpb_reanimate_func_t ) __attribute__((weak));
+void   unregister_object( void * obj ) __attribute__((weak));
+void   checkpt_data( const void * data, size_t sz_ele, size_t str_ele, size_t n_ele, size_t max_ele, size_t align ) __attribute__((weak));
+void * restore_data( void ) __attribute__((weak));
+void   checkpt_ptr( const void * ptr ) __attribute__((weak));
+void * restore_ptr( void ) __attribute__((weak));
+void   checkpt_sym( const void * saddr ) __attribute__((weak));
+void * restore_sym( void ) __attribute__((weak));
+}
+
 using namespace vpb;
 
 namespace {
@@ -303,6 +322,8 @@ vpb_field_array_t * new_standard_field_array( vpb_grid_t * g, const vpb_material
   }
   fa->params = p;
   memset( fa->kernel, 0, sizeof(fa->kernel) );
+  if( register_object && checkpt_data && checkpt_ptr && checkpt_sym )
+    register_object( fa, vpic_b200_checkpt_fa, vpic_b200_restore_fa, nullptr );
   fa->kernel->delete_fa      = vpic_b200_delete_fa;
   fa->kernel->advance_b      = vpic_b200_advance_b;
   fa->kernel->advance_e      = vpic_b200_advance_e;
@@ -323,8 +344,39 @@ vpb_field_array_t * new_standard_field_array( vpb_grid_t * g, const vpb_material
   return fa;
 }
 
+// sfa.c:161-188 (checkpt_standard_field_array / restore_standard_field_array)
+// with field_advance.c:17-58 for the kernel table; the host copy is made
+// current first, the device mirror of a restored array is rebuilt on first use.
+void vpic_b200_checkpt_fa( const void * obj ) {
+  const vpb_field_array_t * fa = (const vpb_field_array_t *)obj;
+  if( !fa || !checkpt_data ) VPB_ERROR( "Bad args" );
+  vpic_b200_sync_to_host( const_cast<vpb_field_array_t *>( fa ) );
+  const vpb_sfa_params_t * p = (const vpb_sfa_params_t *)fa->params;
+  checkpt_data( fa, sizeof(*fa), sizeof(*fa), 1, 1, 0 );
+  { const size_t sz = sizeof(vpb_field_t)*(size_t)fa->g->nv; checkpt_data( fa->f, sz, sz, 1, 1, 128 ); }
+  checkpt_ptr( fa->g );
+  checkpt_data( p, sizeof(*p), sizeof(*p), 1, 1, 0 );
+  { const size_t sz = sizeof(vpb_material_coefficient_t)*(size_t)p->n_mc; checkpt_data( p->mc, sz, sz, 1, 1, 128 ); }
+  void * const * k = (void * const *)fa->kernel;
+  for( size_t i=0; i<sizeof(vpb_field_advance_kernels_t)/sizeof(void *); i++ ) checkpt_sym( k[i] );
+}
+
+void * vpic_b200_restore_fa( void ) {
+  if( !restore_data || !restore_ptr || !restore_sym ) VPB_ERROR( "no checkpoint service in this program" );
+  vpb_field_array_t * fa = (vpb_field_array_t *)restore_data();
+  fa->f = (vpb_field_t *)restore_data();
+  fa->g = (vpb_grid_t *)restore_ptr();
+  vpb_sfa_params_t * p = (vpb_sfa_params_t *)restore_data();
+  p->mc = (vpb_material_coefficient_t *)restore_data();
+  fa->params = p;
+  void ** k = (void **)fa->kernel;
+  for( size_t i=0; i<sizeof(vpb_field_advance_kernels_t)/sizeof(void *); i++ ) k[i] = restore_sym();
+  return fa;
+}
+
 void vpic_b200_delete_fa( vpb_field_array_t * fa ) {
   if( !fa ) return;
+  if( unregister_object && register_object ) unregister_object( fa );
   vpic_b200_forget( fa );
   vpb_sfa_params_t * p = (vpb_sfa_params_t *)fa->params;
   if( p ) { free( p->mc ); free( p ); }
