@@ -166,6 +166,21 @@ typedef struct vpb_field_advance_kernels {
   void   (*clean_div_b)( struct vpb_field_array * fa );
 } vpb_field_advance_kernels_t;
 
+/* particle_bc_t, src/boundary/boundary_private.h:14-44: a user handler for
+   particles that hit a face whose neighbor[] code is id (<= -3).  interact()
+   is a HOST function of the host program; boundary_p calls it for every such
+   particle in the reference's order and injects what it returns. */
+struct vpb_species;
+typedef int (*vpb_particle_bc_func_t)( void * params, struct vpb_species * sp, vpb_particle_t * p, vpb_particle_mover_t * pm,
+                                       vpb_particle_injector_t * pi, int max_pi, int face );
+typedef struct vpb_particle_bc {
+  void * params;
+  vpb_particle_bc_func_t interact;
+  void (*delete_pbc)( struct vpb_particle_bc * pbc );
+  int64_t id;
+  struct vpb_particle_bc * next;
+} vpb_particle_bc_t;
+
 typedef struct vpb_field_array {
   vpb_field_t                *f;
   vpb_grid_t                 *g;

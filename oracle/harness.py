@@ -218,3 +218,31 @@ def set_world(rank, size):
     L.orc_set_world.argtypes = [C.c_int, C.c_int]
     L.orc_set_world(rank, size)
     load_b200().vpic_b200_set_world(rank, size)
+
+
+# ---- user particle-boundary handlers for tests --------------------------------
+
+def fixture_bounce_handler():
+    """Address of oracle/orc_boundary.c's deterministic test handler and a
+    6-int hit counter to pass as its params."""
+    L = _load(ORACLE_LIB)
+    counts = (C.c_int * 6)()
+    return C.cast(L.orc_fixture_bounce_handler, _P).value, counts
+
+
+def reference_maxwellian_reflux(sim, ut_para, ut_perp, seed=7):
+    """The REFERENCE's own maxwellian_reflux handler (src/boundary/maxwellian_reflux.c)
+    with its own rng pool, attached to `sim` (any backend: the handler is a host
+    callback that only sees the POD structs).  Needs oracle/_ref."""
+    ref_backend()                                       # boots the reference library once
+    L = _load(REF_SCALAR)
+    L.new_rng_pool.restype, L.new_rng_pool.argtypes = _P, [C.c_int, C.c_int, C.c_int]
+    L.maxwellian_reflux.restype, L.maxwellian_reflux.argtypes = _P, [_P, _P]
+    L.set_reflux_temp.restype, L.set_reflux_temp.argtypes = None, [_P, _P, C.c_float, C.c_float]
+    rp = L.new_rng_pool(1, seed, 0)
+    pbc = L.maxwellian_reflux(sim.sp_list_head, rp)
+    for sp in sim.species:
+        L.set_reflux_temp(pbc, sp, ut_para, ut_perp)
+    from vpic_b200 import abi
+    s = C.cast(pbc, C.POINTER(abi.ParticleBC)).contents
+    return s.interact, s.params

@@ -63,6 +63,13 @@ static void orc_exchange_var( int X, int rem_lo, int rem_hi,
    reverse), received injectors appended in reverse order and finished with
    move_p on accumulator copy 0. */
 void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa ) {
+  orc_boundary_p_pbc( NULL, sp_list, fa, aa );
+}
+
+/* The same with the user handler list (boundary_p.cc:81-89, 236-253, 426-432):
+   a particle that hits a face whose neighbor[] code is a handler id is given
+   to that handler; the injectors the handlers return are injected first. */
+void orc_boundary_p_pbc( vpb_particle_bc_t * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa ) {
   if( !sp_list ) return;
   if( !fa || !aa || sp_list->g!=aa->g || fa->g!=aa->g ) ORC_FAIL( "Bad args" );
   static const int f2b[6] = { VPB_BOUNDARY(-1,0,0), VPB_BOUNDARY(0,-1,0), VPB_BOUNDARY(0,0,-1),
@@ -80,6 +87,15 @@ void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumu
   }
   int nm_tot = 0;
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) nm_tot += sp->nm;
+  enum { ORC_MAX_PBC = 32 };
+  vpb_particle_bc_func_t pbc_interact[ORC_MAX_PBC] = { 0 }; void * pbc_params[ORC_MAX_PBC] = { 0 };
+  int nb = pbc_list ? (int)( -pbc_list->id-2 ) : 0;
+  if( nb>ORC_MAX_PBC ) ORC_FAIL( "Update this to support more particle boundary conditions" );
+  for( vpb_particle_bc_t * pbc=pbc_list; pbc; pbc=pbc->next ) {
+    pbc_interact[-pbc->id-3] = pbc->interact; pbc_params[-pbc->id-3] = pbc->params;
+  }
+  vpb_particle_injector_t * ci = (vpb_particle_injector_t *)orc_alloc( sizeof(vpb_particle_injector_t)*(size_t)( nm_tot+1 ), 16 );
+  int n_ci = 0;
   vpb_particle_injector_t * pi_send[6]; int n_send[6], n_recv[6];
   vpb_particle_injector_t * pi_recv[6];
   for( int face=0; face<6; face++ ) {
@@ -105,6 +121,8 @@ void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumu
         (&pi->dx)[axis[face]] = dir[face];
         pi->i = (int32_t)( nn - range[face] );
         pi->sp_id = sp_id;
+      } else if( -nn-3>=0 && -nn-3<nb ) {
+        n_ci += pbc_interact[-nn-3]( pbc_params[-nn-3], sp, p0+i, pm, ci+n_ci, 1, face );
       } else fprintf( stderr, "oracle warning: unknown boundary interaction ... dropping particle (species=%s)\n", sp->name );
       np--;
       p0[i] = p0[np];
@@ -126,7 +144,7 @@ void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumu
   }
 
   /* grow storage for the worst case (boundary_p.cc:318-406; shrinking is not restated) */
-  int max_inj = 0;
+  int max_inj = n_ci;
   for( int face=0; face<6; face++ ) max_inj += n_recv[face];
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
     int n = sp->np + max_inj;
@@ -150,10 +168,12 @@ void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumu
     if( sp->id<0 || sp->id>=ORC_MAX_SP ) ORC_FAIL( "species id out of range" );
     by_id[sp->id] = sp;
   }
-  for( int face=0; face<6; face++ ) {
-    if( !shared[face] ) continue;
-    const vpb_particle_injector_t * pi = pi_recv[face] + n_recv[face] - 1;
-    for( int n=n_recv[face]; n; pi--, n-- ) {
+  for( int k=0; k<7; k++ ) {                             /* custom local injection first, then faces 0..5 */
+    const int fc = k==0 ? 6 : k-1;
+    if( fc<6 && !shared[fc] ) continue;
+    const int cnt = fc==6 ? n_ci : n_recv[fc];
+    const vpb_particle_injector_t * pi = ( fc==6 ? ci : pi_recv[fc] ) + cnt - 1;
+    for( int n=cnt; n; pi--, n-- ) {
       vpb_species_t * sp = ( pi->sp_id>=0 && pi->sp_id<ORC_MAX_SP ) ? by_id[pi->sp_id] : NULL;
       if( !sp ) ORC_FAIL( "received an injector for an unknown species" );
       vpb_particle_t * p = sp->p; vpb_particle_mover_t * pm = sp->pm; int np = sp->np, nm = sp->nm;
@@ -165,4 +185,24 @@ void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumu
     }
   }
   for( int face=0; face<6; face++ ) { free( pi_send[face] ); free( pi_recv[face] ); }
+  free( ci );
+}
+
+/* A deterministic user handler for tests: the particle comes back from the
+   wall with the momentum component along the face axis reversed and halved,
+   the other two scaled by 3/4, and a quarter of its remaining displacement
+   turned around; params counts the hits per face (int[6]). */
+int orc_fixture_bounce_handler( void * params, vpb_species_t * sp, vpb_particle_t * p, vpb_particle_mover_t * pm,
+                                vpb_particle_injector_t * pi, int max_pi, int face ) {
+  (void)sp;
+  if( max_pi<1 ) return 0;
+  if( params ) ( (int *)params )[face]++;
+  const int ax = face%3;
+  float u[3] = { 0.75f*p->ux, 0.75f*p->uy, 0.75f*p->uz }, d[3] = { 0.25f*pm->dispx, 0.25f*pm->dispy, 0.25f*pm->dispz };
+  u[ax] = -0.5f*(&p->ux)[ax];
+  d[ax] = -d[ax];
+  pi->dx = p->dx; pi->dy = p->dy; pi->dz = p->dz; pi->i = p->i;
+  pi->ux = u[0]; pi->uy = u[1]; pi->uz = u[2]; pi->w = p->w;
+  pi->dispx = d[0]; pi->dispy = d[1]; pi->dispz = d[2]; pi->sp_id = sp->id;
+  return 1;
 }

@@ -103,6 +103,11 @@ void   orc_set_allsum( void (*fn)( double * v, int n ) );
 /* F14 src/boundary/boundary_p.cc:36-518 (absorb/reflect/periodic/remote; no
        custom handlers) and F15 src/species_advance/standard/rho_p.cc:125-171 */
 void orc_boundary_p( vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa );
+/* ... with the user handler list (boundary_p.cc:81-89, 236-253, 426-432) */
+void orc_boundary_p_pbc( vpb_particle_bc_t * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa );
+/* a deterministic handler for tests (params: int[6] hit counters or NULL) */
+int  orc_fixture_bounce_handler( void * params, vpb_species_t * sp, vpb_particle_t * p, vpb_particle_mover_t * pm,
+                                 vpb_particle_injector_t * pi, int max_pi, int face );
 void orc_accumulate_rhob( vpb_field_t * f, const vpb_particle_t * p, const vpb_grid_t * g, float qsp );
 
 /* Material coefficient table, src/field_advance/standard/sfa.c:55-151.

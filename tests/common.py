@@ -6,14 +6,14 @@ from vpic_b200 import Simulation, abi
 
 def make_sim(be, host=None, kind="periodic", n=(6, 5, 4), length=None, dt_frac=0.95, damp=0.0,
              species=(("electron", -1.0, 1.0), ("ion", 1.0, 100.0)), ppc=8, max_np_factor=1.5,
-             sort_interval=0, n_pipeline=1, topo=(1, 1, 1), max_nm=None, materials=()):
+             sort_interval=0, n_pipeline=1, topo=(1, 1, 1), max_nm=None, materials=(), pbc=-2):
     nx, ny, nz = n
     L = length if length is not None else tuple(0.5 * k for k in n)
     dx = [L[a] / n[a] for a in range(3)]
     inv = sum(1.0 / d ** 2 for a, d in enumerate(dx) if n[a] > 1)
     dt = dt_frac / np.sqrt(inv) if inv > 0 else dt_frac * dx[0]
     s = Simulation(be, host, n_pipeline=n_pipeline)
-    s.define_grid(kind, (0, 0, 0), L, n, topo=topo, dt=float(np.float32(dt)))
+    s.define_grid(kind, (0, 0, 0), L, n, topo=topo, dt=float(np.float32(dt)), pbc=pbc)
     s.define_fields(damp=damp, materials=materials)
     ncell = nx * ny * nz
     for name, q, m in species:

@@ -433,3 +433,50 @@ def test_parity_mode_cleaning_free_running_bit_exact(parity_mode, case):
             assert same_bits(fg[k], fo[k]), k      # absorbing walls: rhob is summed with atomics (accumulate_rhob)
     for a, b in zip(so.species, sg.species):
         assert same_bits(sg.particles(b), so.particles(a))
+
+
+# ---- user particle-boundary handlers (host callbacks of the host program) ------
+
+@pytest.mark.parametrize("handler", ["fixture", "maxwellian_reflux"])
+@pytest.mark.parametrize("coherence", [0, 1])
+def test_custom_particle_boundary_handlers(gpu, handler, coherence):
+    """Particles that reach a wall with a user handler are handed to the host
+    callback in the reference's order and what it returns is injected first
+    (boundary_p.cc:236-253, 426-432).  (a) a deterministic test handler,
+    (b) the reference's own maxwellian_reflux (needs oracle/_ref), each side
+    with its own identically seeded instance; PARITY deposit so that the whole
+    free-running state stays bit-comparable; STRICT and RESIDENT coherence."""
+    import ctypes as C
+    if handler == "maxwellian_reflux" and not H.have_ref():
+        pytest.skip("oracle/_ref not built")
+    L = load_b200()
+    L.vpic_b200_set_deposit_mode(1)
+    try:
+        so, sg = pair(gpu, kind="absorbing", n=(8, 6, 5), damp=0.01, pbc=-3, sort_interval=3, max_nm=4000)
+        counts = []
+        for s in (so, sg):
+            if handler == "fixture":
+                fn, c = H.fixture_bounce_handler()
+                counts.append(c)
+                assert s.define_particle_bc(fn, C.addressof(c)) == -3
+            else:
+                fn, prm = H.reference_maxwellian_reflux(s, 0.05, 0.08)
+                assert s.define_particle_bc(fn, prm) == -3
+            s.num_comm_round = 8
+            s.initialize()
+        n0 = [so.sp_struct(a).np for a in so.species]
+        L.vpic_b200_set_coherence(coherence)
+        for step in range(10):
+            so.advance(); sg.advance()
+        for obj in [sg.fa, sg.ia, sg.aa] + sg.species:
+            L.vpic_b200_sync_to_host(obj)
+    finally:
+        L.vpic_b200_set_coherence(0)
+        L.vpic_b200_set_deposit_mode(0)
+    assert [sg.sp_struct(b).np for b in sg.species] == n0 == [so.sp_struct(a).np for a in so.species]
+    for a, b in zip(so.species, sg.species):
+        assert same_bits(sg.particles(b), so.particles(a))
+    for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "jfx", "jfy", "jfz"):
+        assert same_bits(sg.fields()[k], so.fields()[k]), k
+    if counts:
+        assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 100

@@ -1,6 +1,7 @@
 """Pin the CPU oracle (oracle/*.c) against the compiled reference, function by
 function and over whole steps, bit for bit.  Needs oracle/_ref (only built where
 /root/reference exists); the committed golden fixtures cover the other machines."""
+import ctypes as C
 import numpy as np
 import pytest
 from oracle import harness as H
@@ -173,3 +174,31 @@ def test_material_variants(case):
         out.append(res)
     assert same_bits(so.fields(), sr.fields())
     assert out[0] == out[1]
+
+
+@pytest.mark.parametrize("handler", ["fixture", "maxwellian_reflux"])
+def test_custom_particle_boundary_handlers(handler):
+    """boundary_p with user handlers (boundary_p.cc:236-253, 426-432): every
+    particle that reaches a wall goes to the handler, what it returns is
+    injected first.  Oracle against the compiled reference with (a) a
+    deterministic test handler and (b) the reference's own maxwellian_reflux,
+    each side with its own identically seeded instance."""
+    so, sr = pair(kind="absorbing", n=(8, 6, 5), damp=0.01, pbc=-3, sort_interval=3, max_nm=4000)
+    counts = []
+    for s in (so, sr):
+        if handler == "fixture":
+            fn, c = H.fixture_bounce_handler()
+            counts.append(c)
+            assert s.define_particle_bc(fn, C.addressof(c)) == -3
+        else:
+            fn, prm = H.reference_maxwellian_reflux(s, 0.05, 0.08)
+            assert s.define_particle_bc(fn, prm) == -3
+        s.num_comm_round = 8        # a refluxed particle near a corner can come back to a wall several times
+        s.initialize()
+    n0 = [so.sp_struct(a).np for a in so.species]
+    for step in range(10):
+        so.advance(); sr.advance()
+        compare(so, sr, f"step {step}")
+    assert [so.sp_struct(a).np for a in so.species] == n0          # every particle came back
+    if counts:
+        assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 100

@@ -83,6 +83,14 @@ class FieldAdvanceKernels(C.Structure):  # field_advance.h:170-218
     _fields_ = [(n, C.c_void_p) for n in KERNEL_NAMES]
 
 
+class ParticleBC(C.Structure):      # boundary_private.h:36-44
+    pass
+
+
+ParticleBC._fields_ = [("params", C.c_void_p), ("interact", C.c_void_p), ("delete_pbc", C.c_void_p),
+                       ("id", C.c_int64), ("next", C.POINTER(ParticleBC))]
+
+
 class FieldArray(C.Structure):      # field_advance.h:223-229
     _fields_ = [("f", C.POINTER(Field)), ("g", C.POINTER(Grid)), ("params", C.c_void_p),
                 ("kernel", FieldAdvanceKernels * 1)]

@@ -30,7 +30,8 @@ struct BndFaces {
   int kind[6];                        // ParticleFaceKind
   int nb_n[6];                        // neighbour extent along the face axis
   vpb_particle_injector_t * send[6];  // device message bodies
-  int * face_count;                   // [6] injectors packed so far (all species)
+  float4 * custom;                    // particles that hit a face with a user handler: 4 x float4 each
+  int * face_count;                   // [7] injectors packed so far (all species); [6] = custom entries
 };
 
 // Ranks of the threads of a block among those holding the same key (0..NKEY-1,
@@ -81,9 +82,9 @@ __device__ __forceinline__ void accumulate_rhob_dev( float * __restrict__ rhob, 
 __global__ void __launch_bounds__(BND_T)
 k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int nm,
                 int sp_id, float q_r8V, float * __restrict__ rhob, GridDev g, BndFaces a, int * __restrict__ n_unknown ) {
-  __shared__ int s_w[BND_T/32][6];
-  __shared__ int s_tot[6], s_base[6];
-  if( threadIdx.x<6 ) s_base[threadIdx.x] = a.face_count[threadIdx.x];
+  __shared__ int s_w[BND_T/32][7];
+  __shared__ int s_tot[7], s_base[7];
+  if( threadIdx.x<7 ) s_base[threadIdx.x] = a.face_count[threadIdx.x];
   __syncthreads();
   for( int c0=0; c0<nm; c0+=BND_T ) {
     const int r = c0 + threadIdx.x;              // position in processing order
@@ -99,10 +100,19 @@ k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_
       const int kind = face<6 ? a.kind[face] : PK_CUSTOM;
       if( kind==PK_ABSORB ) accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V );
       else if( kind==PK_REMOTE ) key = face;
+      else if( kind==PK_CUSTOM && a.custom ) key = 6;
       else atomicAdd( n_unknown, 1 );
     }
-    const int rank = block_rank_by_key<6>( key, s_w, s_tot );
-    if( key>=0 ) {
+    const int rank = block_rank_by_key<7>( key, s_w, s_tot );
+    if( key==6 ) {
+      // handed to the host program's handler in processing order (boundary_p.cc:236-253);
+      // the handler sees the particle with its voxel restored (:196-199)
+      float4 * out = a.custom + 4*(size_t)( s_base[6] + rank );
+      out[0] = make_float4( r0.x, r0.y, r0.z, __int_as_float( voxel ) );
+      out[1] = r1;
+      out[2] = d;
+      out[3] = make_float4( __int_as_float( face ), __int_as_float( sp_id ), 0.f, 0.f );
+    } else if( key>=0 ) {
       // the same voxel seen from the neighbour brick (boundary_p.cc:215-230)
       const int axis = face>=3 ? face-3 : face;
       int c[3] = { voxel % g.sy, ( voxel / g.sy ) % ( g.ny+2 ), voxel / g.sz };
@@ -118,10 +128,10 @@ k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_
       out[2] = make_float4( d.x, d.y, d.z, __int_as_float( sp_id ) );
     }
     __syncthreads();
-    if( threadIdx.x<6 ) s_base[threadIdx.x] += s_tot[threadIdx.x];
+    if( threadIdx.x<7 ) s_base[threadIdx.x] += s_tot[threadIdx.x];
     __syncthreads();
   }
-  if( threadIdx.x<6 ) a.face_count[threadIdx.x] = s_base[threadIdx.x];
+  if( threadIdx.x<7 ) a.face_count[threadIdx.x] = s_base[threadIdx.x];
 }
 
 // All nm movers (ascending particle index in pm) leave.  The reference's
@@ -156,8 +166,8 @@ k_bnd_backfill( vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __
 }
 
 struct BndInject {
-  const vpb_particle_injector_t * recv[6];
-  int start[7];                        // prefix sums of the received counts, faces 0..5
+  const vpb_particle_injector_t * recv[7];
+  int start[8];                        // prefix sums of the counts: local handler injectors, then faces 0..5
   vpb_particle_t * p[BND_MAX_SP];
   vpb_particle_mover_t * pm[BND_MAX_SP];
   int np[BND_MAX_SP], nm[BND_MAX_SP], max_nm[BND_MAX_SP];
@@ -165,15 +175,62 @@ struct BndInject {
   int * counters;                      // [0..MAX_SP) injected, [MAX_SP..2 MAX_SP) movers appended, [2 MAX_SP..) movers dropped
 };
 
-// Append the received particles (faces 0..5, each message last-first) to their
-// species and finish their move (boundary_p.cc:440-494).
+// One injected particle: appended at idx, its remaining displacement finished
+// with move_p (currents into the accumulator, a new mover if it leaves again).
+__device__ __forceinline__ void inject_one( const BndInject & a, float * __restrict__ acc, const GridDev & g,
+                                            float4 i0, float4 i1, float4 i2, int key, int idx ) {
+  MoveState ms;
+  ms.dx = i0.x; ms.dy = i0.y; ms.dz = i0.z; ms.i = __float_as_int( i0.w );
+  ms.ux = i1.x; ms.uy = i1.y; ms.uz = i1.z;
+  ms.dispx = i2.x; ms.dispy = i2.y; ms.dispz = i2.z;
+  const float q = a.q[key]*i1.w;
+  float j[12]; int status;
+  do {
+    int vox;
+    status = move_p_streak( ms, q, g, j, vox );
+    commit_currents( acc, vox, j );
+  } while( status==1 );
+  float4 * dst = reinterpret_cast<float4 *>( a.p[key] + idx );
+  dst[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
+  dst[1] = make_float4( ms.ux, ms.uy, ms.uz, i1.w );
+  if( status==2 ) {
+    const int k = a.nm[key] + atomicAdd( a.counters + BND_MAX_SP + key, 1 );
+    if( k<a.max_nm[key] ) reinterpret_cast<float4 *>( a.pm[key] )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
+    else atomicAdd( a.counters + 2*BND_MAX_SP + key, 1 );
+  }
+}
+
+// PARITY deposit: the same injection by one thread, so that the currents of
+// injected particles are added to the accumulator in the reference's order.
+__global__ void k_bnd_inject_serial( BndInject a, float * __restrict__ acc, GridDev g ) {
+  if( threadIdx.x || blockIdx.x ) return;
+  int count[BND_MAX_SP];
+  for( int k=0; k<BND_MAX_SP; k++ ) count[k] = 0;
+  const int total = a.start[7];
+  int face = 0;
+  for( int r=0; r<total; r++ ) {
+    while( r>=a.start[face+1] ) face++;
+    const int n = a.start[face+1] - a.start[face];
+    const float4 * src = reinterpret_cast<const float4 *>( a.recv[face] + ( n-1-( r-a.start[face] ) ) );
+    const float4 i0 = src[0], i1 = src[1], i2 = src[2];
+    const int key = __float_as_int( i2.w );
+    if( key<0 || key>=BND_MAX_SP || !a.p[key] ) { atomicAdd( a.counters + 3*BND_MAX_SP, 1 ); continue; }
+    inject_one( a, acc, g, i0, i1, i2, key, a.np[key] + count[key] );
+    count[key]++;
+  }
+  for( int k=0; k<BND_MAX_SP; k++ ) a.counters[k] = count[k];
+}
+
+// Append the injected particles (the local handlers' injectors first, then the
+// messages of faces 0..5, each list last-first) to their species and finish
+// their move (boundary_p.cc:426-494).
 __global__ void __launch_bounds__(BND_T)
 k_bnd_inject( BndInject a, float * __restrict__ acc, GridDev g ) {
   __shared__ int s_w[BND_T/32][BND_MAX_SP];
   __shared__ int s_tot[BND_MAX_SP], s_base[BND_MAX_SP];
   if( threadIdx.x<BND_MAX_SP ) s_base[threadIdx.x] = 0;
   __syncthreads();
-  const int total = a.start[6];
+  const int total = a.start[7];
   for( int c0=0; c0<total; c0+=BND_T ) {
     const int r = c0 + threadIdx.x;
     int key = -1; float4 i0 = {}, i1 = {}, i2 = {};
@@ -187,28 +244,8 @@ k_bnd_inject( BndInject a, float * __restrict__ acc, GridDev g ) {
       if( key<0 || key>=BND_MAX_SP || !a.p[key] ) key = -1;      // unknown species: dropped (counted below)
     }
     const int rank = block_rank_by_key<BND_MAX_SP>( key, s_w, s_tot );
-    if( key>=0 ) {
-      const int idx = a.np[key] + s_base[key] + rank;
-      MoveState ms;
-      ms.dx = i0.x; ms.dy = i0.y; ms.dz = i0.z; ms.i = __float_as_int( i0.w );
-      ms.ux = i1.x; ms.uy = i1.y; ms.uz = i1.z;
-      ms.dispx = i2.x; ms.dispy = i2.y; ms.dispz = i2.z;
-      const float q = a.q[key]*i1.w;
-      float j[12]; int status;
-      do {
-        int vox;
-        status = move_p_streak( ms, q, g, j, vox );
-        commit_currents( acc, vox, j );
-      } while( status==1 );
-      float4 * dst = reinterpret_cast<float4 *>( a.p[key] + idx );
-      dst[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
-      dst[1] = make_float4( ms.ux, ms.uy, ms.uz, i1.w );
-      if( status==2 ) {
-        const int k = a.nm[key] + atomicAdd( a.counters + BND_MAX_SP + key, 1 );
-        if( k<a.max_nm[key] ) reinterpret_cast<float4 *>( a.pm[key] )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx ) );
-        else atomicAdd( a.counters + 2*BND_MAX_SP + key, 1 );
-      }
-    } else if( r<total ) atomicAdd( a.counters + 3*BND_MAX_SP, 1 );
+    if( key>=0 ) inject_one( a, acc, g, i0, i1, i2, key, a.np[key] + s_base[key] + rank );
+    else if( r<total ) atomicAdd( a.counters + 3*BND_MAX_SP, 1 );
     __syncthreads();
     if( threadIdx.x<BND_MAX_SP ) s_base[threadIdx.x] += s_tot[threadIdx.x];
     __syncthreads();
@@ -245,6 +282,9 @@ struct BndBuffers {
   vpb_particle_injector_t * send[6] = {}, * recv[6] = {};
   size_t send_cap[6] = {}, recv_cap[6] = {};
   int * d_int = nullptr;     // [0..6) face_count  [8..14) recv counts  [16] n_unknown  [32..32+4*MAX_SP] inject counters
+  // particles handed to the host program's boundary handlers, and what the handlers inject
+  float4 * custom = nullptr; size_t custom_cap = 0;
+  vpb_particle_injector_t * ci = nullptr; size_t ci_cap = 0;
   // sparse STRICT transfers: page-locked host staging and its device twin (rows, then indices)
   char * h_rows = nullptr, * d_rows = nullptr; size_t rows_cap = 0;
 } B;
@@ -284,6 +324,7 @@ namespace vpb {
 void release_boundary_buffers() {
   for( int f=0; f<6; f++ ) { cudaFree( B.send[f] ); cudaFree( B.recv[f] ); B.send[f] = B.recv[f] = nullptr; B.send_cap[f] = B.recv_cap[f] = 0; }
   cudaFree( B.d_int ); B.d_int = nullptr;
+  cudaFree( B.custom ); cudaFree( B.ci ); B.custom = nullptr; B.ci = nullptr; B.custom_cap = B.ci_cap = 0;
   cudaFree( B.d_rows ); if( B.h_rows ) cudaFreeHost( B.h_rows ); B.d_rows = B.h_rows = nullptr; B.rows_cap = 0;
 }
 }
@@ -438,9 +479,19 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   long long nm_tot = 0;
   for( SpeciesMirror * m : sps ) nm_tot += m->nm;
   if( !any_remote && nm_tot==0 ) { if( sparse ) sparse_download( ss ); return; }   // nothing left the domain and nobody to talk to
-  if( nm_tot>0 && pbc_list ) {
-    for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_CUSTOM )
-      VPB_ERROR( "custom particle boundary handlers (host callbacks) are not available on the device yet" );
+  // User handlers (boundary_p.cc:81-89): indexed by -id-3.  They are host
+  // functions of the host program, called below in the reference's order.
+  constexpr int MAX_PBC = 32;
+  vpb_particle_bc_func_t pbc_interact[MAX_PBC] = {}; void * pbc_params[MAX_PBC] = {};
+  bool any_custom = false;
+  for( const vpb_particle_bc_t * pbc=(const vpb_particle_bc_t *)pbc_list; pbc; pbc=pbc->next ) {
+    const long long k = -pbc->id-3;
+    if( k<0 || k>=MAX_PBC ) VPB_ERROR( "Update this to support more particle boundary conditions" );
+    pbc_interact[k] = pbc->interact; pbc_params[k] = pbc->params;
+  }
+  for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_CUSTOM && gm->pcode[f]<=-3 ) {
+    const long long k = -gm->pcode[f]-3;
+    if( k<MAX_PBC && pbc_interact[k] ) any_custom = true;
   }
   FieldMirror * mf = mirror( fa );
   AccMirror   * ma = mirror( aa );
@@ -459,6 +510,16 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     bf.send[f] = B.send[f];
   }
   bf.face_count = B.d_int;
+  bf.custom = nullptr;
+  if( any_custom && nm_tot>0 ) {
+    if( (size_t)nm_tot>B.custom_cap ) {
+      VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+      if( B.custom ) VPB_CUDA( cudaFree( B.custom ) );
+      B.custom_cap = (size_t)nm_tot + (size_t)nm_tot/4 + 256;
+      VPB_CUDA( cudaMalloc( &B.custom, sizeof(float4)*4*B.custom_cap ) );
+    }
+    bf.custom = B.custom;
+  }
   bool touched_rhob = false;
   for( SpeciesMirror * m : sps ) {
     if( m->nm<=0 ) continue;
@@ -479,6 +540,41 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   int n_send[6], n_recv[6] = { 0, 0, 0, 0, 0, 0 };
   for( int f=0; f<6; f++ ) n_send[f] = h_int[f];
 
+  // ---- user handlers (boundary_p.cc:236-253) ----
+  // The particles that hit a handler's face come back in processing order
+  // (species in list order, movers last-first); each is given to the host
+  // program's interact() with its own copy of the particle and mover, and the
+  // injectors it returns form the local list that is injected first.
+  int n_ci = 0;
+  const int n_custom = h_int[6];
+  if( n_custom>0 ) {
+    std::vector<float4> ent( 4*(size_t)n_custom );
+    d2h( ent.data(), B.custom, sizeof(float4)*4*(size_t)n_custom, r.stream );
+    // handlers may read or update the host fields (absorb_tally -> accumulate_rhob):
+    // the charge absorbed on the device goes down first
+    if( touched_rhob && r.coherence==VPB_COHERENCE_STRICT ) { mark_dev_written( mf ); to_host( mf ); touched_rhob = false; }
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    std::vector<vpb_particle_injector_t> ci( (size_t)n_custom );
+    vpb_species_t * sp_by_id[BND_MAX_SP] = {};
+    for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) sp_by_id[sp->id] = sp;
+    for( int k=0; k<n_custom; k++ ) {
+      vpb_particle_t prt; vpb_particle_mover_t mv;
+      memcpy( &prt, &ent[4*(size_t)k], sizeof(prt) );
+      memcpy( &mv, &ent[4*(size_t)k+2], sizeof(mv) );
+      int face, sp_id;
+      memcpy( &face, &ent[4*(size_t)k+3].x, 4 ); memcpy( &sp_id, &ent[4*(size_t)k+3].y, 4 );
+      const long long h = -gm->pcode[face]-3;
+      if( (size_t)n_ci+1>ci.size() ) ci.resize( ci.size()*2 );
+      n_ci += pbc_interact[h]( pbc_params[h], sp_by_id[sp_id], &prt, &mv, ci.data()+n_ci, 1, face );
+    }
+    if( n_ci>0 ) {
+      grow( &B.ci, &B.ci_cap, (size_t)n_ci );
+      h2d( B.ci, ci.data(), sizeof(vpb_particle_injector_t)*(size_t)n_ci, r.stream );
+      VPB_CUDA( cudaStreamSynchronize( r.stream ) );      // ci is a local vector
+    }
+    if( r.coherence==VPB_COHERENCE_STRICT ) { mf->dev_valid = false; mf->host_valid = true; }   // a handler may have written host fields
+  }
+
   // ---- exchange counts, then injectors (boundary_p.cc:285-316) ----
   if( any_remote ) {
     if( counts_done ) for( int f=0; f<6; f++ ) n_recv[f] = pre_recv[f];
@@ -496,13 +592,14 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   }
 
   // ---- inject (boundary_p.cc:318-494) ----
-  int max_inj = 0;
+  int max_inj = n_ci;
   for( int f=0; f<6; f++ ) max_inj += n_recv[f];
   if( max_inj>0 ) {
     if( sparse ) to_device( ma );
     BndInject bi = {};
     bi.start[0] = 0;
-    for( int f=0; f<6; f++ ) { bi.recv[f] = B.recv[f]; bi.start[f+1] = bi.start[f] + n_recv[f]; }
+    bi.recv[0] = B.ci; bi.start[1] = n_ci;                                  // custom local injection first (:426-432)
+    for( int f=0; f<6; f++ ) { bi.recv[f+1] = B.recv[f]; bi.start[f+2] = bi.start[f+1] + n_recv[f]; }
     for( SpeciesMirror * m : sps ) {
       grow_particles( m, (size_t)m->np + (size_t)max_inj );
       const int id = m->host->id;
@@ -510,7 +607,8 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
       bi.q[id] = m->host->q;
     }
     bi.counters = B.d_int + 32;
-    k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
+    if( r.deposit_mode==VPB_DEPOSIT_PARITY ) k_bnd_inject_serial<<< 1, 32, 0, r.stream >>>( bi, ma->d, g );
+    else k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
     VPB_CHECK_LAUNCH(); r.launches++;
     int h_cnt[4*BND_MAX_SP+1];
     d2h( h_cnt, B.d_int+32, sizeof(h_cnt), r.stream );

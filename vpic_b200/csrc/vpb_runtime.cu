@@ -144,7 +144,7 @@ GridMirror * mirror( const vpb_grid_t * g ) {
   if( !g->neighbor ) VPB_ERROR( "grid_t.neighbor is NULL" );
   if( !g->range ) VPB_ERROR( "grid_t.range is NULL" );
   const int64_t rangem = g->range[g_world_size];
-  for( int f=0; f<6; f++ ) { m->pkind[f] = PK_LOCAL; m->nb_n[f] = 0; }
+  for( int f=0; f<6; f++ ) { m->pkind[f] = PK_LOCAL; m->nb_n[f] = 0; m->pcode[f] = 0; }
   for( int f=0; f<6 && regular; f++ ) {
     const int a = f%3, side = f<3 ? -1 : 1;
     int cls = -1, kind = PK_LOCAL;
@@ -163,7 +163,8 @@ GridMirror * mirror( const vpb_grid_t * g ) {
         k = FACE_EXIT;
         pk = nb==VPB_ABSORB_PARTICLES ? PK_ABSORB : ( nb>=0 && nb<=rangem ) ? PK_REMOTE : PK_CUSTOM;
       }
-      if( cls<0 ) { cls = k; kind = pk; } else if( cls!=k || kind!=pk ) { regular = false; break; }
+      if( cls<0 ) { cls = k; kind = pk; m->pcode[f] = pk==PK_CUSTOM ? (long long)nb : 0; }
+      else if( cls!=k || kind!=pk || ( pk==PK_CUSTOM && m->pcode[f]!=(long long)nb ) ) { regular = false; break; }
     }
     d.face[f] = cls<0 ? FACE_REFLECT : cls;
     m->pkind[f] = kind;
@@ -187,7 +188,7 @@ GridMirror * mirror( const vpb_grid_t * g ) {
     VPB_CUDA( cudaMalloc( &m->d_neighbor, t.size()*sizeof(int32_t) ) );
     VPB_CUDA( cudaMemcpy( m->d_neighbor, t.data(), t.size()*sizeof(int32_t), cudaMemcpyHostToDevice ) );
     d.neighbor = m->d_neighbor;
-    for( int f=0; f<6; f++ ) { d.face[f] = FACE_EXIT; m->pkind[f] = PK_CUSTOM; }
+    for( int f=0; f<6; f++ ) { d.face[f] = FACE_EXIT; m->pkind[f] = PK_CUSTOM; m->pcode[f] = 0; }   // per-voxel codes: no device handler table
   }
   r.grids[g] = m;
   return m;

@@ -69,7 +69,7 @@ constexpr int32_t NB_EXIT    = -2;
 enum ParticleFaceKind : int { PK_LOCAL = 0,    // wrap / reflect: move_p never hands these over
                               PK_ABSORB = 1,   // absorb_particles: accumulate_rhob, drop
                               PK_REMOTE = 2,   // neighbouring rank: send an injector
-                              PK_CUSTOM = 3 }; // user handler (host callback): not on the device
+                              PK_CUSTOM = 3 }; // user handler: a host callback of the host program (boundary_private.h:14-33)
 
 struct GridMirror {
   const vpb_grid_t * host = nullptr;
@@ -78,6 +78,7 @@ struct GridMirror {
   int fbc[6];                // field boundary per face: rank (>=0) or local code (<0)
   int pkind[6];              // ParticleFaceKind per face
   int nb_n[6];               // for PK_REMOTE: the neighbour brick's cell count along the face axis
+  long long pcode[6];        // for PK_CUSTOM: the face's neighbor[] code (user handler id, <= -3)
 };
 
 struct FieldMirror {

@@ -73,6 +73,8 @@ class Simulation:
         self.num_div_e_round = self.num_div_b_round = 2
         self.last_div_e_err = self.last_div_b_err = self.last_sync_err = None
         self.g = self.fa = self.ia = self.aa = None
+        self.pbc_list = None       # particle_bc_t list head (user handlers), src/vpic/vpic.h:561-571
+        self._pbc_keep = []
 
     # ---- setup (deck-like helpers, src/vpic/vpic.h:326-653) ----
     def define_grid(self, kind, lo, hi, n, topo=(1, 1, 1), dt=None, cvac=1.0, eps0=1.0, pbc=-2):
@@ -111,6 +113,19 @@ class Simulation:
         s.next = C.cast(self.species[-1], C.POINTER(abi.Species)) if self.species else None
         self.species.append(sp)
         return sp
+
+    def define_particle_bc(self, interact, params=None):
+        """append_particle_bc (src/boundary/boundary.c:66-76): `interact` is the address of a host
+        function with the particle_bc_func_t signature; returns the id (-3, -4, ...) to put on faces
+        with set_pbc / define_grid(pbc=...)."""
+        pbc = abi.ParticleBC()
+        pbc.params, pbc.interact, pbc.delete_pbc = params, interact, None
+        n = 0 if self.pbc_list is None else -C.cast(self.pbc_list, C.POINTER(abi.ParticleBC)).contents.id - 2
+        pbc.id = -3 - n
+        pbc.next = C.cast(self.pbc_list, C.POINTER(abi.ParticleBC)) if self.pbc_list else None
+        self._pbc_keep.append(pbc)
+        self.pbc_list = C.addressof(pbc)
+        return pbc.id
 
     @staticmethod
     def sp_struct(sp):
@@ -197,7 +212,7 @@ class Simulation:
             be.advance_p(sp, self.aa, self.ia)
         be.reduce_accumulator_array(self.aa)                          # :65-66
         for _ in range(self.num_comm_round):                          # :73-77
-            be.boundary_p(None, self.sp_list_head, self.fa, self.aa)
+            be.boundary_p(self.pbc_list, self.sp_list_head, self.fa, self.aa)
         for sp in self.species_in_list_order():                       # :78-101 (drop unprocessed movers)
             if self.sp_struct(sp).nm:
                 raise RuntimeError("unprocessed particle movers left after boundary_p")

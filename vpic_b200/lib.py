@@ -107,9 +107,9 @@ class Backend:
                 fn = getattr(lib, prefix + name)
                 fn.restype, fn.argtypes = res, args
                 setattr(self, name, fn)
-            fn = lib.orc_boundary_p
-            fn.restype, fn.argtypes = None, [_P, _P, _P]
-            self.boundary_p = lambda pbc, sp, fa, aa: fn(sp, fa, aa)
+            fn = lib.orc_boundary_p_pbc
+            fn.restype, fn.argtypes = None, [_P, _P, _P, _P]
+            self.boundary_p = fn
         else:
             bp = lib.boundary_p
             bp.restype, bp.argtypes = None, [_P, _P, _P, _P]
