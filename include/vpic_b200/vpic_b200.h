@@ -114,6 +114,10 @@ int  vpic_b200_abi_check( int sizeof_interpolator, int sizeof_accumulator, int s
 void vpic_b200_sync_to_host( void * obj );     /* device -> host struct arrays      */
 void vpic_b200_sync_from_host( void * obj );   /* host struct arrays -> device       */
 void vpic_b200_forget( void * obj );           /* drop the mirror (before free())    */
+/* g->neighbor / g->bc were edited after the first particle step (the edits a
+   deck makes before its first step -- set_region_bc, set_domain_particle_bc --
+   are picked up without this call: the table is read at the first advance_p). */
+void vpic_b200_grid_changed( const void * grid );
 void vpic_b200_device_synchronize( void );
 long long vpic_b200_launch_count( void );      /* kernels launched so far            */
 void vpic_b200_transfer_bytes( long long * h2d_d2h ); /* bytes copied host->device, device->host so far */

@@ -65,3 +65,20 @@ def same_bits(a, b):
     if a.dtype.names:
         return all(same_bits(a[n], b[n]) for n in a.dtype.names if not n.startswith("_"))
     return a.shape == b.shape and bool(np.all(a == b))
+
+
+def paint_region_bc(s):
+    """Boundary codes inside the box, as the reference's set_region_bc paints
+    them (deck/wrapper.h:255-310): an absorbing sheet seen from the +x side, a
+    handler sheet seen from the -x side, a reflecting patch and one lone
+    handler voxel face."""
+    g = s.grid_struct(s.g)
+    nb = s.neighbor_table()
+    vox = lambda x, y, z: x + (g.nx + 2) * (y + (g.ny + 2) * z)
+    for z in range(1, g.nz + 1):
+        for y in range(1, g.ny + 1):
+            nb[vox(5, y, z), 0] = -2          # absorb_particles
+            nb[vox(4, y, z), 3] = -3          # user handler
+        for x in range(1, 4):
+            nb[vox(x, 3, z), 4] = -1          # reflect_particles
+    nb[vox(7, 2, 2), 5] = -3

@@ -73,6 +73,38 @@ def test_reference_driver_fast_deposit_meets_the_reference_criteria(tmp_path):
     assert np.all(np.abs(got[:, 7:9] - gold[:, 7:9]) <= 2e-3 * gold[:, 7:9])
 
 
+def run_sample_deck(tmp_path, deck, min_launches):
+    import hashlib
+    import json
+    exe = os.path.join(ROOT, "oracle", "_ref", f"deckrun_{deck}_b200")
+    if not os.path.exists(exe):
+        pytest.skip(f"oracle/_ref/deckrun_{deck}_b200 not built (needs /root/reference at build time)")
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", f"{deck}_outputs.json")))
+    r = subprocess.run([exe, "--tpp", "1"], cwd=tmp_path, env=deck_env(VPIC_B200_DEPOSIT="parity", VPIC_B200_COHERENCE="strict"),
+                       capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, (r.stdout[-1500:], [l for l in r.stderr.splitlines() if "rror" in l][:5], r.stderr[-2500:])
+    launches(r.stderr, min_launches)
+    if gold["energies"] is not None:
+        assert open(os.path.join(tmp_path, "energies")).read() == gold["energies"]
+    bad = [n for n, h in gold["files"].items()
+           if not os.path.exists(os.path.join(tmp_path, n))
+           or hashlib.sha256(open(os.path.join(tmp_path, n), "rb").read()).hexdigest() != h]
+    assert not bad, bad
+    return gold
+
+
+def test_reference_lpi_deck_every_output_file_identical(tmp_path):
+    """The reference's sample/lpi_2d_F6_test (BASELINE configs[4] physics: laser
+    injected through user_field_injection, absorbing field walls, the
+    reference's maxwellian_reflux handler on the particle walls, electrons +
+    He ions, div cleaning) with four numbers reduced (oracle/Makefile), built
+    from the unmodified reference program with libvpic_b200.so ahead of the
+    reference library: field and hydro dumps at steps 0 / 20 / 40 / 60 equal the
+    pure-CPU reference run's, SHA-256 for SHA-256."""
+    gold = run_sample_deck(tmp_path, "lpi_small", 60 * 20)
+    assert len(gold["files"]) == 13
+
+
 def test_reference_harris_deck_every_output_file_identical(tmp_path):
     """The reference's sample/harris deck, built from the unmodified reference
     program (deck/main.cc + deck/wrapper.cc + src/vpic) with libvpic_b200.so
@@ -82,18 +114,5 @@ def test_reference_harris_deck_every_output_file_identical(tmp_path):
     host arrays (energies, 21 field dumps, 42 hydro dumps, 42 particle dumps)
     has the SHA-256 of the pure-CPU reference run (tests/golden/harris_outputs.json,
     made by make_harris_golden.py)."""
-    import hashlib
-    import json
-    exe = os.path.join(ROOT, "oracle", "_ref", "deckrun_harris_b200")
-    if not os.path.exists(exe):
-        pytest.skip("oracle/_ref/deckrun_harris_b200 not built (needs /root/reference at build time)")
-    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "harris_outputs.json")))
-    r = subprocess.run([exe, "--tpp", "1"], cwd=tmp_path, env=deck_env(VPIC_B200_DEPOSIT="parity", VPIC_B200_COHERENCE="strict"),
-                       capture_output=True, text=True, timeout=1500)
-    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-3000:])
-    launches(r.stderr, 480 * 20)
-    assert open(os.path.join(tmp_path, "energies")).read() == gold["energies"]
-    bad = [n for n, h in gold["files"].items()
-           if hashlib.sha256(open(os.path.join(tmp_path, n), "rb").read()).hexdigest() != h]
-    assert not bad, bad
+    gold = run_sample_deck(tmp_path, "harris", 480 * 20)
     assert len(gold["files"]) == 106

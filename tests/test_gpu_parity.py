@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 from oracle import harness as H
 from vpic_b200 import b200_backend, load_b200
-from common import make_sim, random_particles, random_fields, same_bits
+from common import make_sim, random_particles, random_fields, same_bits, paint_region_bc
 
 pytestmark = pytest.mark.gpu
 
@@ -480,3 +480,45 @@ def test_custom_particle_boundary_handlers(gpu, handler, coherence):
         assert same_bits(sg.fields()[k], so.fields()[k]), k
     if counts:
         assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 100
+
+
+@pytest.mark.parametrize("coherence", [0, 1])
+def test_boundary_codes_inside_the_box(gpu, coherence):
+    """g->neighbor with absorbing, reflecting and handler codes on interior
+    voxel faces (set_region_bc): move_p ends at them from any voxel and
+    boundary_p decides per particle from the voxel's code.  Three steps on the
+    plain periodic box first, then the table is edited under live arrays
+    (vpic_b200_grid_changed), ten more steps; PARITY deposit, so everything
+    stays bit-comparable with the reference algorithm reading g->neighbor."""
+    import ctypes as C
+    L = load_b200()
+    L.vpic_b200_set_deposit_mode(1)
+    try:
+        so, sg = pair(gpu, kind="periodic", n=(8, 6, 5), damp=0.01, sort_interval=3, max_nm=4000)
+        counts = []
+        for s in (so, sg):
+            fn, c = H.fixture_bounce_handler()
+            counts.append(c)
+            assert s.define_particle_bc(fn, C.addressof(c)) == -3
+            s.num_comm_round = 8
+            s.initialize()
+        L.vpic_b200_set_coherence(coherence)
+        for step in range(3):
+            so.advance(); sg.advance()
+        paint_region_bc(so); paint_region_bc(sg)
+        L.vpic_b200_grid_changed(sg.g)
+        n0 = sum(sg.sp_struct(b).np for b in sg.species)
+        for step in range(10):
+            so.advance(); sg.advance()
+        for obj in [sg.fa, sg.ia, sg.aa] + sg.species:
+            L.vpic_b200_sync_to_host(obj)
+    finally:
+        L.vpic_b200_set_coherence(0)
+        L.vpic_b200_set_deposit_mode(0)
+    nps = [sg.sp_struct(b).np for b in sg.species]
+    assert nps == [so.sp_struct(a).np for a in so.species] and sum(nps) < n0 - 50     # the sheet absorbed some
+    for a, b in zip(so.species, sg.species):
+        assert same_bits(sg.particles(b), so.particles(a))
+    for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "jfx", "jfy", "jfz", "rhob"):
+        assert same_bits(sg.fields()[k], so.fields()[k]), k
+    assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 50

@@ -202,3 +202,25 @@ def test_custom_particle_boundary_handlers(handler):
     assert [so.sp_struct(a).np for a in so.species] == n0          # every particle came back
     if counts:
         assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 100
+
+
+def test_boundary_codes_inside_the_box():
+    """g->neighbor edited the way set_region_bc does it (deck/wrapper.h:255-310):
+    absorbing, reflecting and handler codes on interior voxel faces.  Oracle
+    against the compiled reference."""
+    from common import paint_region_bc
+    so, sr = pair(kind="periodic", n=(8, 6, 5), damp=0.01, sort_interval=3, max_nm=4000)
+    counts = []
+    for s in (so, sr):
+        fn, c = H.fixture_bounce_handler()
+        counts.append(c)
+        assert s.define_particle_bc(fn, C.addressof(c)) == -3
+        s.num_comm_round = 8
+        s.initialize()
+        paint_region_bc(s)
+    n0 = sum(so.sp_struct(a).np for a in so.species)
+    for step in range(10):
+        so.advance(); sr.advance()
+        compare(so, sr, f"step {step}")
+    assert sum(so.sp_struct(a).np for a in so.species) < n0 - 50
+    assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 50

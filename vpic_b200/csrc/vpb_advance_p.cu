@@ -310,6 +310,7 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   SpeciesMirror * ms = mirror( sp );
   AccMirror     * ma = mirror( aa );
   InterpMirror  * mi = mirror( const_cast<vpb_interpolator_array_t *>( ia ) );
+  particle_grid( ms->grid );
   to_device( ma ); to_device( mi );
   const vpb_grid_t * hg = sp->g;
   PushCoef c;

@@ -28,6 +28,8 @@ constexpr int BND_MAX_SP = 16;        // species ids the inject kernel can addre
 
 struct BndFaces {
   int kind[6];                        // ParticleFaceKind
+  int code[6];                        // regular box: the face's neighbor[] code (handler id) if kind is PK_CUSTOM
+  unsigned handler_mask;              // bit h set: the host program registered the handler with id -h-3
   int nb_n[6];                        // neighbour extent along the face axis
   vpb_particle_injector_t * send[6];  // device message bodies
   float4 * custom;                    // particles that hit a face with a user handler: 4 x float4 each
@@ -81,14 +83,16 @@ __device__ __forceinline__ void accumulate_rhob_dev( float * __restrict__ rhob, 
 // order (last mover first).  Single block; chunks of BND_T movers.
 __global__ void __launch_bounds__(BND_T)
 k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int nm,
-                int sp_id, float q_r8V, float * __restrict__ rhob, GridDev g, BndFaces a, int * __restrict__ n_unknown ) {
+                int sp_id, float q_r8V, float * __restrict__ rhob, GridDev g, BndFaces a, int * __restrict__ n_unknown,
+                bool ordered ) {
   __shared__ int s_w[BND_T/32][7];
   __shared__ int s_tot[7], s_base[7];
   if( threadIdx.x<7 ) s_base[threadIdx.x] = a.face_count[threadIdx.x];
   __syncthreads();
   for( int c0=0; c0<nm; c0+=BND_T ) {
     const int r = c0 + threadIdx.x;              // position in processing order
-    int key = -1, face = 0, voxel = 0, i = 0;
+    int key = -1, face = 0, voxel = 0, i = 0, code = 0;
+    bool absorbed = false;
     float4 r0 = {}, r1 = {}, d = {};
     if( r<nm ) {
       d = reinterpret_cast<const float4 *>( pm )[ nm-1-r ];
@@ -97,11 +101,34 @@ k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_
       r1 = reinterpret_cast<const float4 *>( p + i )[1];
       const int vi = __float_as_int( r0.w );
       face = vi & 7; voxel = vi >> 3;
-      const int kind = face<6 ? a.kind[face] : PK_CUSTOM;
-      if( kind==PK_ABSORB ) accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V );
+      // what the host table says about this exit (boundary_p.cc:196-260): the
+      // face's kind on a regular box, the voxel's own code otherwise
+      int kind = -1;
+      if( face<6 ) {
+        if( g.neighbor ) {
+          code = g.neighbor[ 6*(size_t)voxel + face ];
+          kind = code==NB_ABSORB ? PK_ABSORB : code==NB_REMOTE ? PK_REMOTE : ( code<=-3 && code>NB_UNKNOWN ) ? PK_CUSTOM : -1;
+        } else { kind = a.kind[face]; code = a.code[face]; }
+      }
+      if( kind==PK_ABSORB ) { if( ordered ) absorbed = true; else accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V ); }
       else if( kind==PK_REMOTE ) key = face;
-      else if( kind==PK_CUSTOM && a.custom ) key = 6;
+      else if( kind==PK_CUSTOM && a.custom && code>=-34 && ( ( a.handler_mask >> ( -code-3 ) ) & 1u ) ) key = 6;
       else atomicAdd( n_unknown, 1 );
+    }
+    if( ordered ) {
+      // PARITY: the absorbed charge lands on rhob one particle after the other
+      // in processing order, like the reference's loop (boundary_p.cc:204-208)
+      for( int w=0; w<BND_T/32; w++ ) {
+        if( ( threadIdx.x>>5 )==w ) {
+          unsigned todo = __ballot_sync( 0xffffffffu, absorbed );
+          while( todo ) {
+            const int l = __ffs( todo )-1; todo &= todo-1;
+            if( ( threadIdx.x&31 )==l ) accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V );
+            __syncwarp();
+          }
+        }
+        __syncthreads();
+      }
     }
     const int rank = block_rank_by_key<7>( key, s_w, s_tot );
     if( key==6 ) {
@@ -111,7 +138,7 @@ k_bnd_classify( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_
       out[0] = make_float4( r0.x, r0.y, r0.z, __int_as_float( voxel ) );
       out[1] = r1;
       out[2] = d;
-      out[3] = make_float4( __int_as_float( face ), __int_as_float( sp_id ), 0.f, 0.f );
+      out[3] = make_float4( __int_as_float( face ), __int_as_float( sp_id ), __int_as_float( code ), 0.f );
     } else if( key>=0 ) {
       // the same voxel seen from the neighbour brick (boundary_p.cc:215-230)
       const int axis = face>=3 ? face-3 : face;
@@ -297,14 +324,40 @@ void grow( vpb_particle_injector_t ** buf, size_t * cap, size_t want ) {
   VPB_CUDA( cudaMalloc( buf, sizeof(vpb_particle_injector_t)*( *cap ) ) );
 }
 
-// Grow a species' device particle storage (the reference reallocates sp->p the
-// same way, boundary_p.cc:346-361).  Host arrays, when present, belong to the
-// host program and are not reallocated from here.
+// The reference's storage policy before an injection (boundary_p.cc:318-406),
+// for species whose arrays live in host memory: grow by 31.25 % when the worst
+// case does not fit, shrink when less than half is in use, grow the mover
+// array likewise.  The device copies follow the host capacities (mirror()).
+constexpr int MIN_NP = 128;
+void resize_like_reference( SpeciesMirror * m, int max_inj ) {
+  vpb_species_t * sp = m->host;
+  if( !sp->p ) return;
+  int n = m->np + max_inj;
+  if( n>sp->max_np ) {
+    n += 0.3125*n;
+    VPB_WARNING( "Resizing local %s particle storage from %i to %i", sp->name, sp->max_np, n );
+    host_resize_particles( sp, (size_t)n );
+  } else if( sp->max_np>MIN_NP && n<( sp->max_np>>1 ) ) {
+    n += 0.125*n;
+    if( n<MIN_NP ) n = MIN_NP;
+    VPB_WARNING( "Resizing (shrinking) local %s particle storage from %i to %i", sp->name, sp->max_np, n );
+    host_resize_particles( sp, (size_t)n );
+  }
+  int nm = m->nm + max_inj;
+  if( nm>sp->max_nm && sp->pm ) {
+    nm += 0.3125*nm;
+    VPB_WARNING( "This happened.  Resizing local %s mover storage from %i to %i based on not enough movers", sp->name, sp->max_nm, nm );
+    host_resize_movers( sp, (size_t)nm );
+  }
+  mirror( sp );                       // device capacities follow max_np / max_nm
+}
+
+// Grow a device-only species' particle storage (the reference reallocates
+// sp->p the same way, boundary_p.cc:346-361).
 void grow_particles( SpeciesMirror * m, size_t want ) {
   if( want<=m->cap_p ) return;
   vpb_species_t * sp = m->host;
-  if( sp->p ) VPB_ERROR( "species \"%s\": %zu particles after migration exceed max_np=%d; raise max_np "
-                         "(host-resident particle arrays are not resized by the device library)", sp->name, want, sp->max_np );
+  if( sp->p ) VPB_ERROR( "species \"%s\": %zu particles exceed the device capacity %zu after the host arrays were resized", sp->name, want, m->cap_p );
   Runtime & r = rt();
   size_t n = want + (size_t)( 0.3125*(double)want );
   if( n>(size_t)INT32_MAX ) n = (size_t)INT32_MAX;
@@ -440,7 +493,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   {
     // Nothing left the domain and no neighbour rank to talk to: return before
     // touching the mirrors (in STRICT coherence that would re-upload every particle).
-    GridMirror * g0 = mirror( sp_list->g );
+    GridMirror * g0 = particle_grid( mirror( sp_list->g ) );
     bool remote = false; long long pending = 0;
     for( int f=0; f<6; f++ ) if( g0->pkind[f]==PK_REMOTE ) remote = true;
     for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) pending += sp->nm;    // always current on the host (movers_to_host)
@@ -472,7 +525,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     if( sp->id<0 || sp->id>=BND_MAX_SP ) VPB_ERROR( "species id %d is outside the device boundary handler's range", sp->id );
   }
   if( sparse ) sparse_upload( ss );
-  GridMirror * gm = sps[0]->grid;
+  GridMirror * gm = particle_grid( sps[0]->grid );
   const GridDev & g = gm->dev;
   bool any_remote = false;
   for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_REMOTE ) any_remote = true;
@@ -484,11 +537,14 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   constexpr int MAX_PBC = 32;
   vpb_particle_bc_func_t pbc_interact[MAX_PBC] = {}; void * pbc_params[MAX_PBC] = {};
   bool any_custom = false;
+  unsigned handler_mask = 0;
   for( const vpb_particle_bc_t * pbc=(const vpb_particle_bc_t *)pbc_list; pbc; pbc=pbc->next ) {
     const long long k = -pbc->id-3;
     if( k<0 || k>=MAX_PBC ) VPB_ERROR( "Update this to support more particle boundary conditions" );
     pbc_interact[k] = pbc->interact; pbc_params[k] = pbc->params;
+    if( pbc->interact ) handler_mask |= 1u<<k;
   }
+  if( gm->per_voxel && gm->any_custom && handler_mask ) any_custom = true;
   for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_CUSTOM && gm->pcode[f]<=-3 ) {
     const long long k = -gm->pcode[f]-3;
     if( k<MAX_PBC && pbc_interact[k] ) any_custom = true;
@@ -497,6 +553,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   AccMirror   * ma = mirror( aa );
   bool any_absorb = false;
   for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_ABSORB ) any_absorb = true;
+  if( gm->per_voxel && gm->any_absorb ) any_absorb = true;
   if( any_absorb || !sparse ) to_device( mf );      // rhob is only touched by absorbed particles
   if( !sparse ) to_device( ma );                    // (sparse: uploaded when something arrives)
   if( !B.d_int ) VPB_CUDA( cudaMalloc( &B.d_int, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ) ) );
@@ -505,11 +562,11 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   // ---- load the send buffers, absorb, back-fill (boundary_p.cc:130-283) ----
   BndFaces bf;
   for( int f=0; f<6; f++ ) {
-    bf.kind[f] = gm->pkind[f]; bf.nb_n[f] = gm->nb_n[f];
+    bf.kind[f] = gm->pkind[f]; bf.nb_n[f] = gm->nb_n[f]; bf.code[f] = (int)gm->pcode[f];
     if( gm->pkind[f]==PK_REMOTE ) grow( &B.send[f], &B.send_cap[f], (size_t)nm_tot );
     bf.send[f] = B.send[f];
   }
-  bf.face_count = B.d_int;
+  bf.face_count = B.d_int; bf.handler_mask = handler_mask;
   bf.custom = nullptr;
   if( any_custom && nm_tot>0 ) {
     if( (size_t)nm_tot>B.custom_cap ) {
@@ -526,10 +583,11 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     if( !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     const vpb_species_t * sp = m->host;
     const float q_r8V = sp->q*sp->g->r8V;
-    k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16 );
+    k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16,
+                                                  r.deposit_mode==VPB_DEPOSIT_PARITY );
     k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
     VPB_CHECK_LAUNCH(); r.launches += 2;
-    for( int f=0; f<6; f++ ) if( gm->pkind[f]==PK_ABSORB ) touched_rhob = true;
+    if( any_absorb ) touched_rhob = true;
     m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
     mark_dev_written( m );
   }
@@ -561,9 +619,9 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
       vpb_particle_t prt; vpb_particle_mover_t mv;
       memcpy( &prt, &ent[4*(size_t)k], sizeof(prt) );
       memcpy( &mv, &ent[4*(size_t)k+2], sizeof(mv) );
-      int face, sp_id;
-      memcpy( &face, &ent[4*(size_t)k+3].x, 4 ); memcpy( &sp_id, &ent[4*(size_t)k+3].y, 4 );
-      const long long h = -gm->pcode[face]-3;
+      int face, sp_id, code;
+      memcpy( &face, &ent[4*(size_t)k+3].x, 4 ); memcpy( &sp_id, &ent[4*(size_t)k+3].y, 4 ); memcpy( &code, &ent[4*(size_t)k+3].z, 4 );
+      const long long h = -(long long)code-3;
       if( (size_t)n_ci+1>ci.size() ) ci.resize( ci.size()*2 );
       n_ci += pbc_interact[h]( pbc_params[h], sp_by_id[sp_id], &prt, &mv, ci.data()+n_ci, 1, face );
     }
@@ -594,6 +652,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   // ---- inject (boundary_p.cc:318-494) ----
   int max_inj = n_ci;
   for( int f=0; f<6; f++ ) max_inj += n_recv[f];
+  for( SpeciesMirror * m : sps ) resize_like_reference( m, max_inj );
   if( max_inj>0 ) {
     if( sparse ) to_device( ma );
     BndInject bi = {};
@@ -602,6 +661,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     for( int f=0; f<6; f++ ) { bi.recv[f+1] = B.recv[f]; bi.start[f+2] = bi.start[f+1] + n_recv[f]; }
     for( SpeciesMirror * m : sps ) {
       grow_particles( m, (size_t)m->np + (size_t)max_inj );
+      if( (size_t)m->nm + (size_t)max_inj>m->cap_pm && !m->host->pm ) VPB_ERROR( "species \"%s\": raise max_nm", m->host->name );
       const int id = m->host->id;
       bi.p[id] = m->d_p; bi.pm[id] = m->d_pm; bi.np[id] = m->np; bi.nm[id] = m->nm; bi.max_nm[id] = (int)m->cap_pm;
       bi.q[id] = m->host->q;

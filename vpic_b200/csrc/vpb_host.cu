@@ -28,11 +28,18 @@ void   checkpt_ptr( const void * ptr ) __attribute__((weak));
 void * restore_ptr( void ) __attribute__((weak));
 void   checkpt_sym( const void * saddr ) __attribute__((weak));
 void * restore_sym( void ) __attribute__((weak));
+// ... and its aligned allocator (src/util/util_base.h:364-387): arrays the
+// host program allocated are resized with the host program's own functions.
+void   util_malloc_aligned( const char * err, void * mem_ref, size_t n, size_t a ) __attribute__((weak));
+void   util_free_aligned( void * mem_ref ) __attribute__((weak));
 }
+#include <set>
 
 using namespace vpb;
 
 namespace {
+
+static std::set<const void *> & own_species() { static std::set<const void *> s; return s; }
 
 void * alloc_aligned( size_t bytes, size_t align ) {
   void * p = nullptr;
@@ -40,6 +47,41 @@ void * alloc_aligned( size_t bytes, size_t align ) {
   if( posix_memalign( &p, align, bytes ) ) VPB_ERROR( "Failed to allocate %zu bytes", bytes );
   return p;
 }
+
+} // namespace
+
+namespace vpb {
+
+// boundary_p.cc:346-394 for HOST-resident particle / mover arrays: a new array
+// of n elements, the old contents copied over, the old array released.  The
+// arrays of a species made by vpic_b200_new_species are this library's; any
+// other species belongs to the host program and is resized with the host
+// program's allocator (the reference's MALLOC_ALIGNED / FREE_ALIGNED).
+static void * host_array_resize( vpb_species_t * sp, void * old, size_t old_bytes, size_t new_bytes ) {
+  const bool ours = own_species().count( sp )!=0;
+  void * np_ = nullptr;
+  if( ours ) np_ = alloc_aligned( new_bytes, 128 );
+  else if( util_malloc_aligned && util_free_aligned )
+    util_malloc_aligned( "libvpic_b200: resizing storage of a species failed (%lu bytes, %lu aligned)", &np_, new_bytes, 128 );
+  else VPB_ERROR( "species \"%s\": its arrays were not allocated by this library and the host program has no "
+                  "util_malloc_aligned / util_free_aligned to resize them with; raise max_np / max_nm", sp->name );
+  memcpy( np_, old, old_bytes<new_bytes ? old_bytes : new_bytes );
+  unpin_host( old );
+  if( ours ) free( old ); else { void * o = old; util_free_aligned( &o ); }
+  return np_;
+}
+void host_resize_particles( vpb_species_t * sp, size_t n ) {
+  sp->p = (vpb_particle_t *)host_array_resize( sp, sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np, sizeof(vpb_particle_t)*n );
+  sp->max_np = (int)n;
+}
+void host_resize_movers( vpb_species_t * sp, size_t n ) {
+  sp->pm = (vpb_particle_mover_t *)host_array_resize( sp, sp->pm, sizeof(vpb_particle_mover_t)*(size_t)sp->max_nm, sizeof(vpb_particle_mover_t)*n );
+  sp->max_nm = (int)n;
+}
+
+} // namespace vpb
+
+namespace {
 
 #define LOCAL_CELL_ID(x,y,z) VPB_VOXEL(x,y,z,lnx,lny,lnz)
 
@@ -163,7 +205,7 @@ void vpic_b200_set_fbc( vpb_grid_t * g, int boundary, int fbc ) {
       ( fbc!=VPB_PEC_FIELDS && fbc!=VPB_SYMMETRIC_FIELDS && fbc!=VPB_PMC_FIELDS && fbc!=VPB_ABSORB_FIELDS ) )
     VPB_ERROR( "Bad args" );
   g->bc[boundary] = fbc;
-  vpic_b200_forget( g );
+  vpic_b200_grid_changed( g );
 }
 
 void vpic_b200_set_pbc( vpb_grid_t * g, int boundary, int pbc ) {
@@ -179,7 +221,7 @@ void vpic_b200_set_pbc( vpb_grid_t * g, int boundary, int pbc ) {
       g->neighbor[ 6*(int64_t)VPB_VOXEL(l[0],l[1],l[2],lnx,lny,lnz) + tag ] = pbc;
     }
   }
-  vpic_b200_forget( g );
+  vpic_b200_grid_changed( g );
 }
 
 // partition.c:82-135 and :137-182: periodic box, then override the faces on the
@@ -228,11 +270,13 @@ vpb_species_t * vpic_b200_new_species( const char * name, float q, float m, size
   sp->sort_interval = sort_interval; sp->sort_out_of_place = sort_out_of_place;
   sp->partition = (int *)alloc_aligned( sizeof(int)*( (size_t)g->nv + 1 ), 128 );
   sp->g = g;
+  own_species().insert( sp );
   return sp;
 }
 
 void vpic_b200_delete_species( vpb_species_t * sp ) {
   if( !sp ) return;
+  own_species().erase( sp );
   vpic_b200_forget( sp );
   free( sp->partition ); free( sp->pm ); free( sp->p ); free( sp->name ); free( sp );
 }

@@ -260,6 +260,17 @@ void vpic_b200_forget( void * obj ) {
   if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
 }
 
+void vpic_b200_grid_changed( const void * grid ) {
+  Runtime & r = rt();
+  if( !r.initialised || !grid ) return;
+  auto it = r.grids.find( grid );
+  if( it==r.grids.end() ) return;
+  GridMirror * m = it->second; const vpb_grid_t * g = m->host;
+  if( m->dev.nx!=g->nx || m->dev.ny!=g->ny || m->dev.nz!=g->nz )
+    VPB_ERROR( "the grid was resized (%dx%dx%d -> %dx%dx%d) while arrays on it exist", m->dev.nx, m->dev.ny, m->dev.nz, g->nx, g->ny, g->nz );
+  build_neighbors( m ); m->neighbors_final = true;
+}
+
 void * vpic_b200_device_ptr( void * obj, int which ) {
   if( auto m = VPB_FIND( species, obj ) ) return which==0 ? (void *)m->d_p : which==1 ? (void *)m->d_pm : (void *)m->d_partition;
   if( auto m = VPB_FIND( fields,  obj ) ) return (void *)m->d;

@@ -112,25 +112,12 @@ void * pinned( size_t bytes ) {
 
 // ---- grid mirror -----------------------------------------------------------
 
-GridMirror * mirror( const vpb_grid_t * g ) {
-  ensure_init();
-  Runtime & r = rt();
-  if( !g ) VPB_ERROR( "NULL grid" );
-  auto it = r.grids.find( g );
-  if( it!=r.grids.end() ) {
-    GridMirror * m = it->second;
-    if( m->dev.nx==g->nx && m->dev.ny==g->ny && m->dev.nz==g->nz ) return m;
-    if( m->d_neighbor ) cudaFree( m->d_neighbor );
-    delete m; r.grids.erase( it );
-  }
-  GridMirror * m = new GridMirror;
-  m->host = g;
+void build_neighbors( GridMirror * m ) {
+  const vpb_grid_t * g = m->host;
   GridDev & d = m->dev;
-  d.nx = g->nx; d.ny = g->ny; d.nz = g->nz;
-  d.sx = 1; d.sy = g->nx+2; d.sz = (g->nx+2)*(g->ny+2); d.nv = d.sz*(g->nz+2);
-  d.nvp = ( d.nv + 31 ) & ~31;
+  if( m->d_neighbor ) { VPB_CUDA( cudaStreamSynchronize( rt().stream ) ); VPB_CUDA( cudaFree( m->d_neighbor ) ); m->d_neighbor = nullptr; }
   d.neighbor = nullptr;
-  if( d.nv!=g->nv ) VPB_ERROR( "grid_t.nv (%d) does not match (nx+2)(ny+2)(nz+2) (%d)", g->nv, d.nv );
+  m->per_voxel = m->any_absorb = m->any_custom = false;
   static const int bnd[6] = { VPB_BOUNDARY(-1,0,0), VPB_BOUNDARY(0,-1,0), VPB_BOUNDARY(0,0,-1),
                               VPB_BOUNDARY( 1,0,0), VPB_BOUNDARY(0, 1,0), VPB_BOUNDARY(0,0, 1) };
   for( int f=0; f<6; f++ ) m->fbc[f] = g->bc[ bnd[f] ];
@@ -178,21 +165,68 @@ GridMirror * mirror( const vpb_grid_t * g ) {
     }
   }
   if( !regular ) {
-    // Irregular (set_region_bc etc.): keep an explicit compact table.
-    std::vector<int32_t> t( 6*(size_t)d.nv );
-    for( size_t i=0; i<t.size(); i++ ) {
-      int64_t nb = g->neighbor[i];
-      t[i] = nb==VPB_REFLECT_PARTICLES ? NB_REFLECT
-           : ( nb>=g->rangel && nb<=g->rangeh ) ? (int32_t)( nb - g->rangel ) : NB_EXIT;
+    // Boundary codes inside the box (deck/wrapper.h:255-310 set_region_bc,
+    // grid/ops.c set_pbc on part of a face ...): keep the table itself, 32-bit.
+    // A particle can then leave from any voxel; what happens to it is decided
+    // per particle from the code (boundary_p.cc:196-260).
+    std::vector<int32_t> t( 6*(size_t)d.nv, NB_UNKNOWN );
+    for( int f=0; f<6; f++ ) { d.face[f] = FACE_EXIT; m->pkind[f] = PK_CUSTOM; m->pcode[f] = 0; m->nb_n[f] = 0; }
+    for( int z=1; z<=n[2]; z++ ) for( int y=1; y<=n[1]; y++ ) for( int x=1; x<=n[0]; x++ ) {
+      const int c[3] = { x, y, z };
+      const int64_t v = x + s[1]*y + s[2]*z;
+      for( int f=0; f<6; f++ ) {
+        const int a = f%3, side = f<3 ? -1 : 1;
+        const int64_t nb = g->neighbor[ 6*v + f ];
+        int32_t code;
+        if( nb==VPB_REFLECT_PARTICLES ) code = NB_REFLECT;
+        else if( nb==VPB_ABSORB_PARTICLES ) { code = NB_ABSORB; m->any_absorb = true; }
+        else if( nb>=g->rangel && nb<=g->rangeh ) code = (int32_t)( nb - g->rangel );
+        else if( nb<0 ) { code = nb>(int64_t)NB_UNKNOWN ? (int32_t)nb : NB_UNKNOWN; m->any_custom = true; }
+        else if( nb<=rangem && ( side<0 ? c[a]==1 : c[a]==n[a] ) ) {
+          // another rank's voxel: only through the face that rank sits behind
+          const int rank = g->bc[ bnd[f] ];
+          if( rank<0 || rank>=g_world_size || nb<g->range[rank] || nb>=g->range[rank+1] )
+            VPB_ERROR( "neighbor[%lld] of voxel %lld does not belong to the rank behind face %d", (long long)nb, (long long)v, f );
+          const int64_t rnc = g->range[rank+1] - g->range[rank];
+          const int64_t plane = (int64_t)( n[(a+1)%3]+2 )*( n[(a+2)%3]+2 );
+          if( rnc%plane ) VPB_ERROR( "the brick of rank %d does not match this rank's face %d", rank, f );
+          m->nb_n[f] = (int)( rnc/plane ) - 2; m->pkind[f] = PK_REMOTE;
+          code = NB_REMOTE;
+        } else code = NB_UNKNOWN;
+        t[ 6*(size_t)v + f ] = code;
+      }
     }
     VPB_CUDA( cudaMalloc( &m->d_neighbor, t.size()*sizeof(int32_t) ) );
     VPB_CUDA( cudaMemcpy( m->d_neighbor, t.data(), t.size()*sizeof(int32_t), cudaMemcpyHostToDevice ) );
     d.neighbor = m->d_neighbor;
-    for( int f=0; f<6; f++ ) { d.face[f] = FACE_EXIT; m->pkind[f] = PK_CUSTOM; m->pcode[f] = 0; }   // per-voxel codes: no device handler table
+    m->per_voxel = true;
   }
+}
+
+GridMirror * mirror( const vpb_grid_t * g ) {
+  ensure_init();
+  Runtime & r = rt();
+  if( !g ) VPB_ERROR( "NULL grid" );
+  auto it = r.grids.find( g );
+  if( it!=r.grids.end() ) {
+    GridMirror * m = it->second;
+    if( m->dev.nx==g->nx && m->dev.ny==g->ny && m->dev.nz==g->nz ) return m;
+    if( m->d_neighbor ) cudaFree( m->d_neighbor );
+    delete m; r.grids.erase( it );
+  }
+  GridMirror * m = new GridMirror;
+  m->host = g;
+  GridDev & d = m->dev;
+  d.nx = g->nx; d.ny = g->ny; d.nz = g->nz;
+  d.sx = 1; d.sy = g->nx+2; d.sz = (g->nx+2)*(g->ny+2); d.nv = d.sz*(g->nz+2);
+  d.nvp = ( d.nv + 31 ) & ~31;
+  d.neighbor = nullptr;
+  if( d.nv!=g->nv ) VPB_ERROR( "grid_t.nv (%d) does not match (nx+2)(ny+2)(nz+2) (%d)", g->nv, d.nv );
+  build_neighbors( m );
   r.grids[g] = m;
   return m;
 }
+
 
 // ---- field mirror ----------------------------------------------------------
 

@@ -58,9 +58,16 @@ struct GridDev {             // passed by value to kernels
   const int32_t * neighbor;  // optional explicit table (6*nv), else nullptr
 };
 
-// Encoding of the explicit neighbour table: >=0 local voxel, NB_REFLECT, NB_EXIT.
+// Encoding of the explicit neighbour table: >=0 local voxel, NB_REFLECT, and
+// for everything that ends the local move (any other negative value): the
+// host table's own code -- NB_ABSORB, a user handler id (<= -3,
+// boundary_p.cc:236-253) -- or NB_REMOTE / NB_UNKNOWN.  The arithmetic path
+// only says NB_EXIT and the face's kind decides (GridMirror::pkind).
 constexpr int32_t NB_REFLECT = -1;
+constexpr int32_t NB_ABSORB  = -2;
 constexpr int32_t NB_EXIT    = -2;
+constexpr int32_t NB_REMOTE  = INT32_MIN;
+constexpr int32_t NB_UNKNOWN = INT32_MIN+1;
 
 // ---- mirrors ---------------------------------------------------------------
 
@@ -79,6 +86,9 @@ struct GridMirror {
   int pkind[6];              // ParticleFaceKind per face
   int nb_n[6];               // for PK_REMOTE: the neighbour brick's cell count along the face axis
   long long pcode[6];        // for PK_CUSTOM: the face's neighbor[] code (user handler id, <= -3)
+  bool per_voxel = false;    // set_region_bc etc.: boundary codes anywhere in the box, read from d_neighbor
+  bool any_absorb = false, any_custom = false;   // per_voxel: which codes the table holds
+  bool neighbors_final = false;                  // rebuilt once more at the first particle call (see particle_grid)
 };
 
 struct FieldMirror {
@@ -160,6 +170,11 @@ void * scratch( size_t bytes );        // grow-only device scratch
 void * pinned( size_t bytes );         // grow-only pinned host scratch
 
 GridMirror    * mirror( const vpb_grid_t * g );
+void build_neighbors( GridMirror * m );          // (re)derive everything that comes from g->neighbor
+// The host program may edit g->neighbor between creating its arrays and the
+// first step (deck/wrapper.h set_region_bc); the particle kernels therefore
+// re-read the table at their first call.
+inline GridMirror * particle_grid( GridMirror * m ) { if( !m->neighbors_final ) { build_neighbors( m ); m->neighbors_final = true; } return m; }
 FieldMirror   * mirror( vpb_field_array_t * fa );
 InterpMirror  * mirror( vpb_interpolator_array_t * ia );
 AccMirror     * mirror( vpb_accumulator_array_t * aa );
@@ -199,6 +214,8 @@ void comm_allsum_d( double * v, int n );
 bool comm_ready();
 void comm_shutdown();
 void release_boundary_buffers();
+void host_resize_particles( vpb_species_t * sp, size_t n );   // boundary_p.cc:346-394 for host-resident arrays
+void host_resize_movers( vpb_species_t * sp, size_t n );
 void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
 // field boundary machinery shared by vpb_fields.cu and vpb_divclean.cu
 bool face_is_remote( const GridMirror * gm, int X, int side );

@@ -97,6 +97,13 @@ class Simulation:
     def grid_struct(g):
         return C.cast(g, C.POINTER(abi.Grid)).contents
 
+    def neighbor_table(self):
+        """g->neighbor as an (nv, 6) int64 view: the table set_region_bc edits
+        (deck/wrapper.h:255-310)."""
+        import numpy as np
+        g = self.grid_struct(self.g)
+        return np.ctypeslib.as_array(g.neighbor, shape=(g.nv, 6))
+
     def define_fields(self, damp=0.0, eps=1.0, mu=1.0, sigma=0.0, materials=()):
         self.m_list = self.host.material_list(eps, mu, sigma, materials)
         self.fa = self.host.field_array(self.g, self.m_list, damp)

@@ -44,7 +44,7 @@ def load_b200():
         "vpic_b200_set_reference_pipelines": (None, [i]),
         "vpic_b200_abi_check": (i, [i] * 6),
         "vpic_b200_sync_to_host": (None, [_P]), "vpic_b200_sync_from_host": (None, [_P]),
-        "vpic_b200_forget": (None, [_P]), "vpic_b200_device_synchronize": (None, []),
+        "vpic_b200_forget": (None, [_P]), "vpic_b200_grid_changed": (None, [_P]), "vpic_b200_device_synchronize": (None, []),
         "vpic_b200_launch_count": (C.c_longlong, []), "vpic_b200_transfer_bytes": (None, [C.POINTER(C.c_longlong)]), "vpic_b200_stream": (_P, []),
         "vpic_b200_device_ptr": (_P, [_P, i]),
         "vpic_b200_load_uniform_maxwellian": (None, [_P, i, f, f, C.c_uint64]),
