@@ -131,6 +131,21 @@ typedef struct vpb_accumulator_array {
   vpb_grid_t        *g;
 } vpb_accumulator_array_t;
 
+/* ---- hydro moments: src/sf_interface/sf_interface.h:185-198 -------------- */
+
+typedef struct vpb_hydro {
+  float jx, jy, jz, rho;   /* current and charge density   */
+  float px, py, pz, ke;    /* momentum and kinetic energy density */
+  float txx, tyy, tzz;     /* stress diagonal              */
+  float tyz, tzx, txy;     /* stress off-diagonal          */
+  float _pad[2];           /* 64 B                         */
+} vpb_hydro_t;
+
+typedef struct vpb_hydro_array {
+  vpb_hydro_t *h;
+  vpb_grid_t  *g;
+} vpb_hydro_array_t;
+
 /* ---- fields: src/field_advance/field_advance.h:152-229 ------------------- */
 
 typedef int16_t vpb_material_id;
@@ -231,6 +246,7 @@ VPB_SA( sizeof(vpb_particle_t)==32,           "particle_t is 32 B" );
 VPB_SA( sizeof(vpb_particle_mover_t)==16,     "particle_mover_t is 16 B" );
 VPB_SA( sizeof(vpb_particle_injector_t)==48,  "particle_injector_t is 48 B" );
 VPB_SA( sizeof(vpb_interpolator_t)==80,       "interpolator_t is 80 B (no USE_V8/V16)" );
+VPB_SA( sizeof(vpb_hydro_t)==64,              "hydro_t is 64 B" );
 VPB_SA( sizeof(vpb_accumulator_t)==48,        "accumulator_t is 48 B (no USE_V8/V16)" );
 VPB_SA( sizeof(vpb_field_t)==80,              "field_t is 80 B" );
 VPB_SA( offsetof(vpb_field_t,cbx)==16 && offsetof(vpb_field_t,tcax)==32 &&

@@ -84,6 +84,17 @@ void vpic_b200_clean_div_b( vpb_field_array_t * fa );                 /* clean_d
    src/species_advance/standard/rho_p.cc:22-112). */
 void accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp );
 
+/* Hydro moments for the dump path.
+   Replace src/species_advance/species_advance.h accumulate_hydro_p
+   (standard/hydro_p.c:26-167) and src/sf_interface/sf_interface.h:214-225
+   clear_hydro_array / synchronize_hydro_array (hydro_array.c:52-222). */
+void accumulate_hydro_p( vpb_hydro_array_t * ha, const vpb_species_t * sp, const vpb_interpolator_array_t * ia );
+void clear_hydro_array( vpb_hydro_array_t * ha );
+void synchronize_hydro_array( vpb_hydro_array_t * ha );
+/* standalone construction; a reference build keeps its own new_/delete_hydro_array */
+vpb_hydro_array_t * vpic_b200_new_hydro_array( vpb_grid_t * g );
+void vpic_b200_delete_hydro_array( vpb_hydro_array_t * ha );
+
 /* ======================= Part 2: control surface ========================== */
 
 enum { VPB_COHERENCE_STRICT = 0,   /* every call: host structs in, host structs out  */

@@ -80,7 +80,7 @@ class RefHost:
             "material": (_P, [C.c_char_p] + [f] * 12),
             "append_material": (_P, [_P, C.POINTER(_P)]),
             "new_standard_field_array": (_P, [_P, _P, f]),
-            "new_interpolator_array": (_P, [_P]), "new_accumulator_array": (_P, [_P]),
+            "new_interpolator_array": (_P, [_P]), "new_accumulator_array": (_P, [_P]), "new_hydro_array": (_P, [_P]),
             "species": (_P, [C.c_char_p, f, f, C.c_size_t, C.c_size_t, i, i, _P]),
         }
         for name, (res, args) in sig.items():
@@ -120,6 +120,9 @@ class RefHost:
 
     def accumulator_array(self, g, n_pipeline):
         return self.L.new_accumulator_array(g)      # n_pipeline is the booted --tpp
+
+    def hydro_array(self, g):
+        return self.L.new_hydro_array(g)
 
     def species(self, name, q, m, max_np, max_nm, sort_interval, sort_out_of_place, g, host_arrays=True):
         return self.L.species(name.encode(), q, m, max_np, max_nm, sort_interval, sort_out_of_place, g)

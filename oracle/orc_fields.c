@@ -916,3 +916,105 @@ double orc_synchronize_tang_e_norm_b( vpb_field_array_t * fa ) {
   if( orc_allsum ) orc_allsum( &err, 1 );
   return err;
 }
+
+/* ---- hydro moments (8(f) N3) ------------------------------------------------ */
+
+/* hydro_array.c:52-56 */
+void orc_clear_hydro_array( vpb_hydro_array_t * ha ) {
+  if( !ha ) ORC_FAIL( "NULL hydro array" );
+  memset( ha->h, 0, sizeof(vpb_hydro_t)*(size_t)ha->g->nv );
+}
+
+/* hydro_p.c:26-167.  One serial loop over the particles: half a Boris step to
+   time-centre the momentum, then the 14 moments spread trilinearly over the
+   eight nodes of the cell.  sqrt() of the float argument is the DOUBLE sqrt
+   (:91), and the (1./3.), 0.4 constants make :96 a double expression. */
+void orc_accumulate_hydro_p( vpb_hydro_array_t * ha, const vpb_species_t * sp, const vpb_interpolator_array_t * ia ) {
+  if( !ha || !sp || !ia || ha->g!=sp->g || ha->g!=ia->g ) ORC_FAIL( "Bad args" );
+  vpb_hydro_t * h = ha->h; const vpb_particle_t * p = sp->p; const vpb_interpolator_t * f = ia->i;
+  const vpb_grid_t * g = sp->g;
+  const float c = g->cvac, qsp = sp->q, mspc = sp->m*c;
+  const float qdt_2mc = (qsp*g->dt)/(2*mspc), qdt_4mc2 = qdt_2mc/(2*c), r8V = g->r8V;
+  const int sx = 1, sy = g->nx+2, sz = (g->nx+2)*(g->ny+2);
+  const int off[8] = { 0, sx, sy, sy+sx, sz, sz+sx, sz+sy, sz+sy+sx };
+  for( int n=0; n<sp->np; n++ ) {
+    float dx = p[n].dx, dy = p[n].dy, dz = p[n].dz; const int i = p[n].i;
+    float ux = p[n].ux, uy = p[n].uy, uz = p[n].uz; const float w = p[n].w;
+    float w0, w1, w2, w3, w4, w5, w6, w7, vx, vy, vz, ke_mc;
+    ux += qdt_2mc*( ( f[i].ex + dy*f[i].dexdy ) + dz*( f[i].dexdz + dy*f[i].d2exdydz ) );
+    uy += qdt_2mc*( ( f[i].ey + dz*f[i].deydz ) + dx*( f[i].deydx + dz*f[i].d2eydzdx ) );
+    uz += qdt_2mc*( ( f[i].ez + dx*f[i].dezdx ) + dy*( f[i].dezdy + dx*f[i].d2ezdxdy ) );
+    w5 = f[i].cbx + dx*f[i].dcbxdx;
+    w6 = f[i].cby + dy*f[i].dcbydy;
+    w7 = f[i].cbz + dz*f[i].dcbzdz;
+    ke_mc = ux*ux + uy*uy + uz*uz;
+    vz = (float)sqrt( (double)( 1+ke_mc ) );
+    ke_mc *= c/( vz+1 );
+    vz = c/vz;
+    w0 = qdt_4mc2*vz;
+    w1 = w5*w5 + w6*w6 + w7*w7;
+    w2 = w0*w0*w1;
+    w3 = (float)( (double)w0*( 1 + ( 1./3. )*(double)w2*( 1 + 0.4*(double)w2 ) ) );
+    w4 = w3/( 1 + w1*w3*w3 ); w4 += w4;
+    w0 = ux + w3*( uy*w7 - uz*w6 );
+    w1 = uy + w3*( uz*w5 - ux*w7 );
+    w2 = uz + w3*( ux*w6 - uy*w5 );
+    ux += w4*( w1*w7 - w2*w6 );
+    uy += w4*( w2*w5 - w0*w7 );
+    uz += w4*( w0*w6 - w1*w5 );
+    vx = ux*vz; vy = uy*vz; vz *= uz;
+    w0 = r8V*w; dx *= w0; w1 = w0+dx; w0 -= dx;
+    w3 = 1+dy; w2 = w0*w3; w3 *= w1; dy = 1-dy; w0 *= dy; w1 *= dy;
+    w7 = 1+dz; w4 = w0*w7; w5 = w1*w7; w6 = w2*w7; w7 *= w3;
+    dz = 1-dz; w0 *= dz; w1 *= dz; w2 *= dz; w3 *= dz;
+    const float wn[8] = { w0, w1, w2, w3, w4, w5, w6, w7 };
+    for( int k=0; k<8; k++ ) {
+      vpb_hydro_t * hk = h + i + off[k];
+      float t = qsp*wn[k];
+      hk->jx += t*vx; hk->jy += t*vy; hk->jz += t*vz; hk->rho += t;
+      t = mspc*wn[k];
+      const float px = t*ux, py = t*uy, pz = t*uz;
+      hk->px += px; hk->py += py; hk->pz += pz; hk->ke += t*ke_mc;
+      hk->txx += px*vx; hk->tyy += py*vy; hk->tzz += pz*vz;
+      hk->tyz += py*vz; hk->tzx += pz*vx; hk->txy += px*vy;
+    }
+  }
+}
+
+/* hydro_array.c:71-222: double the moments on locally handled faces (half
+   cells), then the twice-weighted sum with each remote (or periodic-to-self)
+   neighbour's copy of the shared node plane, axis by axis. */
+void orc_synchronize_hydro_array( vpb_hydro_array_t * ha ) {
+  if( !ha ) ORC_FAIL( "NULL hydro array" );
+  vpb_hydro_t * h = ha->h; const vpb_grid_t * g = ha->g;
+  const int nx = g->nx, ny = g->ny, nz = g->nz; const int n[3] = { nx, ny, nz };
+  const float d[3] = { g->dx, g->dy, g->dz };
+  for( int side=-1; side<=1; side+=2 ) for( int X=0; X<3; X++ ) {          /* ADJUST_HYDRO order: -x,-y,-z,+x,+y,+z */
+    if( !orc_bc_is_local( orc_face_bc( g, X, side ) ) ) continue;
+    orc_box_t b = orc_plane( g, X, side<0 ? 1 : n[X]+1, ORC_NODE );
+    ORC_BOX_LOOP(b) { float * v = &h[ORC_VOX(x,y,z)].jx; for( int c=0; c<14; c++ ) v[c] *= 2; }
+  }
+  for( int X=0; X<3; X++ ) {
+    const int Y = (X+1)%3, Z = (X+2)%3;
+    int nf = 1 + 14*(n[Y]+1)*(n[Z]+1);
+    float * buf = (float *)malloc( 4*sizeof(float)*(size_t)nf );
+    float * s[2] = { buf, buf+nf }, * r[2] = { buf+2*nf, buf+3*nf };
+    for( int k=0; k<2; k++ ) {
+      float * p = s[k];
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X]+1, ORC_NODE );
+      *(p++) = d[X];
+      ORC_BOX_LOOP(b) { const float * v = &h[ORC_VOX(x,y,z)].jx; for( int c=0; c<14; c++ ) *(p++) = v[c]; }
+    }
+    int got[2];
+    orc_face_exchange( g, X, s[0], s[1], r[0], r[1], nf, &got[0], &got[1] );
+    for( int k=0; k<2; k++ ) {
+      if( !got[k] ) continue;
+      const float * p = r[k];
+      float rw = *(p++), lw = rw + d[X];
+      rw /= lw; lw = d[X]/lw; lw += lw; rw += rw;
+      orc_box_t b = orc_plane( g, X, k==0 ? 1 : n[X]+1, ORC_NODE );
+      ORC_BOX_LOOP(b) { float * v = &h[ORC_VOX(x,y,z)].jx; for( int c=0; c<14; c++ ) v[c] = lw*v[c] + rw*(*(p++)); }
+    }
+    free( buf );
+  }
+}

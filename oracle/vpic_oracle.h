@@ -85,6 +85,11 @@ void orc_energy_f( double * en /*[6]*/, const vpb_field_array_t * fa );
 /* N1: divergence cleaning, charge synchronisation, shared-face synchronisation
    (sfa_private.h:256-373; local.c; remote.c:137-415,534-624; rho_p.cc:22-112)
    and N2's field initialisation kernels. */
+/* 8(f) N3: hydro moments for the dump path */
+void   orc_clear_hydro_array( vpb_hydro_array_t * ha );                           /* hydro_array.c:52-56 */
+void   orc_accumulate_hydro_p( vpb_hydro_array_t * ha, const vpb_species_t * sp,
+                               const vpb_interpolator_array_t * ia );             /* hydro_p.c:26-167 */
+void   orc_synchronize_hydro_array( vpb_hydro_array_t * ha );                     /* hydro_array.c:71-222 */
 void   orc_clear_rhof( vpb_field_array_t * fa );                                  /* sfa.c:239-245 */
 void   orc_accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp );   /* rho_p.cc:22-112 */
 void   orc_synchronize_rho( vpb_field_array_t * fa );                             /* remote.c:534-624 */

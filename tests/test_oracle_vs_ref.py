@@ -224,3 +224,19 @@ def test_boundary_codes_inside_the_box():
         compare(so, sr, f"step {step}")
     assert sum(so.sp_struct(a).np for a in so.species) < n0 - 50
     assert list(counts[0]) == list(counts[1]) and sum(counts[0]) > 50
+
+
+@pytest.mark.parametrize("kind", ["periodic", "absorbing", "metal"])
+def test_hydro_moments(kind):
+    """accumulate_hydro_p + synchronize_hydro_array (hydro_p.c:26-167,
+    hydro_array.c:71-222): the 14 moments per node for each species, oracle
+    against the compiled reference, bit for bit."""
+    so, sr = pair(kind=kind, n=(7, 6, 5), damp=0.01)
+    for s in (so, sr):
+        s.initialize()
+        s.advance()
+    for a, b in zip(so.species, sr.species):
+        ho, hr = so.hydro_moments(a).copy(), sr.hydro_moments(b).copy()
+        for k in ho.dtype.names[:14]:
+            assert same_bits(ho[k], hr[k]), k
+        assert np.abs(ho["rho"]).max() > 0 and np.abs(ho["txx"]).max() > 0

@@ -57,6 +57,10 @@ class InterpolatorArray(C.Structure):   # sf_interface.h:77-80
     _fields_ = [("i", C.POINTER(Interpolator)), ("g", C.POINTER(Grid))]
 
 
+class HydroArray(C.Structure):          # sf_interface.h:194-198
+    _fields_ = [("h", C.c_void_p), ("g", C.POINTER(Grid))]
+
+
 class Accumulator(C.Structure):     # sf_interface.h:115-123
     _fields_ = [("jx", C.c_float * 4), ("jy", C.c_float * 4), ("jz", C.c_float * 4)]
 
@@ -131,7 +135,10 @@ interp_dtype = np.dtype([(n, "f4") for n in
                          ("ex", "dexdy", "dexdz", "d2exdydz", "ey", "deydz", "deydx", "d2eydzdx",
                           "ez", "dezdx", "dezdy", "d2ezdxdy", "cbx", "dcbxdx", "cby", "dcbydy", "cbz", "dcbzdz")] +
                         [("_pad1", "f4", (2,))])
+hydro_dtype = np.dtype([(n, "f4") for n in ("jx", "jy", "jz", "rho", "px", "py", "pz", "ke",
+                                             "txx", "tyy", "tzz", "tyz", "tzx", "txy")] + [("_pad", "f4", (2,))])
 assert particle_dtype.itemsize == 32 and field_dtype.itemsize == 80 and interp_dtype.itemsize == 80
+assert hydro_dtype.itemsize == 64
 
 
 def as_array(ptr, count, dtype):

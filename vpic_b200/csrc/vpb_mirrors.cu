@@ -237,6 +237,7 @@ void vpic_b200_sync_to_host( void * obj ) {
   if( auto m = VPB_FIND( fields,  obj ) ) { to_host( m ); return; }
   if( auto m = VPB_FIND( interps, obj ) ) { to_host( m ); return; }
   if( auto m = VPB_FIND( accs,    obj ) ) { to_host( m ); return; }
+  if( auto m = VPB_FIND( hydros,  obj ) ) { to_host( m ); return; }
 }
 
 void vpic_b200_sync_from_host( void * obj ) {
@@ -246,6 +247,7 @@ void vpic_b200_sync_from_host( void * obj ) {
   if( r.fields.count( obj )  ) { auto m = r.fields[obj];  m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
   if( r.interps.count( obj ) ) { auto m = r.interps[obj]; m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
   if( r.accs.count( obj )    ) { auto m = r.accs[obj];    m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
+  if( r.hydros.count( obj )  ) { auto m = r.hydros[obj];  m->dev_valid = false; m->host_valid = true; to_device( m ); return; }
   VPB_ERROR( "vpic_b200_sync_from_host: object %p has no device mirror yet", obj );
 }
 
@@ -257,6 +259,7 @@ void vpic_b200_forget( void * obj ) {
   if( r.fields.count( obj )  ) { auto m = r.fields[obj]; unpin_host( m->host->f ); cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
   if( r.interps.count( obj ) ) { auto m = r.interps[obj]; unpin_host( m->host->i ); cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
   if( r.accs.count( obj )    ) { auto m = r.accs[obj]; unpin_host( m->host->a ); cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }
+  if( r.hydros.count( obj )  ) { release( r.hydros[obj] ); r.hydros.erase( obj ); return; }
   if( r.grids.count( obj )   ) { auto m = r.grids[obj]; cudaFree( m->d_neighbor ); delete m; r.grids.erase( obj ); return; }
 }
 
@@ -276,6 +279,7 @@ void * vpic_b200_device_ptr( void * obj, int which ) {
   if( auto m = VPB_FIND( fields,  obj ) ) return (void *)m->d;
   if( auto m = VPB_FIND( interps, obj ) ) return (void *)m->d;
   if( auto m = VPB_FIND( accs,    obj ) ) return (void *)m->d;
+  if( auto m = VPB_FIND( hydros,  obj ) ) return (void *)m->d;
   return nullptr;
 }
 
@@ -288,6 +292,7 @@ void vpic_b200_finalize( void ) {
   for( auto & kv : r.fields  ) keys.push_back( kv.first );
   for( auto & kv : r.interps ) keys.push_back( kv.first );
   for( auto & kv : r.accs    ) keys.push_back( kv.first );
+  for( auto & kv : r.hydros  ) keys.push_back( kv.first );
   for( auto & kv : r.grids   ) keys.push_back( kv.first );
   for( auto k : keys ) vpic_b200_forget( (void *)k );
   release_boundary_buffers(); release_sort_buffers(); release_parity_buffers(); comm_shutdown(); unpin_all();

@@ -22,6 +22,7 @@
 // arithmetic of the FAST kernel: a verification mode, not the fast path.
 #include "vpb_push.cuh"
 #include "vpb_sortutil.cuh"
+#include "vpb_hydro.cuh"
 
 namespace vpb {
 
@@ -354,6 +355,89 @@ void accumulate_rho_p_parity( FieldMirror * mf, SpeciesMirror * ms, float q_8V )
     int * big   = (int *)need( B_big, sizeof(int)*( 2*(size_t)nrec+64 ) );
     bin_indices( key, nrec, g.nv, start, perm );
     k_rho_sum<<< div_up( g.nv, FIX_WARPS ), 32*FIX_WARPS, 0, r.stream >>>( start, g.nv, nrec, perm, big, val, mf->comp( F_RHOF ) );
+    VPB_CHECK_LAUNCH(); r.launches++;
+  }
+}
+
+// ---- accumulate_hydro_p in the reference's order (hydro_p.c:62-165) ----------
+// Same scheme as accumulate_rho_p above with 14 moments per record: the
+// per-particle part (half Boris step, velocities, weights) is computed once
+// into a 16-float record; every node's (particle, corner) records are put in
+// ascending order by one warp, whose lanes form the 14 increments of 32
+// records at a time and add them one record after the other.
+__global__ void __launch_bounds__(256)
+k_hydro_records( int * __restrict__ key, float * __restrict__ rec, const vpb_particle_t * __restrict__ p, int n,
+                 const float * __restrict__ ip, int sy, int sz, HydroCoef k ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if( i>=n ) return;
+  const float4 * pp = reinterpret_cast<const float4 *>( p + i );
+  const float4 r0 = __ldg( pp ), r1 = __ldg( pp+1 );
+  const int v = __float_as_int( r0.w );
+  const HydroParticle h = hydro_particle( r0, r1, load_interp( ip, v ), k );
+  int * kk = key + 8*(size_t)i;
+  kk[0] = v;    kk[1] = v+1;    kk[2] = v+sy;    kk[3] = v+sy+1;
+  kk[4] = v+sz; kk[5] = v+sz+1; kk[6] = v+sz+sy; kk[7] = v+sz+sy+1;
+  float4 * o = reinterpret_cast<float4 *>( rec + 16*(size_t)i );
+  o[0] = make_float4( h.wn[0], h.wn[1], h.wn[2], h.wn[3] );
+  o[1] = make_float4( h.wn[4], h.wn[5], h.wn[6], h.wn[7] );
+  o[2] = make_float4( h.ux, h.uy, h.uz, h.vx );
+  o[3] = make_float4( h.vy, h.vz, h.ke_mc, 0.f );
+}
+
+__global__ void __launch_bounds__(32*FIX_WARPS)
+k_hydro_sum( const int * __restrict__ start, int nbin, int nrec, int * __restrict__ perm, int * __restrict__ big_scratch,
+             const float * __restrict__ rec, float * __restrict__ hy, HydroCoef k ) {
+  __shared__ int s[FIX_WARPS][FIX_SMEM];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int bin = blockIdx.x*FIX_WARPS + w;
+  if( bin>=nbin ) return;
+  const int b = start[bin], e = bin+1<nbin ? start[bin+1] : nrec, n = e-b;
+  if( n<=0 ) return;
+  int n2 = 32; while( n2<n ) n2 <<= 1;
+  int * a = n2<=FIX_SMEM ? s[w] : big_scratch + 2*(size_t)b;
+  for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+  __threadfence_block(); __syncwarp();
+  bitonic_mem( a, n2, lane );
+  float * h = hy + (size_t)bin*HY_STRIDE;
+  float acc[14];
+# pragma unroll
+  for( int c=0; c<14; c++ ) acc[c] = h[c];
+  for( int t0=0; t0<n; t0+=32 ) {
+    const int cnt = n-t0<32 ? n-t0 : 32;
+    float o[14];
+#   pragma unroll
+    for( int c=0; c<14; c++ ) o[c] = 0.f;
+    if( lane<cnt ) {
+      const int r = a[t0+lane];
+      const float * q = rec + 16*(size_t)( r>>3 );
+      hydro_node_terms( o, q[ r&7 ], k, q[8], q[9], q[10], q[11], q[12], q[13], q[14] );
+    }
+    for( int t=0; t<cnt; t++ ) {
+#     pragma unroll
+      for( int c=0; c<14; c++ ) acc[c] = acc[c] + __shfl_sync( 0xffffffffu, o[c], t );
+    }
+  }
+  if( lane==0 ) {
+#   pragma unroll
+    for( int c=0; c<14; c++ ) h[c] = acc[c];
+  }
+}
+
+void accumulate_hydro_p_parity( HydroMirror * mh, SpeciesMirror * ms, InterpMirror * mi, const HydroCoef & k ) {
+  Runtime & r = rt();
+  const GridDev & g = mh->grid->dev;
+  const int CHUNK = 1<<22;                            // particles per pass (32 M records)
+  for( long long first=0; first<ms->np; first+=CHUNK ) {
+    const int n = ms->np-first<CHUNK ? (int)( ms->np-first ) : CHUNK, nrec = 8*n;
+    int   * key = (int *)need( B_bin, sizeof(int)*( (size_t)nrec+32 ) );
+    float * rec = (float *)need( B_val, sizeof(float)*16*( (size_t)n+8 ) );
+    k_hydro_records<<< div_up( n, 256 ), 256, 0, r.stream >>>( key, rec, ms->d_p + first, n, mi->d, g.sy, g.sz, k );
+    VPB_CHECK_LAUNCH(); r.launches++;
+    int * start = (int *)need( B_start, sizeof(int)*( (size_t)g.nv+64 ) );
+    int * perm  = (int *)need( B_perm, sizeof(int)*( (size_t)nrec+32 ) );
+    int * big   = (int *)need( B_big, sizeof(int)*( 2*(size_t)nrec+64 ) );
+    bin_indices( key, nrec, g.nv, start, perm );
+    k_hydro_sum<<< div_up( g.nv, FIX_WARPS ), 32*FIX_WARPS, 0, r.stream >>>( start, g.nv, nrec, perm, big, rec, mh->d, k );
     VPB_CHECK_LAUNCH(); r.launches++;
   }
 }

@@ -125,6 +125,15 @@ struct AccMirror {
   bool dev_valid = false, host_valid = true;
 };
 
+struct HydroMirror {
+  vpb_hydro_array_t * host = nullptr;
+  GridMirror * grid = nullptr;
+  float * d = nullptr;             // nv * 16 floats == host hydro_t layout
+  float * d_face = nullptr;        // [send_lo | send_hi | recv_lo | recv_hi] for synchronize_hydro_array
+  size_t face_floats = 0;
+  bool dev_valid = false, host_valid = true;
+};
+
 struct SpeciesMirror {
   vpb_species_t * host = nullptr;
   GridMirror * grid = nullptr;
@@ -159,6 +168,7 @@ struct Runtime {
   std::unordered_map<const void *, InterpMirror *>  interps;
   std::unordered_map<const void *, AccMirror *>     accs;
   std::unordered_map<const void *, SpeciesMirror *> species;
+  std::unordered_map<const void *, HydroMirror *>   hydros;
 };
 
 Runtime & rt();
@@ -179,6 +189,8 @@ FieldMirror   * mirror( vpb_field_array_t * fa );
 InterpMirror  * mirror( vpb_interpolator_array_t * ia );
 AccMirror     * mirror( vpb_accumulator_array_t * aa );
 SpeciesMirror * mirror( vpb_species_t * sp );
+HydroMirror   * mirror( vpb_hydro_array_t * ha );
+void release( HydroMirror * m );
 
 // Coherence helpers.  to_device(): make the device copy current (uploads if the
 // host copy is the valid one, or always in STRICT mode).  to_host(): the
@@ -187,6 +199,7 @@ void to_device( FieldMirror * m );   void to_host( FieldMirror * m );
 void to_device( InterpMirror * m );  void to_host( InterpMirror * m );
 void to_device( AccMirror * m );     void to_host( AccMirror * m );
 void to_device( SpeciesMirror * m ); void to_host( SpeciesMirror * m );
+void to_device( HydroMirror * m );   void to_host( HydroMirror * m );
 void movers_to_host( SpeciesMirror * m );
 template<class M> inline void mark_dev_written( M * m ) { m->dev_valid = true; m->host_valid = false; }
 // In STRICT mode every entry point finishes by pushing what it wrote back.
@@ -200,6 +213,8 @@ struct PushCoef;
 void advance_p_parity( SpeciesMirror *, AccMirror *, InterpMirror *, const PushCoef & );
 void reduce_accumulators_parity( AccMirror * );
 void accumulate_rho_p_parity( FieldMirror * mf, SpeciesMirror * ms, float q_8V );   // reference summation order
+struct HydroCoef;
+void accumulate_hydro_p_parity( HydroMirror * mh, SpeciesMirror * ms, InterpMirror * mi, const HydroCoef & k );   // reference summation order
 void energy_f_parity( double * en6, FieldMirror * m );           // local (pre-allreduce) energies, reference summation order
 double energy_p_parity( SpeciesMirror * ms, InterpMirror * mi, float qdt_2mc, float msp );
 // counting-sort front end shared by sort_p and the PARITY deposit: start[0..nbin] = first slot of each bin,

@@ -54,6 +54,9 @@ class B200Host:
     def accumulator_array(self, g, n_pipeline):
         return self.L.vpic_b200_new_accumulator_array(g, n_pipeline)
 
+    def hydro_array(self, g):
+        return self.L.vpic_b200_new_hydro_array(g)
+
     def species(self, name, q, m, max_np, max_nm, sort_interval, sort_out_of_place, g, host_arrays=True):
         return self.L.vpic_b200_new_species(name.encode(), q, m, max_np, max_nm, sort_interval,
                                             sort_out_of_place, g, 1 if host_arrays else 0)
@@ -162,6 +165,22 @@ class Simulation:
     def fields(self):
         fa = C.cast(self.fa, C.POINTER(abi.FieldArray)).contents
         return abi.as_array(fa.f, self.grid_struct(self.g).nv, abi.field_dtype)
+
+    def hydro(self):
+        """The hydro array (created on first use) as a numpy view."""
+        if getattr(self, "ha", None) is None:
+            self.ha = self.host.hydro_array(self.g)
+        ha = C.cast(self.ha, C.POINTER(abi.HydroArray)).contents
+        return abi.as_array(ha.h, self.grid_struct(self.g).nv, abi.hydro_dtype)
+
+    def hydro_moments(self, sp):
+        """What dump_hydro computes for one species (src/vpic/dump.cc:227-229):
+        clear, accumulate, synchronize."""
+        self.hydro()
+        self.be.clear_hydro_array(self.ha)
+        self.be.accumulate_hydro_p(self.ha, sp, self.ia)
+        self.be.synchronize_hydro_array(self.ha)
+        return self.hydro()
 
     def interpolators(self):
         ia = C.cast(self.ia, C.POINTER(abi.InterpolatorArray)).contents

@@ -57,6 +57,7 @@ def load_b200():
         "vpic_b200_delete_species": (None, [_P]),
         "vpic_b200_new_interpolator_array": (_P, [_P]), "vpic_b200_delete_interpolator_array": (None, [_P]),
         "vpic_b200_new_accumulator_array": (_P, [_P, i]), "vpic_b200_delete_accumulator_array": (None, [_P]),
+        "vpic_b200_new_hydro_array": (_P, [_P]), "vpic_b200_delete_hydro_array": (None, [_P]),
         "vpic_b200_new_material": (_P, [C.c_char_p, f, f, f]),
         "vpic_b200_append_material": (_P, [_P, C.POINTER(_P)]),
         "new_standard_field_array": (_P, [_P, _P, f]), "delete_field_array": (None, [_P]),
@@ -75,6 +76,8 @@ _SPECIES_FUNCS = {
     "load_interpolator_array": (None, [_P, _P]), "clear_accumulator_array": (None, [_P]),
     "reduce_accumulator_array": (None, [_P]), "unload_accumulator_array": (None, [_P, _P]),
     "accumulate_rho_p": (None, [_P, _P]),
+    # hydro moments of the dump path (hydro_p.c, hydro_array.c)
+    "accumulate_hydro_p": (None, [_P, _P, _P]), "clear_hydro_array": (None, [_P]), "synchronize_hydro_array": (None, [_P]),
 }
 _FIELD_FUNCS = {
     "advance_b": (None, [_P, C.c_float]), "advance_e": (None, [_P, C.c_float]),
