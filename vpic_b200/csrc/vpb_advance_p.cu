@@ -32,18 +32,31 @@
 
 namespace vpb {
 
-constexpr int AP_K      = 8;            // consecutive particles per lane
+#ifndef VPB_AP_K
+#define VPB_AP_K 8
+#endif
+#ifndef VPB_AP_NBUF
+#define VPB_AP_NBUF 1
+#endif
+#ifndef VPB_AP_MINBLK
+#define VPB_AP_MINBLK 5
+#endif
+constexpr int AP_K      = VPB_AP_K;     // consecutive particles per lane
+constexpr int AP_NBUF   = VPB_AP_NBUF;  // tile buffers per warp: 2 = the next tile is loading while this one is pushed
 constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
-constexpr int AP_WARPS  = 4;            // warps per block
-constexpr int AP_MINBLK = 5;            // resident blocks per SM the registers are budgeted for
+#ifndef VPB_AP_WARPS
+#define VPB_AP_WARPS 4
+#endif
+constexpr int AP_WARPS  = VPB_AP_WARPS;            // warps per block
+constexpr int AP_MINBLK = VPB_AP_MINBLK;            // resident blocks per SM the registers are budgeted for
 constexpr int AP_QCAP   = 64;           // crosser queue entries per warp
 
 struct __align__(128) WarpTile {
-  float4 tile[2*AP_TILE];               // the particles, array order (8 KB)
+  float4 tile[AP_NBUF][2*AP_TILE];      // the particles, array order (8 KB per buffer)
   // queue of particles that left their voxel: remaining displacement + index
   // (position, voxel, momentum and weight are still in the particle's slot)
   float4 q[AP_QCAP];                    // dispx, dispy, dispz, index relative to the launch's first particle
-  unsigned long long bar;               // mbarrier of the tile load
+  unsigned long long bar[AP_NBUF];      // mbarrier of each buffer's tile load
 };
 
 __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_t)__cvta_generic_to_shared( p ); }
@@ -52,7 +65,7 @@ __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_
 // Entries of the tile that is still in shared memory are finished there;
 // entries carried over from tiles already written back are finished in global
 // memory (the caller has waited for those bulk stores to complete).
-__device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, int lane,
+__device__ __forceinline__ void drain_crossers( WarpTile & S, float4 * __restrict__ T, int base, int n, int lane,
                                                 vpb_particle_t * __restrict__ p, int idx_base, long long t0, int cnt,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
                                                 int max_nm, int * __restrict__ counters, const GridDev & g, float qsp ) {
@@ -61,7 +74,7 @@ __device__ __forceinline__ void drain_crossers( WarpTile & S, int base, int n, i
   const float4 qe = S.q[e];
   const int rel = __float_as_int( qe.w );
   const bool in_tile = rel>=t0 && rel<t0+cnt;
-  float4 * slot = in_tile ? &S.tile[ 2*(int)( rel-t0 ) ] : reinterpret_cast<float4 *>( p + rel );
+  float4 * slot = in_tile ? &T[ 2*(int)( rel-t0 ) ] : reinterpret_cast<float4 *>( p + rel );
   const float4 r0 = slot[0], r1 = slot[1];
   MoveState ms;
   ms.dx = r0.x; ms.dy = r0.y; ms.dz = r0.z; ms.i = __float_as_int( r0.w );
@@ -99,15 +112,26 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   const int total_warps = gridDim.x*AP_WARPS;
   const int gw = blockIdx.x*AP_WARPS + warp;
   if( gw>=ntile ) return;
-  const uint32_t bar = smem_u32( &S.bar ), tile_s = smem_u32( S.tile );
   if( lane==0 ) {
-    asm volatile( "mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar) : "memory" );
+#   pragma unroll
+    for( int b=0; b<AP_NBUF; b++ ) asm volatile( "mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(smem_u32( &S.bar[b] )) : "memory" );
     asm volatile( "fence.mbarrier_init.release.cluster;" ::: "memory" );
     asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
   }
   __syncwarp();
 
-  uint32_t phase = 0;
+  // one elected lane starts the bulk copy of a tile into buffer b
+  auto start_load = [&]( int tile, int b ) {
+    const long long t0 = (long long)tile*AP_TILE;
+    const uint32_t bytes = (uint32_t)( ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE )*32u;
+    const uint32_t bar = smem_u32( &S.bar[b] ), dst = smem_u32( S.tile[b] );
+    asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
+    asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                  :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
+  };
+
+  uint32_t phase = 0;                          // bit b: parity the next wait on buffer b expects
+  int buf = 0;
   int qn = 0;                                  // queued crossers (warp uniform)
   int n_carry = 0;                             // of which: from tiles whose bulk store may still be in flight
   int cur = -1;                                // voxel whose current sums this lane holds in run[]
@@ -117,33 +141,39 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   for( int k=0; k<12; k++ ) run[k] = 0.f;
   Interp f = {};
 
+  if( AP_NBUF>1 && lane==0 ) start_load( gw, 0 );
   for( int tile=gw; tile<ntile; tile+=total_warps ) {
     const long long t0 = (long long)tile*AP_TILE;
     const int cnt = ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE;
-    if( lane==0 ) {
-      const uint32_t bytes = (uint32_t)cnt*32u;
-      asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
-      asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                    :: "r"(tile_s), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
-    }
+    if( AP_NBUF==1 && lane==0 ) start_load( tile, 0 );
+    float4 * __restrict__ T = S.tile[buf];
     {
+      const uint32_t bar = smem_u32( &S.bar[buf] );
       uint32_t ok;
       do {
         asm volatile( "{ .reg .pred P1; mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2; selp.u32 %0, 1, 0, P1; }"
-                      : "=r"(ok) : "r"(bar), "r"(phase) : "memory" );
+                      : "=r"(ok) : "r"(bar), "r"( ( phase>>buf )&1u ) : "memory" );
       } while( !ok );
-      phase ^= 1u;
+      phase ^= 1u<<buf;
     }
 
 #   pragma unroll 1
     for( int k=0; k<AP_K; k++ ) {
+      if( AP_NBUF>1 && k==AP_K/2 && tile+total_warps<ntile ) {
+        // the other buffer's store was issued half a tile ago: its shared-memory
+        // read is long done, so the next tile can start loading into it now
+        if( lane==0 ) {
+          asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );
+          start_load( tile+total_warps, buf^1 );
+        }
+      }
       // rotate the start of each lane's run so the 128-bit shared accesses of a
       // quarter warp spread over the banks
       const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
       bool cross = false;
       float cux = 0, cuy = 0, cuz = 0;
       if( loc<cnt ) {
-        const float4 r0 = S.tile[2*loc], r1 = S.tile[2*loc+1];
+        const float4 r0 = T[2*loc], r1 = T[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
         float ux = r1.x, uy = r1.y, uz = r1.z;
         if( ii!=fvox ) { f = load_interp( ip, ii ); fvox = ii; }
@@ -154,7 +184,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
           bool stray = false;
           if( k+1<AP_K ) {
             const int nloc = lane*AP_K + ( ( k + 1 + lane ) & ( AP_K-1 ) );
-            stray = nloc<cnt && __float_as_int( S.tile[2*nloc].w )==cur;
+            stray = nloc<cnt && __float_as_int( T[2*nloc].w )==cur;
           }
           if( !stray ) {
             if( cur>=0 ) commit_currents( acc, cur, run );
@@ -163,18 +193,25 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             cur = ii;
           }
         }
-        boris( f, c, dx, dy, dz, ux, uy, uz );
-        const float sux = ux, suy = uy, suz = uz;            // momentum to store
         const float one = 1.0f, one_third = 1.0/3.0;
-        float v0 = one/sqrtf( one + ( ux*ux + ( uy*uy + uz*uz ) ) );
+        float v0, x1, b2;
+        boris_inrange( f, c, dx, dy, dz, ux, uy, uz, x1, b2 );
+        const float x2 = one + ( ux*ux + ( uy*uy + uz*uz ) );
+        v0 = rcp_inrange( sqrt_inrange( x2 ) );
+        if( __builtin_expect( !( x1<=VPB_INRANGE_MAX ) || !( b2<=VPB_INRANGE_MAX ) || !( x2<=VPB_INRANGE_MAX ) || c.guarded, 0 ) ) {
+          ux = r1.x; uy = r1.y; uz = r1.z;                   // out of range (or NaN): the guarded operators
+          boris( f, c, dx, dy, dz, ux, uy, uz );
+          v0 = one/sqrtf( one + ( ux*ux + ( uy*uy + uz*uz ) ) );
+        }
+        const float sux = ux, suy = uy, suz = uz;            // momentum to store
         ux *= c.cdt_dx; uy *= c.cdt_dy; uz *= c.cdt_dz;
         ux *= v0; uy *= v0; uz *= v0;
         v0 = dx + ux; const float v1 = dy + uy, v2 = dz + uz;  // streak midpoint
         const float v3 = v0 + ux, v4 = v1 + uy, v5 = v2 + uz;  // new position
         const float q = r1.w*c.qsp;
-        S.tile[2*loc+1] = make_float4( sux, suy, suz, r1.w );
-        if( v3<=one && v4<=one && v5<=one && -v3<=one && -v4<=one && -v5<=one ) {
-          S.tile[2*loc] = make_float4( v3, v4, v5, r0.w );
+        T[2*loc+1] = make_float4( sux, suy, suz, r1.w );
+        if( fmaxf( fmaxf( fabsf( v3 ), fabsf( v4 ) ), fabsf( v5 ) )<=one ) {   // all six faces at once (move_p otherwise)
+          T[2*loc] = make_float4( v3, v4, v5, r0.w );
           float j[12];
           streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
           if( ii==cur ) {
@@ -201,7 +238,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             __syncwarp();
             n_carry = qn;
           }
-          drain_crossers( S, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
+          drain_crossers( S, T, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
           __syncwarp();
         }
       }
@@ -217,7 +254,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       while( qn>0 ) {
         const int n = qn<32 ? qn : 32;
         qn -= n;
-        drain_crossers( S, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
+        drain_crossers( S, T, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
         __syncwarp();
       }
     }
@@ -227,17 +264,18 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     __syncwarp();
     if( lane==0 ) {
       const uint32_t bytes = (uint32_t)cnt*32u;
-      asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(tile_s), "r"(bytes) : "memory" );
+      asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(smem_u32( T )), "r"(bytes) : "memory" );
       asm volatile( "cp.async.bulk.commit_group;" ::: "memory" );
-      asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer may be reused
+      if( AP_NBUF==1 ) asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer is reused at once
     }
     __syncwarp();
+    if( AP_NBUF>1 ) buf ^= 1;
   }
 
   if( qn>0 ) {                 // all tiles are stored: finish the stragglers in global memory
     if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
     __syncwarp();
-    drain_crossers( S, 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g, c.qsp );
+    drain_crossers( S, S.tile[0], 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g, c.qsp );
   }
   if( cur>=0 ) commit_currents( acc, cur, run );
 }
@@ -319,6 +357,7 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   c.cdt_dy  = hg->cvac*hg->dt*hg->rdy;
   c.cdt_dz  = hg->cvac*hg->dt*hg->rdz;
   c.qsp     = sp->q;
+  { const float a = fabsf( c.qdt_2mc ); c.guarded = ( a>=9.31322574615478515625e-10f && a<=1073741824.0f ) ? 0 : 1; }
   VPB_CUDA( cudaMemsetAsync( ms->d_counters, 0, sizeof(int)*2, r.stream ) );
   const bool streamed = advance_p_streamed( ms, ma, mi, c );
   if( !streamed ) {
