@@ -219,7 +219,12 @@ def run_b200(args):
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": f"uniform Maxwellian e-/ion plasma, periodic {args.cells} cells per GPU, "
-                                  f"2 species x {args.ppc} ppc, sort every {args.sort_interval} steps (BASELINE configs[3])",
+                                  f"2 species x {args.ppc} ppc, sort every {args.sort_interval} steps "
+                                  + ("(BASELINE configs[3])" if args.ppc == 64 else
+                                     f"(BASELINE configs[3]'s box and physics at {args.ppc} ppc instead of 64: at 64 ppc the "
+                                     f"particle arrays are 140 GB and sort_p's out-of-place scratch 69 GB more, over one "
+                                     f"B200's 180 GB; bytes_per_push below is the figure for the ppc that ran)"),
+                      "ppc": args.ppc, "ppc_of_named_config": 64,
                       "particles_per_gpu": np_total, "l2": "inputs (particles, fields) far larger than the 126 MB L2",
                       "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, slab decomposition ({world},1,1): ghost-B / jf face exchange and "
                                                                           f"particle migration over NCCL every step"},
