@@ -129,7 +129,8 @@ class EventTimer:
 
     def total_ms(self):
         self.torch.cuda.synchronize()
-        t = sum(a.elapsed_time(b) for a, b in self.pairs)
+        self.last = [a.elapsed_time(b) for a, b in self.pairs]
+        t = sum(self.last)
         n = len(self.pairs)
         self.pairs = []
         return t, n
@@ -214,7 +215,10 @@ def run_b200(args):
                 "achieved_unit_per_launch_GB": round(bytes_per_push * np_total / 2 / 1e9, 3), "peak_source": peak_src,
                 "bytes_per_push": bytes_per_push, "ms_per_launch": ap_ms / max(ap_calls, 1),
                 "pushes_per_s_kernel_only": np_total * args.steps / (ap_ms * 1e-3),
-                "share_of_step": round(ap_ms / ms, 4)}
+                "share_of_step": round(ap_ms / ms, 4),
+                # advance() walks the species list head first (the species defined last): ion, electron, ion ...
+                "ms_per_launch_by_species": {"ion": sum(tm.last[0::2]) / max(len(tm.last[0::2]), 1),
+                                             "electron": sum(tm.last[1::2]) / max(len(tm.last[1::2]), 1)}}
     out = {"metric": "particle_pushes_per_sec", "value": value, "unit": "pushes/s", "n_gpus": world,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

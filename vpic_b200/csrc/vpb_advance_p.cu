@@ -29,6 +29,7 @@
 // 64 + 176/ppc bytes per push).
 #include "vpb_push.cuh"
 #include <vector>
+#include <cstdlib>
 
 namespace vpb {
 
@@ -136,6 +137,11 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   int n_carry = 0;                             // of which: from tiles whose bulk store may still be in flight
   int cur = -1;                                // voxel whose current sums this lane holds in run[]
   int fvox = -1;                               // voxel whose coefficients this lane holds in f
+  // run[] is never zeroed in a branch (that made the compiler copy all twelve
+  // sums twice per particle): a new run starts with keepf = 0 and its first
+  // deposit is run*0 + j; keepf = 1 afterwards makes the FMA an exact add.
+  // keepf != 0 also says "run[] holds sums that are not committed yet".
+  float keepf = 0.f;
   float run[12];
 # pragma unroll
   for( int k=0; k<12; k++ ) run[k] = 0.f;
@@ -172,6 +178,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
       bool cross = false;
       float cux = 0, cuy = 0, cuz = 0;
+      const int qtag = (int)t0 + loc;
       if( loc<cnt ) {
         const float4 r0 = T[2*loc], r1 = T[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
@@ -187,10 +194,8 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             stray = nloc<cnt && __float_as_int( T[2*nloc].w )==cur;
           }
           if( !stray ) {
-            if( cur>=0 ) commit_currents( acc, cur, run );
-#           pragma unroll
-            for( int m=0; m<12; m++ ) run[m] = 0.f;
-            cur = ii;
+            if( keepf!=0.f ) commit_currents( acc, cur, run );
+            cur = ii; keepf = 0.f;
           }
         }
         const float one = 1.0f, one_third = 1.0/3.0;
@@ -216,7 +221,8 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
           streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
           if( ii==cur ) {
 #           pragma unroll
-            for( int m=0; m<12; m++ ) run[m] += j[m];
+            for( int m=0; m<12; m++ ) run[m] = __fmaf_rn( run[m], keepf, j[m] );
+            keepf = 1.f;
           } else commit_currents( acc, ii, j );
         } else {
           cross = true;
@@ -227,7 +233,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       if( m ) {
         if( cross ) {
           const int e = qn + __popc( m & ( ( 1u<<lane )-1u ) );
-          S.q[e] = make_float4( cux, cuy, cuz, __int_as_float( (int)t0 + loc ) );
+          S.q[e] = make_float4( cux, cuy, cuz, __int_as_float( qtag ) );
         }
         qn += __popc( m );
         __syncwarp();
@@ -277,7 +283,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     __syncwarp();
     drain_crossers( S, S.tile[0], 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g, c.qsp );
   }
-  if( cur>=0 ) commit_currents( acc, cur, run );
+  if( keepf!=0.f ) commit_currents( acc, cur, run );
 }
 
 } // namespace vpb
@@ -292,6 +298,16 @@ int advance_p_blocks_per_sm() {
     VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
     VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, k_advance_p, 32*AP_WARPS, 0 ) );
     if( blocks_per_sm<1 ) VPB_ERROR( "k_advance_p does not fit on an SM" );
+    // Ask for no more shared memory than the resident blocks use (tiles + 1 KB
+    // per block that the driver reserves): what is left of the 256 KB is L1
+    // for the interpolator gathers.  VPIC_B200_AP_CARVEOUT (percent) overrides.
+    int pct = (int)( ( (size_t)blocks_per_sm*( sizeof(WarpTile)*AP_WARPS + 1024 )*100 + 228*1024 - 1 )/( 228*1024 ) );
+    if( const char * e = getenv( "VPIC_B200_AP_CARVEOUT" ) ) pct = atoi( e );
+    if( pct>100 ) pct = 100;
+    VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, pct ) );
+    int check = 0;
+    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &check, k_advance_p, 32*AP_WARPS, 0 ) );
+    if( check<blocks_per_sm ) VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
   }
   return blocks_per_sm;
 }
