@@ -66,16 +66,18 @@ __device__ __forceinline__ uint32_t smem_u32( const void * p ) { return (uint32_
 // Entries of the tile that is still in shared memory are finished there;
 // entries carried over from tiles already written back are finished in global
 // memory (the caller has waited for those bulk stores to complete).
-__device__ __forceinline__ void drain_crossers( WarpTile & S, float4 * __restrict__ T, int base, int n, int lane,
-                                                vpb_particle_t * __restrict__ p, int idx_base, long long t0, int cnt,
+// `on_chip( rel )` returns the particle's slot in shared memory, or nullptr.
+template< class OnChip >
+__device__ __forceinline__ void drain_crossers( const float4 * __restrict__ queue, OnChip on_chip, int base, int n, int lane,
+                                                vpb_particle_t * __restrict__ p, int idx_base,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
                                                 int max_nm, int * __restrict__ counters, const GridDev & g, float qsp ) {
   if( lane>=n ) return;
   const int e = base + lane;
-  const float4 qe = S.q[e];
+  const float4 qe = queue[e];
   const int rel = __float_as_int( qe.w );
-  const bool in_tile = rel>=t0 && rel<t0+cnt;
-  float4 * slot = in_tile ? &T[ 2*(int)( rel-t0 ) ] : reinterpret_cast<float4 *>( p + rel );
+  float4 * slot = on_chip( rel );
+  if( !slot ) slot = reinterpret_cast<float4 *>( p + rel );
   const float4 r0 = slot[0], r1 = slot[1];
   MoveState ms;
   ms.dx = r0.x; ms.dy = r0.y; ms.dz = r0.z; ms.i = __float_as_int( r0.w );
@@ -153,6 +155,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     const int cnt = ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE;
     if( AP_NBUF==1 && lane==0 ) start_load( tile, 0 );
     float4 * __restrict__ T = S.tile[buf];
+    auto on_chip = [&]( int rel ) -> float4 * { return ( rel>=t0 && rel<t0+cnt ) ? &T[ 2*(int)( rel-t0 ) ] : nullptr; };
     {
       const uint32_t bar = smem_u32( &S.bar[buf] );
       uint32_t ok;
@@ -244,7 +247,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             __syncwarp();
             n_carry = qn;
           }
-          drain_crossers( S, T, qn, 32, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
+          drain_crossers( S.q, on_chip, qn, 32, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
           __syncwarp();
         }
       }
@@ -260,7 +263,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       while( qn>0 ) {
         const int n = qn<32 ? qn : 32;
         qn -= n;
-        drain_crossers( S, T, qn, n, lane, p, idx_base, t0, cnt, acc, pm, max_nm, counters, g, c.qsp );
+        drain_crossers( S.q, on_chip, qn, n, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
         __syncwarp();
       }
     }
@@ -281,7 +284,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   if( qn>0 ) {                 // all tiles are stored: finish the stragglers in global memory
     if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
     __syncwarp();
-    drain_crossers( S, S.tile[0], 0, qn, lane, p, idx_base, -1, 0, acc, pm, max_nm, counters, g, c.qsp );
+    drain_crossers( S.q, []( int ) -> float4 * { return nullptr; }, 0, qn, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
   }
   if( keepf!=0.f ) commit_currents( acc, cur, run );
 }
