@@ -231,7 +231,9 @@ def run_b200(args):
                       "ppc": args.ppc, "ppc_of_named_config": 64,
                       "particles_per_gpu": np_total, "l2": "inputs (particles, fields) far larger than the 126 MB L2",
                       "parallelism": "1 GPU" if world == 1 else f"{world} GPUs, slab decomposition ({world},1,1): ghost-B / jf face exchange and "
-                                                                          f"particle migration over NCCL every step"},
+                                                                          f"particle migration every step through "
+                                                                          + ("our put kernels (stores into the neighbours' IPC-mapped mailboxes over NVLink peer memory)"
+                                                                             if world > 1 and L.vpic_b200_comm_transport() else "ncclSend/ncclRecv")},
            "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary(),
            "sort_p": {"ms_per_call": sort_ms / max(sort_calls, 1), "calls": sort_calls, "share_of_step": round(sort_ms / ms, 4),
                       "GB/s": (np_total / 2 * 68.0 / (sort_ms / max(sort_calls, 1) * 1e-3) / 1e9) if sort_calls else None,

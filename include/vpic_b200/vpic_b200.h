@@ -113,6 +113,10 @@ void vpic_b200_set_world( int world_rank, int world_size );
 int  vpic_b200_comm_unique_id( void * out, int nbytes );           /* returns bytes written */
 void vpic_b200_comm_init( const void * id_bytes, int nbytes );
 int  vpic_b200_comm_ready( void );
+/* 1 = face exchanges / particle migration use the put transport (kernels storing
+   into the neighbours' IPC-mapped mailboxes over NVLink), 0 = ncclSend/ncclRecv
+   (VPIC_B200_TRANSPORT=nccl, or the mailbox could not be exported). */
+int  vpic_b200_comm_transport( void );
 void vpic_b200_finalize( void );
 void vpic_b200_set_coherence( int mode );
 void vpic_b200_set_deposit_mode( int mode );

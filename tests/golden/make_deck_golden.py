@@ -9,7 +9,12 @@ against libvpic_b200.so and compares with these digests.
   lpi_small  sample/lpi_2d_F6_test with four numbers reduced (oracle/Makefile:
              32 ppc, 60 steps, status / field dumps every 20 steps)
 
-Usage: python tests/golden/make_deck_golden.py [harris] [lpi_small]"""
+  harris_c3  sample/harris at BASELINE configs[2]'s size (oracle/Makefile: 512x1x256
+             cells, 2 x 100 ppc = 26.2 M particles, 24 steps, dumps every 12)
+  lpi_c5     sample/lpi_2d_F6_test at BASELINE configs[4]'s size (96x1x549 cells,
+             512 ppc per species as shipped), 20 steps, dumps every 10
+
+Usage: python tests/golden/make_deck_golden.py [harris] [lpi_small] [harris_c3] [lpi_c5]"""
 import hashlib
 import json
 import os
@@ -24,6 +29,10 @@ DECKS = {
               "div-clean and shared-face sync every 24 steps)",
     "lpi_small": "sample/lpi_2d_F6_test reduced to 32 ppc / 60 steps (96x1x549 cells, laser field injection, "
                  "absorbing field walls, maxwellian_reflux particle walls, electrons + He ions)",
+    "harris_c3": "sample/harris at BASELINE configs[2]'s size: 512x1x256 cells, 2 species x 100 ppc (26.2 M particles), "
+                 "24 steps, div-clean / shared-face sync / field + hydro dumps every 12 steps",
+    "lpi_c5": "sample/lpi_2d_F6_test at BASELINE configs[4]'s size: 96x1x549 cells, 512 ppc per species as shipped, "
+              "20 steps, field + hydro dumps every 10 steps",
 }
 
 

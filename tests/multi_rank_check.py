@@ -180,6 +180,12 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch):
         box = [bytes(buf)]
         dist.broadcast_object_list(box, src=0)
         L.vpic_b200_comm_init(box[0], 128)
+    want = 0 if os.environ.get("VPIC_B200_TRANSPORT") == "nccl" else 1
+    if L.vpic_b200_comm_transport() != want:
+        print(f"rank {rank}: transport {L.vpic_b200_comm_transport()} instead of {want}")
+        return False
+    if rank == 0:
+        print("transport:", "put (NVLink peer-memory mailboxes)" if want else "ncclSend/ncclRecv")
     L.vpic_b200_set_coherence(0)
     sg, origin, ln = build(b200_backend(), kind, gn, topo, rank, 6, 40)
     for s in (so, sg):

@@ -116,3 +116,22 @@ def test_reference_harris_deck_every_output_file_identical(tmp_path):
     made by make_harris_golden.py)."""
     gold = run_sample_deck(tmp_path, "harris", 480 * 20)
     assert len(gold["files"]) == 106
+
+
+def test_reference_harris_deck_at_config3_size_every_output_file_identical(tmp_path):
+    """BASELINE configs[2] at its named size (oracle/Makefile harris_c3.deck:
+    512 x 1 x 256 cells, 2 species x 100 ppc = 26.2 M particles, PEC +
+    reflecting x walls, 24 steps with div-clean / shared-face sync / field and
+    hydro dumps every 12): energies and all nine dump files equal the CPU
+    reference run's (tests/golden/harris_c3_outputs.json)."""
+    gold = run_sample_deck(tmp_path, "harris_c3", 24 * 20)
+    assert len(gold["files"]) == 10
+
+
+def test_reference_lpi_deck_at_config5_size_every_output_file_identical(tmp_path):
+    """BASELINE configs[4] at its named size (oracle/Makefile lpi_c5.deck: the
+    shipped 96 x 1 x 549 cells and 512 ppc per species, 2 x 27.0 M particles,
+    laser injection, absorbing field walls, maxwellian_reflux particle walls),
+    20 steps, dumps every 10."""
+    gold = run_sample_deck(tmp_path, "lpi_c5", 20 * 20)
+    assert len(gold["files"]) >= 7

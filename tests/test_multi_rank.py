@@ -15,11 +15,11 @@ def free_port():
     return p
 
 
-def launch(mode, nproc=2, timeout=900):
+def launch(mode, nproc=2, timeout=900, **env):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
            "--master-addr", "127.0.0.1", "--master-port", str(free_port()),
            os.path.join(ROOT, "tests", "multi_rank_check.py"), "--mode", mode]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=dict(os.environ, **env))
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "PASS" in r.stdout
 
@@ -29,8 +29,12 @@ def test_two_rank_oracle_matches_one_rank_oracle_gloo():
 
 
 @pytest.mark.gpu
-def test_two_gpus_match_two_rank_oracle_nccl():
+@pytest.mark.parametrize("transport", ["put", "nccl"])
+def test_two_gpus_match_two_rank_oracle(transport):
+    """put: ghost planes, current folds and migrating particles are stored by our
+    kernels into the neighbour's IPC-mapped mailbox over NVLink; nccl: the same
+    exchanges through ncclSend/ncclRecv.  Same bit-exact checks either way."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    launch("gpu")
+    launch("gpu", VPIC_B200_TRANSPORT=transport)

@@ -6,14 +6,33 @@
 //
 // The domain decomposition is the reference's brick-per-rank with six face
 // neighbours (src/grid/partition.c:25-80); every exchange is a pair of
-// messages along one axis, so the whole transport is ncclSend/ncclRecv inside
-// one group on the compute stream (device buffers in, device buffers out, no
-// host staging).  NCCL is bound at run time (dlopen) so the library loads on
-// machines without it; a rank with a remote neighbour and no communicator
-// fails loudly.
+// messages along one axis.  NCCL is bound at run time (dlopen) so the library
+// loads on machines without it; a rank with a remote neighbour and no
+// communicator fails loudly.
+//
+// Data path ("put" transport, the default when every rank's mailbox can be
+// mapped): the messages of the step are sub-MB and latency-bound, so they do
+// not go through ncclSend/ncclRecv.  Every rank owns a MAILBOX in device
+// memory, exported with cudaIpc and mapped by its neighbours over NVLink peer
+// memory: slot (source rank, direction, parity).  One kernel stores the
+// outgoing messages straight into the neighbours' mailboxes (128-bit stores
+// over NVLink), fences, and the last block publishes the message's sequence
+// number in the mailbox's flag word (st.release.sys); one kernel on the
+// receiving rank acquires the flag and copies the payload out.  No host
+// round-trip, no proxy thread, two launches per exchange.  Every exchange is
+// bidirectional per neighbour pair (zero-byte messages still publish their
+// flag), which is what makes two parity slots enough: a rank cannot send
+// message k+2 before it has received k+1, which its neighbour sent after
+// consuming k.  NCCL remains for the bootstrap (all-gather of the IPC
+// handles), the energy all-reduce and messages larger than a mailbox slot.
+// VPIC_B200_TRANSPORT=nccl selects the ncclSend/ncclRecv path for A/B runs.
 #include "vpb_runtime.h"
 #include <dlfcn.h>
+#include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <vector>
+#include <algorithm>
 
 namespace vpb {
 
@@ -34,6 +53,7 @@ struct Nccl {
   int  (*Send)( const void *, size_t, int, int, ncclComm_t, cudaStream_t ) = nullptr;
   int  (*Recv)( void *, size_t, int, int, ncclComm_t, cudaStream_t ) = nullptr;
   int  (*AllReduce)( const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t ) = nullptr;
+  int  (*AllGather)( const void *, void *, size_t, int, ncclComm_t, cudaStream_t ) = nullptr;
   int  (*GroupStart)() = nullptr;
   int  (*GroupEnd)() = nullptr;
   const char * (*GetErrorString)( int ) = nullptr;
@@ -51,7 +71,7 @@ void load_nccl() {
   if( !N.lib ) VPB_ERROR( "multi-GPU run requested but libnccl.so.2 cannot be loaded: %s", dlerror() );
 # define SYM( field, name ) *(void **)( &N.field ) = dlsym( N.lib, name ); if( !N.field ) VPB_ERROR( "libnccl has no %s", name )
   SYM( GetUniqueId, "ncclGetUniqueId" ); SYM( CommInitRank, "ncclCommInitRank" ); SYM( CommDestroy, "ncclCommDestroy" );
-  SYM( Send, "ncclSend" ); SYM( Recv, "ncclRecv" ); SYM( AllReduce, "ncclAllReduce" );
+  SYM( Send, "ncclSend" ); SYM( Recv, "ncclRecv" ); SYM( AllReduce, "ncclAllReduce" ); SYM( AllGather, "ncclAllGather" );
   SYM( GroupStart, "ncclGroupStart" ); SYM( GroupEnd, "ncclGroupEnd" ); SYM( GetErrorString, "ncclGetErrorString" );
 # undef SYM
 }
@@ -62,6 +82,152 @@ void load_nccl() {
 void need_comm( const char * what ) {
   if( !N.comm ) VPB_ERROR( "%s needs a remote rank (world_size=%d) but no multi-GPU transport is initialised: "
                            "call vpic_b200_comm_init on every rank first", what, g_world_size );
+}
+
+// ---- put transport over NVLink peer memory -------------------------------------
+constexpr size_t MB_SLOT  = 8u<<20;            // payload bytes per mailbox slot
+constexpr int    MB_FLAGW = 32;                // one 128 B line per flag
+
+struct Mailbox {
+  bool     on = false, tried = false;
+  char *   mine = nullptr;                     // this rank's mailbox (cudaMalloc, IPC-exported)
+  std::vector<char *> peer;                    // mapped mailboxes of the other ranks (nullptr until first use)
+  std::vector<cudaIpcMemHandle_t> handle;
+  std::vector<unsigned> sent, rcvd;            // per (rank, direction): messages put to / taken from that slot pair
+  unsigned * d_done = nullptr;                 // block counters of the put kernel (2)
+  int *    d_err = nullptr;                    // set by a receive that timed out
+  size_t   bytes = 0;
+} MB;
+
+// mailbox layout of one rank: [world][2 directions][2 parities] payload slots, then the flags
+__host__ __device__ inline size_t mb_slot_off( int src, int dir, int par ) { return ( ( (size_t)src*2 + dir )*2 + par )*MB_SLOT; }
+inline size_t mb_flag_off( int world, int src, int dir, int par ) {
+  return (size_t)world*4*MB_SLOT + ( ( (size_t)src*2 + dir )*2 + par )*MB_FLAGW*sizeof(unsigned);
+}
+
+struct PutMsg { const char * src; char * dst; unsigned * flag; unsigned nbytes, seq; };
+
+// blockIdx.y picks the message.  Payload first, then a system-scope fence per
+// thread; the last block to finish publishes the sequence number.
+__global__ void k_put( PutMsg m0, PutMsg m1, unsigned * __restrict__ done ) {
+  const PutMsg m = blockIdx.y ? m1 : m0;
+  if( !m.flag ) return;
+  const unsigned n16 = m.nbytes>>4;
+  if( ( ( (size_t)m.src | (size_t)m.dst ) & 15 )==0 ) {
+    const uint4 * s = reinterpret_cast<const uint4 *>( m.src ); uint4 * d = reinterpret_cast<uint4 *>( m.dst );
+    for( unsigned i=blockIdx.x*blockDim.x+threadIdx.x; i<n16; i+=gridDim.x*blockDim.x ) d[i] = s[i];
+    for( unsigned i=( n16<<4 )+blockIdx.x*blockDim.x+threadIdx.x; i<m.nbytes; i+=gridDim.x*blockDim.x ) m.dst[i] = m.src[i];
+  } else
+    for( unsigned i=blockIdx.x*blockDim.x+threadIdx.x; i<m.nbytes; i+=gridDim.x*blockDim.x ) m.dst[i] = m.src[i];
+  __threadfence_system();
+  __syncthreads();
+  if( threadIdx.x==0 ) {
+    if( atomicAdd( done+blockIdx.y, 1u )==gridDim.x-1 ) {
+      done[blockIdx.y] = 0;
+      asm volatile( "st.release.sys.global.u32 [%0], %1;" :: "l"(m.flag), "r"(m.seq) : "memory" );
+    }
+  }
+}
+
+struct GetMsg { char * dst; const char * src; const unsigned * flag; unsigned nbytes, seq; };
+
+__global__ void k_get( GetMsg m0, GetMsg m1, int * __restrict__ err ) {
+  const GetMsg m = blockIdx.y ? m1 : m0;
+  if( !m.flag ) return;
+  if( threadIdx.x==0 ) {
+    unsigned v; const long long t0 = clock64();
+    do {
+      asm volatile( "ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(m.flag) : "memory" );
+      if( (int)( v-m.seq )>=0 ) break;
+      if( clock64()-t0>60000000000ll ) {                                        // ~30 s: the neighbour is gone
+        printf( "[vpic_b200] put transport: message %u never arrived (flag %u)\n", m.seq, v );
+        atomicExch( err, 1 ); __trap();
+      }
+      __nanosleep( 64 );
+    } while( true );
+  }
+  __syncthreads();
+  const unsigned n16 = m.nbytes>>4;
+  if( ( ( (size_t)m.src | (size_t)m.dst ) & 15 )==0 ) {
+    const uint4 * s = reinterpret_cast<const uint4 *>( m.src ); uint4 * d = reinterpret_cast<uint4 *>( m.dst );
+    for( unsigned i=blockIdx.x*blockDim.x+threadIdx.x; i<n16; i+=gridDim.x*blockDim.x ) d[i] = s[i];
+    for( unsigned i=( n16<<4 )+blockIdx.x*blockDim.x+threadIdx.x; i<m.nbytes; i+=gridDim.x*blockDim.x ) m.dst[i] = m.src[i];
+  } else
+    for( unsigned i=blockIdx.x*blockDim.x+threadIdx.x; i<m.nbytes; i+=gridDim.x*blockDim.x ) m.dst[i] = m.src[i];
+}
+
+// Allocate and export this rank's mailbox, gather every rank's handle.  Collective.
+void mailbox_setup() {
+  if( MB.tried ) return;
+  MB.tried = true;
+  if( const char * e = getenv( "VPIC_B200_TRANSPORT" ) ) if( !strcmp( e, "nccl" ) ) return;
+  Runtime & r = rt();
+  const int W = g_world_size;
+  MB.bytes = (size_t)W*4*MB_SLOT + (size_t)W*4*MB_FLAGW*sizeof(unsigned);
+  VPB_CUDA( cudaMalloc( &MB.mine, MB.bytes ) );
+  VPB_CUDA( cudaMemset( MB.mine + (size_t)W*4*MB_SLOT, 0, (size_t)W*4*MB_FLAGW*sizeof(unsigned) ) );
+  VPB_CUDA( cudaMalloc( &MB.d_done, sizeof(unsigned)*2 ) ); VPB_CUDA( cudaMemset( MB.d_done, 0, sizeof(unsigned)*2 ) );
+  VPB_CUDA( cudaMalloc( &MB.d_err, sizeof(int) ) );         VPB_CUDA( cudaMemset( MB.d_err, 0, sizeof(int) ) );
+  cudaIpcMemHandle_t h; memset( &h, 0, sizeof(h) );
+  int ok = cudaIpcGetMemHandle( &h, MB.mine )==cudaSuccess ? 1 : 0;
+  if( !ok ) cudaGetLastError();
+  // all-gather { ok, handle } through NCCL (device buffers)
+  const size_t rec = 16 + sizeof(h);
+  std::vector<char> host( rec*W, 0 );
+  memcpy( &host[rec*g_world_rank], &ok, sizeof(int) ); memcpy( &host[rec*g_world_rank+16], &h, sizeof(h) );
+  char * d_all = nullptr;
+  VPB_CUDA( cudaMalloc( &d_all, rec*W ) );
+  VPB_CUDA( cudaMemcpyAsync( d_all, host.data(), rec*W, cudaMemcpyHostToDevice, r.stream ) );
+  VPB_NCCL( N.AllGather( d_all + rec*g_world_rank, d_all, rec, ncclChar, N.comm, r.stream ) );
+  VPB_CUDA( cudaMemcpyAsync( host.data(), d_all, rec*W, cudaMemcpyDeviceToHost, r.stream ) );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  VPB_CUDA( cudaFree( d_all ) );
+  MB.handle.resize( W ); MB.peer.assign( W, nullptr ); MB.sent.assign( 2*W, 0 ); MB.rcvd.assign( 2*W, 0 );
+  bool all = true;
+  for( int k=0; k<W; k++ ) { int f; memcpy( &f, &host[rec*k], sizeof(int) ); all = all && f; memcpy( &MB.handle[k], &host[rec*k+16], sizeof(h) ); }
+  MB.on = all;                                 // every rank reaches the same verdict
+  if( !all && g_world_rank==0 ) VPB_WARNING( "cudaIpc export of the mailbox failed on some rank: face exchanges use ncclSend/ncclRecv" );
+}
+
+char * mailbox_of( int rank ) {
+  if( rank==g_world_rank ) return MB.mine;
+  if( !MB.peer[rank] ) {
+    void * q = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle( &q, MB.handle[rank], cudaIpcMemLazyEnablePeerAccess );
+    if( e!=cudaSuccess ) VPB_ERROR( "cannot map the mailbox of rank %d over NVLink peer memory (%s); set VPIC_B200_TRANSPORT=nccl", rank, cudaGetErrorString( e ) );
+    MB.peer[rank] = (char *)q;
+  }
+  return MB.peer[rank];
+}
+
+bool put_sendrecv( int rank_lo, int rank_hi, const void * slo, size_t nslo, const void * shi, size_t nshi,
+                   void * rlo, size_t nrlo, void * rhi, size_t nrhi ) {
+  if( !MB.on ) return false;
+  if( nslo>MB_SLOT || nshi>MB_SLOT || nrlo>MB_SLOT || nrhi>MB_SLOT ) return false;   // both ends see the same sizes
+  Runtime & r = rt();
+  const int W = g_world_size, me = g_world_rank;
+  PutMsg p[2] = {}; GetMsg q[2] = {};
+  // my "lo" message lands in rank_lo's slot (me, direction 0); my "hi" message in rank_hi's slot (me, 1)
+  const int to[2] = { rank_lo, rank_hi }; const void * sb[2] = { slo, shi }; const size_t sn[2] = { nslo, nshi };
+  for( int d=0; d<2; d++ ) if( to[d]>=0 ) {
+    const unsigned k = MB.sent[2*to[d]+d]++;
+    char * box = mailbox_of( to[d] );
+    p[d].src = (const char *)sb[d]; p[d].dst = box + mb_slot_off( me, d, k&1 ); p[d].nbytes = (unsigned)sn[d]; p[d].seq = k+1;
+    p[d].flag = reinterpret_cast<unsigned *>( box + mb_flag_off( W, me, d, k&1 ) );
+  }
+  // what arrives from rank_lo was its "hi" message (direction 1); from rank_hi its "lo" message (direction 0)
+  const int from[2] = { rank_lo, rank_hi }; void * rb[2] = { rlo, rhi }; const size_t rn[2] = { nrlo, nrhi };
+  for( int d=0; d<2; d++ ) if( from[d]>=0 ) {
+    const int dir = 1-d;
+    const unsigned k = MB.rcvd[2*from[d]+dir]++;
+    q[d].dst = (char *)rb[d]; q[d].src = MB.mine + mb_slot_off( from[d], dir, k&1 ); q[d].nbytes = (unsigned)rn[d]; q[d].seq = k+1;
+    q[d].flag = reinterpret_cast<const unsigned *>( MB.mine + mb_flag_off( W, from[d], dir, k&1 ) );
+  }
+  const size_t big = std::max( std::max( nslo, nshi ), std::max( nrlo, nrhi ) );
+  const int nb = (int)std::min<size_t>( 64, std::max<size_t>( 1, big/( 256*16*4 ) ) );
+  if( p[0].flag || p[1].flag ) { k_put<<< dim3( nb, 2 ), 256, 0, r.stream >>>( p[0], p[1], MB.d_done ); VPB_CHECK_LAUNCH(); r.launches++; }
+  if( q[0].flag || q[1].flag ) { k_get<<< dim3( nb, 2 ), 256, 0, r.stream >>>( q[0], q[1], MB.d_err ); VPB_CHECK_LAUNCH(); r.launches++; }
+  return true;
 }
 
 } // namespace
@@ -75,6 +241,7 @@ void comm_sendrecv( int rank_lo, int rank_hi,
                     void * rlo, size_t nrlo, void * rhi, size_t nrhi ) {
   need_comm( "a face exchange" );
   Runtime & r = rt();
+  if( put_sendrecv( rank_lo, rank_hi, slo, nslo, shi, nshi, rlo, nrlo, rhi, nrhi ) ) return;
   VPB_NCCL( N.GroupStart() );
   if( rank_lo>=0 && nslo ) VPB_NCCL( N.Send( slo, nslo, ncclChar, rank_lo, N.comm, r.stream ) );
   if( rank_hi>=0 && nshi ) VPB_NCCL( N.Send( shi, nshi, ncclChar, rank_hi, N.comm, r.stream ) );
@@ -108,6 +275,11 @@ bool comm_ready() { return N.comm!=nullptr; }
 void comm_shutdown() {
   if( N.comm ) { N.CommDestroy( N.comm ); N.comm = nullptr; }
   if( N.d_red ) { cudaFree( N.d_red ); N.d_red = nullptr; }
+  for( char * q : MB.peer ) if( q ) cudaIpcCloseMemHandle( q );
+  if( MB.mine ) cudaFree( MB.mine );
+  if( MB.d_done ) cudaFree( MB.d_done );
+  if( MB.d_err ) cudaFree( MB.d_err );
+  MB = Mailbox();
 }
 
 } // namespace vpb
@@ -133,7 +305,12 @@ void vpic_b200_comm_init( const void * id_bytes, int nbytes ) {
   if( N.comm ) return;
   ncclUniqueId id; memcpy( &id, id_bytes, sizeof(id) );
   VPB_NCCL( N.CommInitRank( &N.comm, g_world_size, id, g_world_rank ) );
+  mailbox_setup();
 }
+
+// 1 = face exchanges and particle migration go through the put transport
+// (NVLink peer-memory mailboxes), 0 = through ncclSend/ncclRecv.
+int vpic_b200_comm_transport( void ) { return MB.on ? 1 : 0; }
 
 int vpic_b200_comm_ready( void ) { return comm_ready() ? 1 : 0; }
 
