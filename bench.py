@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-yee", action="store_true")
+    ap.add_argument("--breakdown", type=int, default=0, metavar="STEPS",
+                    help="after the timed region: STEPS more steps with a device synchronize around every entry point, "
+                         "reported as breakdown_ms (per step, this rank)")
     return ap.parse_args()
 
 
@@ -238,6 +241,8 @@ def run_b200(args):
            "sort_p": {"ms_per_call": sort_ms / max(sort_calls, 1), "calls": sort_calls, "share_of_step": round(sort_ms / ms, 4),
                       "GB/s": (np_total / 2 * 68.0 / (sort_ms / max(sort_calls, 1) * 1e-3) / 1e9) if sort_calls else None,
                       "bytes_per_particle": 68.0}}
+    if args.breakdown:
+        out["breakdown_ms"] = breakdown(torch, sim, be, args.breakdown)
     free_sim(L, sim)
 
     if rank == 0 and not args.no_yee:      # single-GPU sub-benchmark: a 1x1x1 topology for the duration
@@ -258,6 +263,30 @@ def run_b200(args):
         print(json.dumps(out))
     if dist is not None:
         dist.barrier(); dist.destroy_process_group()
+
+
+def breakdown(torch, sim, be, steps):
+    """Wall time per entry point with the device drained before and after each call."""
+    names = ["sort_p", "clear_accumulator_array", "advance_p", "reduce_accumulator_array", "boundary_p", "clear_jf",
+             "unload_accumulator_array", "synchronize_jf", "advance_b", "advance_e", "load_interpolator_array"]
+    acc, raw = {n: 0.0 for n in names}, {n: getattr(be, n) for n in names}
+
+    def wrap(n):
+        def f(*a):
+            torch.cuda.synchronize(); t = time.perf_counter()
+            r = raw[n](*a)
+            torch.cuda.synchronize(); acc[n] += time.perf_counter() - t
+            return r
+        return f
+    for n in names:
+        setattr(be, n, wrap(n))
+    try:
+        for _ in range(steps):
+            sim.advance()
+    finally:
+        for n in names:
+            setattr(be, n, raw[n])
+    return {n: round(v / steps * 1e3, 4) for n, v in acc.items()}
 
 
 def free_sim(L, sim):

@@ -280,6 +280,123 @@ k_bnd_inject( BndInject a, float * __restrict__ acc, GridDev g ) {
   if( threadIdx.x<BND_MAX_SP ) a.counters[threadIdx.x] = s_base[threadIdx.x];
 }
 
+// ---- multi-block versions (FAST deposit) ------------------------------------------
+// The single-block kernels above walk the movers 1024 at a time, one chunk after
+// the other; at config 4's face sizes (10^5 movers per species and step) that
+// serial walk was the largest part of boundary_p.  Here every chunk of BND_T
+// movers is a block of its own: the block ranks its movers per key, then takes
+// the running per-key totals from the chunk before it and publishes its own
+// (a chained scan: chunk numbers are handed out by an atomic ticket, so the
+// chunk a block waits for has always started).  Slots are the same as the
+// single-block kernel's, so message and array order stay bit-exact.
+struct ChainScan {
+  int * ticket;          // [1]
+  int * flag;            // [nchunk]  1 = prefix[c] is published
+  int * prefix;          // [nchunk][16] inclusive per-key totals
+};
+
+template<int NKEY>
+__device__ __forceinline__ void chain_bases( const ChainScan & cs, int chunk, int nchunk, const int * s_tot, int * s_base,
+                                             const int * first_base, int * last_out ) {
+  if( threadIdx.x<NKEY ) {
+    int base;
+    if( chunk==0 ) base = first_base ? first_base[threadIdx.x] : 0;
+    else {
+      const volatile int * fl = cs.flag + ( chunk-1 );
+      while( *fl==0 ) __nanosleep( 20 );
+      __threadfence();
+      base = reinterpret_cast<const volatile int *>( cs.prefix )[ 16*(size_t)( chunk-1 ) + threadIdx.x ];
+    }
+    s_base[threadIdx.x] = base;
+    const int incl = base + s_tot[threadIdx.x];
+    cs.prefix[ 16*(size_t)chunk + threadIdx.x ] = incl;
+    if( chunk==nchunk-1 && last_out ) last_out[threadIdx.x] = incl;
+    __threadfence();
+  }
+  __syncthreads();
+  if( threadIdx.x==0 ) { __threadfence(); reinterpret_cast<volatile int *>( cs.flag )[chunk] = 1; }
+}
+
+__global__ void __launch_bounds__(BND_T)
+k_bnd_classify_mb( const vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int nm,
+                   int sp_id, float q_r8V, float * __restrict__ rhob, GridDev g, BndFaces a, int * __restrict__ n_unknown,
+                   ChainScan cs, int nchunk ) {
+  __shared__ int s_w[BND_T/32][7];
+  __shared__ int s_tot[7], s_base[7], s_chunk;
+  if( threadIdx.x==0 ) s_chunk = atomicAdd( cs.ticket, 1 );
+  __syncthreads();
+  const int chunk = s_chunk;
+  const int r = chunk*BND_T + threadIdx.x;       // position in processing order
+  int key = -1, face = 0, voxel = 0, i = 0, code = 0;
+  float4 r0 = {}, r1 = {}, d = {};
+  if( r<nm ) {
+    d = reinterpret_cast<const float4 *>( pm )[ nm-1-r ];
+    i = __float_as_int( d.w );
+    r0 = reinterpret_cast<const float4 *>( p + i )[0];
+    r1 = reinterpret_cast<const float4 *>( p + i )[1];
+    const int vi = __float_as_int( r0.w );
+    face = vi & 7; voxel = vi >> 3;
+    int kind = -1;
+    if( face<6 ) {
+      if( g.neighbor ) {
+        code = g.neighbor[ 6*(size_t)voxel + face ];
+        kind = code==NB_ABSORB ? PK_ABSORB : code==NB_REMOTE ? PK_REMOTE : ( code<=-3 && code>NB_UNKNOWN ) ? PK_CUSTOM : -1;
+      } else { kind = a.kind[face]; code = a.code[face]; }
+    }
+    if( kind==PK_ABSORB ) accumulate_rhob_dev( rhob, g, r0.x, r0.y, r0.z, voxel, r1.w, q_r8V );
+    else if( kind==PK_REMOTE ) key = face;
+    else if( kind==PK_CUSTOM && a.custom && code>=-34 && ( ( a.handler_mask >> ( -code-3 ) ) & 1u ) ) key = 6;
+    else atomicAdd( n_unknown, 1 );
+  }
+  const int rank = block_rank_by_key<7>( key, s_w, s_tot );
+  chain_bases<7>( cs, chunk, nchunk, s_tot, s_base, a.face_count, a.face_count );
+  if( key==6 ) {
+    float4 * out = a.custom + 4*(size_t)( s_base[6] + rank );
+    out[0] = make_float4( r0.x, r0.y, r0.z, __int_as_float( voxel ) );
+    out[1] = r1;
+    out[2] = d;
+    out[3] = make_float4( __int_as_float( face ), __int_as_float( sp_id ), __int_as_float( code ), 0.f );
+  } else if( key>=0 ) {
+    const int axis = face>=3 ? face-3 : face;
+    int c[3] = { voxel % g.sy, ( voxel / g.sy ) % ( g.ny+2 ), voxel / g.sz };
+    int rn[3] = { g.nx, g.ny, g.nz };
+    rn[axis] = a.nb_n[face];
+    c[axis] = face<3 ? rn[axis] : 1;
+    const int nv_i = c[0] + ( rn[0]+2 )*( c[1] + ( rn[1]+2 )*c[2] );
+    float pos[3] = { r0.x, r0.y, r0.z };
+    pos[axis] = face<3 ? 1.f : -1.f;
+    float4 * out = reinterpret_cast<float4 *>( a.send[face] + s_base[face] + rank );
+    out[0] = make_float4( pos[0], pos[1], pos[2], __int_as_float( nv_i ) );
+    out[1] = r1;
+    out[2] = make_float4( d.x, d.y, d.z, __int_as_float( sp_id ) );
+  }
+}
+
+__global__ void __launch_bounds__(BND_T)
+k_bnd_inject_mb( BndInject a, float * __restrict__ acc, GridDev g, ChainScan cs, int nchunk ) {
+  __shared__ int s_w[BND_T/32][BND_MAX_SP];
+  __shared__ int s_tot[BND_MAX_SP], s_base[BND_MAX_SP], s_chunk;
+  if( threadIdx.x==0 ) s_chunk = atomicAdd( cs.ticket, 1 );
+  __syncthreads();
+  const int chunk = s_chunk;
+  const int total = a.start[7];
+  const int r = chunk*BND_T + threadIdx.x;
+  int key = -1; float4 i0 = {}, i1 = {}, i2 = {};
+  if( r<total ) {
+    int face = 0;
+    while( r>=a.start[face+1] ) face++;
+    const int n = a.start[face+1] - a.start[face];
+    const float4 * src = reinterpret_cast<const float4 *>( a.recv[face] + ( n-1-( r-a.start[face] ) ) );
+    i0 = src[0]; i1 = src[1]; i2 = src[2];
+    key = __float_as_int( i2.w );
+    if( key<0 || key>=BND_MAX_SP || !a.p[key] ) key = -1;
+  }
+  const int rank = block_rank_by_key<BND_MAX_SP>( key, s_w, s_tot );
+  chain_bases<BND_MAX_SP>( cs, chunk, nchunk, s_tot, s_base, nullptr, a.counters );
+  if( key>=0 ) inject_one( a, acc, g, i0, i1, i2, key, a.np[key] + s_base[key] + rank );
+  else if( r<total ) atomicAdd( a.counters + 3*BND_MAX_SP, 1 );
+}
+
 // STRICT coherence, sparse transfers: rows of the particle array named by an
 // index list, device <-> a compact staging buffer.
 __global__ void __launch_bounds__(256)
@@ -314,7 +431,23 @@ struct BndBuffers {
   vpb_particle_injector_t * ci = nullptr; size_t ci_cap = 0;
   // sparse STRICT transfers: page-locked host staging and its device twin (rows, then indices)
   char * h_rows = nullptr, * d_rows = nullptr; size_t rows_cap = 0;
+  // chained scan of the multi-block kernels: ticket, flags, per-chunk prefixes
+  int * d_chain = nullptr; size_t chain_cap = 0;
 } B;
+
+// Zeroed scratch for a chained scan over nchunk chunks (on the compute stream).
+ChainScan chain_scan( int nchunk ) {
+  Runtime & r = rt();
+  if( (size_t)nchunk>B.chain_cap ) {
+    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+    if( B.d_chain ) VPB_CUDA( cudaFree( B.d_chain ) );
+    B.chain_cap = (size_t)nchunk*2 + 64;
+    VPB_CUDA( cudaMalloc( &B.d_chain, sizeof(int)*( 32 + 17*B.chain_cap ) ) );
+  }
+  VPB_CUDA( cudaMemsetAsync( B.d_chain, 0, sizeof(int)*( 32 + (size_t)nchunk ), r.stream ) );     // ticket + flags
+  ChainScan cs; cs.ticket = B.d_chain; cs.flag = B.d_chain + 32; cs.prefix = B.d_chain + 32 + B.chain_cap;
+  return cs;
+}
 
 void grow( vpb_particle_injector_t ** buf, size_t * cap, size_t want ) {
   if( want<=*cap ) return;
@@ -379,6 +512,7 @@ void release_boundary_buffers() {
   cudaFree( B.d_int ); B.d_int = nullptr;
   cudaFree( B.custom ); cudaFree( B.ci ); B.custom = nullptr; B.ci = nullptr; B.custom_cap = B.ci_cap = 0;
   cudaFree( B.d_rows ); if( B.h_rows ) cudaFreeHost( B.h_rows ); B.d_rows = B.h_rows = nullptr; B.rows_cap = 0;
+  cudaFree( B.d_chain ); B.d_chain = nullptr; B.chain_cap = 0;
 }
 }
 
@@ -583,8 +717,14 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     if( !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     const vpb_species_t * sp = m->host;
     const float q_r8V = sp->q*sp->g->r8V;
-    k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16,
-                                                  r.deposit_mode==VPB_DEPOSIT_PARITY );
+    if( r.deposit_mode==VPB_DEPOSIT_PARITY || m->nm<=BND_T )
+      k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16,
+                                                    r.deposit_mode==VPB_DEPOSIT_PARITY );
+    else {
+      const int nchunk = div_up( m->nm, BND_T );
+      k_bnd_classify_mb<<< nchunk, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16,
+                                                            chain_scan( nchunk ), nchunk );
+    }
     k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
     VPB_CHECK_LAUNCH(); r.launches += 2;
     if( any_absorb ) touched_rhob = true;
@@ -668,7 +808,11 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     }
     bi.counters = B.d_int + 32;
     if( r.deposit_mode==VPB_DEPOSIT_PARITY ) k_bnd_inject_serial<<< 1, 32, 0, r.stream >>>( bi, ma->d, g );
-    else k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
+    else if( max_inj<=BND_T ) k_bnd_inject<<< 1, BND_T, 0, r.stream >>>( bi, ma->d, g );
+    else {
+      const int nchunk = div_up( max_inj, BND_T );
+      k_bnd_inject_mb<<< nchunk, BND_T, 0, r.stream >>>( bi, ma->d, g, chain_scan( nchunk ), nchunk );
+    }
     VPB_CHECK_LAUNCH(); r.launches++;
     int h_cnt[4*BND_MAX_SP+1];
     d2h( h_cnt, B.d_int+32, sizeof(h_cnt), r.stream );
