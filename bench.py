@@ -38,7 +38,8 @@ def parse_args():
     ap.add_argument("--ppc", type=int, default=32, help="particles per cell per species")
     ap.add_argument("--sort-interval", default="8", help="steps between sorts: one value, or electron,ion (species_t::sort_interval is per species)")
     ap.add_argument("--e2e-cells", default="256x128x128")
-    ap.add_argument("--cpu-cells", default="64x64x32")
+    ap.add_argument("--cpu-cells", default="128x128x64", help="box of the bounded CPU sample (same physics and ppc)")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="cpu_baseline leg: keep stepping the sample for about this long")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-yee", action="store_true")
@@ -377,8 +378,10 @@ def host_simd_ok():
         return False
 
 
-def reference_run(args, steps, warmup):
-    """The reference's own CPU implementation of the step on the host cores."""
+def reference_run(args, steps, warmup, seconds=None):
+    """The reference's own CPU implementation of the step on the host cores.
+    seconds: keep stepping (at least `steps` steps) until about that much CPU
+    time has been spent in the timed region."""
     import numpy as np
     from oracle import harness as H
     cores = len(os.sched_getaffinity(0))
@@ -420,17 +423,19 @@ def reference_run(args, steps, warmup):
         sim.advance()
     t_ap[0] = 0.0
     t0 = time.perf_counter()
-    for _ in range(steps):
-        sim.advance()
+    done = 0
+    while done < steps or (seconds and time.perf_counter() - t0 < seconds and done < 2000):
+        sim.advance(); done += 1
+    steps = done
     dt = time.perf_counter() - t0
     return {"value": np_total * steps / dt, "unit": "pushes/s", "cores": tpp, "kind": kind,
             "sample": f"{build}, --tpp {tpp}, {args.cpu_cells} cells x 2 species x {args.ppc} ppc "
-                      f"({np_total} particles), {steps} full steps",
+                      f"({np_total} particles), {steps} full steps = {dt:.1f} s of wall time on {tpp} threads",
             "advance_p_only_pushes_per_s": np_total * steps / max(t_ap[0], 1e-9), "ms_per_step": dt / steps * 1e3}
 
 
 def cpu_baseline(args):
-    return reference_run(args, steps=3, warmup=1)
+    return reference_run(args, steps=3, warmup=1, seconds=args.cpu_seconds)
 
 
 def run_reference(args):
