@@ -139,7 +139,7 @@ __global__ void k_get( GetMsg m0, GetMsg m1, int * __restrict__ err ) {
     do {
       asm volatile( "ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(m.flag) : "memory" );
       if( (int)( v-m.seq )>=0 ) break;
-      if( clock64()-t0>60000000000ll ) {                                        // ~30 s: the neighbour is gone
+      if( clock64()-t0>1200000000000ll ) {                                      // ~10 min: the neighbour is gone
         printf( "[vpic_b200] put transport: message %u never arrived (flag %u)\n", m.seq, v );
         atomicExch( err, 1 ); __trap();
       }
