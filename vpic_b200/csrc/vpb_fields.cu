@@ -218,8 +218,7 @@ struct PlaneArgs {
   float * buf;           // packed face buffer
 };
 
-__global__ void __launch_bounds__(128)
-k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
+__device__ __forceinline__ void plane_op_item( float * __restrict__ f, const GridDev & g, const PlaneArgs & a, const int t ) {
   const int n3[3] = { g.nx, g.ny, g.nz };
   const int s3[3] = { 1, g.sy, g.sz };
   const int X = a.X, Y = (X+1)%3, Z = (X+2)%3;
@@ -230,7 +229,6 @@ k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
   if( a.op==OP_NORM_B_ZERO ) { uA = nY; nA = nY*nZ; uB = 1; nB = 0; }
   else if( bkind ) { uA = nY+1; nA = (nY+1)*nZ; uB = nY;   nB = nY*(nZ+1); }
   else             { uA = nY;   nA = nY*(nZ+1); uB = nY+1; nB = (nY+1)*nZ; }
-  const int t = blockIdx.x*blockDim.x + threadIdx.x;
   if( t>=nA+nB ) return;
   const bool isA = t<nA;
   const int k = isA ? t : t-nA;
@@ -283,6 +281,22 @@ k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
   }
 }
 
+__global__ void __launch_bounds__(128)
+k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
+  plane_op_item( f, g, a, blockIdx.x*blockDim.x + threadIdx.x );
+}
+
+// Several INDEPENDENT plane operations in one launch (blockIdx.y picks the
+// operation): the planes are a few hundred KB at most, so a step's ~24 single
+// launches cost more in launch latency than in traffic.
+constexpr int PLANE_BATCH = 12;
+struct PlaneBatch { PlaneArgs a[PLANE_BATCH]; };
+
+__global__ void __launch_bounds__(128)
+k_plane_ops( float * __restrict__ f, GridDev g, PlaneBatch b ) {
+  plane_op_item( f, g, b.a[blockIdx.y], blockIdx.x*blockDim.x + threadIdx.x );
+}
+
 static int plane_items( const GridDev & g, int X, int op ) {
   const int n3[3] = { g.nx, g.ny, g.nz };
   const int nY = n3[(X+1)%3], nZ = n3[(X+2)%3];
@@ -298,6 +312,26 @@ static void launch_plane( FieldMirror * m, PlaneArgs a ) {
   VPB_CHECK_LAUNCH(); r.launches++;
 }
 
+// Collects operations that do not depend on one another and launches them together.
+struct PlaneQueue {
+  FieldMirror * m; PlaneBatch b; int n = 0, items = 0;
+  explicit PlaneQueue( FieldMirror * m_ ) : m( m_ ) {}
+  void add( const PlaneArgs & a ) {
+    if( n==PLANE_BATCH ) flush();
+    b.a[n++] = a;
+    const int k = plane_items( m->grid->dev, a.X, a.op );
+    if( k>items ) items = k;
+  }
+  void flush() {
+    if( !n ) return;
+    Runtime & r = rt();
+    if( n==1 ) k_plane_op<<< div_up(items,128), 128, 0, r.stream >>>( m->d, m->grid->dev, b.a[0] );
+    else       k_plane_ops<<< dim3( div_up(items,128), n ), 128, 0, r.stream >>>( m->d, m->grid->dev, b );
+    VPB_CHECK_LAUNCH(); r.launches++;
+    n = 0; items = 0;
+  }
+};
+
 bool face_is_remote( const GridMirror * gm, int X, int side ) {
   int bc = gm->fbc[ X + ( side>0 ? 3 : 0 ) ];
   return bc>=0 && bc<g_world_size;
@@ -309,9 +343,10 @@ int face_bc( const GridMirror * gm, int X, int side ) { return gm->fbc[ X + ( si
 // receive buffer IS the opposite send buffer.  Multi-GPU: vpb_comm.cu.
 
 // Device layout of m->d_face: [send_lo | send_hi | recv_lo | recv_hi], each face_floats long.
-void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi ) {
-  float * slo = m->d_face, * shi = m->d_face + m->face_floats;
-  float * rlo = m->d_face + 2*m->face_floats, * rhi = m->d_face + 3*m->face_floats;
+void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi, float * base ) {
+  if( !base ) base = m->d_face;
+  float * slo = base, * shi = base + m->face_floats;
+  float * rlo = base + 2*m->face_floats, * rhi = base + 3*m->face_floats;
   const GridMirror * gm = m->grid;
   const bool rem_lo = face_is_remote( gm, X, -1 ), rem_hi = face_is_remote( gm, X, +1 );
   *from_lo = nullptr; *from_hi = nullptr;
@@ -336,6 +371,12 @@ void fill_ghost_tang_b( FieldMirror * m ) {
   const float d3[3] = { hg->dx, hg->dy, hg->dz };
   const float cdt[3] = { hg->cvac*hg->dt*hg->rdx, hg->cvac*hg->dt*hg->rdy, hg->cvac*hg->dt*hg->rdz };
   const float higend = ( g.nx>1 || g.ny>1 || g.nz>1 ) ? 1.03527618 : 1.;
+  // Three phases instead of per-axis sequences: (1) every local ghost plane and
+  // every message is written / packed in ONE launch -- the ghost planes of
+  // different axes are disjoint, and the packs read face-normal and interior
+  // values that no ghost operation writes; (2) the exchanges, each axis in its
+  // own set of face buffers; (3) every received plane is unpacked in one launch.
+  PlaneQueue q( m );
   for( int X=0; X<3; X++ ) {
     const int Y = (X+1)%3, Z = (X+2)%3;
     // local boundary conditions
@@ -356,23 +397,28 @@ void fill_ghost_tang_b( FieldMirror * m ) {
       } break;
       default: VPB_ERROR( "Bad boundary condition encountered." );
       }
-      launch_plane( m, a );
+      q.add( a );
     }
     // remote (or periodic-to-self) neighbours
-    const bool rem_lo = face_is_remote( gm, X, -1 ), rem_hi = face_is_remote( gm, X, +1 );
-    if( !rem_lo && !rem_hi ) continue;
-    const int nf = plane_items( g, X, OP_PACK_B );
-    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = -1; a.plane = 1;     a.buf = m->d_face;                  launch_plane( m, a ); }
-    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = +1; a.plane = n3[X]; a.buf = m->d_face + m->face_floats; launch_plane( m, a ); }
-    float * from_lo, * from_hi;
-    exchange_axis( m, X, nf, &from_lo, &from_hi );
+    float * base = m->d_face + (size_t)X*4*m->face_floats;
+    if( face_is_remote( gm, X, -1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = -1; a.plane = 1;     a.buf = base;                  q.add( a ); }
+    if( face_is_remote( gm, X, +1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = +1; a.plane = n3[X]; a.buf = base + m->face_floats; q.add( a ); }
+  }
+  q.flush();
+  float * from[3][2] = {};
+  for( int X=0; X<3; X++ ) {
+    if( !face_is_remote( gm, X, -1 ) && !face_is_remote( gm, X, +1 ) ) continue;
+    exchange_axis( m, X, plane_items( g, X, OP_PACK_B ), &from[X][0], &from[X][1], m->d_face + (size_t)X*4*m->face_floats );
+  }
+  for( int X=0; X<3; X++ ) {
     // equal cell size on both sides (checked when the communicator is set up)
     float lw = d3[X];
     const float rw = (2.*d3[X])/(lw+d3[X]);
     lw = (lw-d3[X])/(lw+d3[X]);
-    if( from_lo ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = -1; a.plane = 0;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; launch_plane( m, a ); }
-    if( from_hi ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; launch_plane( m, a ); }
+    if( from[X][0] ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = -1; a.plane = 0;       a.w0 = rw; a.w1 = lw; a.buf = from[X][0]; q.add( a ); }
+    if( from[X][1] ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from[X][1]; q.add( a ); }
   }
+  q.flush();
 }
 
 // local.c:267-296
@@ -535,15 +581,20 @@ void vpic_b200_synchronize_jf( vpb_field_array_t * fa ) {
     if( !rem_lo && !rem_hi ) continue;
     const int nf = plane_items( g, X, OP_PACK_J );
     // both messages are packed before either is folded in (remote.c:474-481)
-    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = -1; a.plane = 1;       a.buf = m->d_face;                  launch_plane( m, a ); }
-    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.buf = m->d_face + m->face_floats; launch_plane( m, a ); }
+    // (the two packs read, and the two folds write, different planes: one launch each;
+    // the axes stay in sequence because edges shared by two faces are folded twice)
+    PlaneQueue q( m );
+    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = -1; a.plane = 1;       a.buf = m->d_face;                  q.add( a ); }
+    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.buf = m->d_face + m->face_floats; q.add( a ); }
+    q.flush();
     float * from_lo, * from_hi;
     exchange_axis( m, X, nf, &from_lo, &from_hi );
     float rw = d3[X], lw = rw + d3[X];
     rw /= lw; lw = d3[X]/lw; lw += lw; rw += rw;
     // from the -X neighbour (its plane nX+1) -> our plane 1; from +X (its plane 1) -> our plane nX+1
-    if( from_lo ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = -1; a.plane = 1;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; launch_plane( m, a ); }
-    if( from_hi ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; launch_plane( m, a ); }
+    if( from_lo ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = -1; a.plane = 1;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; q.add( a ); }
+    if( from_hi ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; q.add( a ); }
+    q.flush();
   }
   finish_write( m );
 }

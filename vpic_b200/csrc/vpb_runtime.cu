@@ -280,7 +280,7 @@ FieldMirror * mirror( vpb_field_array_t * fa ) {
   size_t a = (size_t)(d.nx+2)*(d.ny+2), b = (size_t)(d.ny+2)*(d.nz+2), c = (size_t)(d.nz+2)*(d.nx+2);
   size_t mx = a>b ? a : b; if( c>mx ) mx = c;
   m->face_floats = 5*mx + 32;
-  VPB_CUDA( cudaMalloc( &m->d_face, sizeof(float)*4*m->face_floats ) );
+  VPB_CUDA( cudaMalloc( &m->d_face, sizeof(float)*12*m->face_floats ) );   // [send_lo|send_hi|recv_lo|recv_hi] x 3 axes
   m->dev_valid = false; m->host_valid = true;
   r.fields[fa] = m;
   return m;

@@ -235,7 +235,7 @@ void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
 // field boundary machinery shared by vpb_fields.cu and vpb_divclean.cu
 bool face_is_remote( const GridMirror * gm, int X, int side );
 int  face_bc( const GridMirror * gm, int X, int side );
-void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi );   // packed faces in m->d_face
+void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float ** from_hi, float * base = nullptr );   // packed faces in base (default m->d_face)
 void fill_ghost_tang_b( FieldMirror * m );
 void local_adjust_norm_b( FieldMirror * m );
 void local_adjust_tang_e( FieldMirror * m );
