@@ -219,6 +219,8 @@ GridMirror * mirror( const vpb_grid_t * g ) {
   GridDev & d = m->dev;
   d.nx = g->nx; d.ny = g->ny; d.nz = g->nz;
   d.sx = 1; d.sy = g->nx+2; d.sz = (g->nx+2)*(g->ny+2); d.nv = d.sz*(g->nz+2);
+  fast_div_magic( (unsigned)d.sy, d.m_sy, d.sh_sy ); fast_div_magic( (unsigned)( g->ny+2 ), d.m_ny2, d.sh_ny2 );
+  fast_div_magic( (unsigned)d.sz, d.m_sz, d.sh_sz );
   d.nvp = ( d.nv + 31 ) & ~31;
   d.neighbor = nullptr;
   if( d.nv!=g->nv ) VPB_ERROR( "grid_t.nv (%d) does not match (nx+2)(ny+2)(nz+2) (%d)", g->nv, d.nv );

@@ -56,7 +56,21 @@ struct GridDev {             // passed by value to kernels
   int sx, sy, sz, nv, nvp;
   int face[6];               // FaceAction for -x,-y,-z,+x,+y,+z
   const int32_t * neighbor;  // optional explicit table (6*nv), else nullptr
+  // exact division of a voxel index (< 2^31) by sy, ny+2 and sz without the
+  // ~20-instruction integer divide: q = umulhi( v, m ) >> sh  (see fast_div)
+  unsigned m_sy, sh_sy, m_ny2, sh_ny2, m_sz, sh_sz;
 };
+
+// Magic pair for d >= 2: l = ceil(log2 d), m = ceil( 2^(31+l) / d ), sh = l-1.
+// m*d - 2^(31+l) < d <= 2^l, so for every v < 2^31 the product error stays
+// below 2^(31+l) and ( v*m ) >> (31+l) is floor( v/d ) exactly.
+inline void fast_div_magic( unsigned d, unsigned & m, unsigned & sh ) {
+  unsigned l = 0; while( ( 1ull<<l )<d ) l++;
+  m = (unsigned)( ( ( 1ull<<( 31+l ) ) + d - 1 )/d ); sh = l-1;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ int fast_div( int v, unsigned m, unsigned sh ) { return (int)( __umulhi( (unsigned)v, m ) >> sh ); }
+#endif
 
 // Encoding of the explicit neighbour table: >=0 local voxel, NB_REFLECT, and
 // for everything that ends the local move (any other negative value): the
