@@ -40,13 +40,13 @@ namespace vpb {
 #define VPB_AP_NBUF 1
 #endif
 #ifndef VPB_AP_MINBLK
-#define VPB_AP_MINBLK 5
+#define VPB_AP_MINBLK 10
 #endif
 constexpr int AP_K      = VPB_AP_K;     // consecutive particles per lane
 constexpr int AP_NBUF   = VPB_AP_NBUF;  // tile buffers per warp: 2 = the next tile is loading while this one is pushed
 constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
 #ifndef VPB_AP_WARPS
-#define VPB_AP_WARPS 4
+#define VPB_AP_WARPS 2
 #endif
 constexpr int AP_WARPS  = VPB_AP_WARPS;            // warps per block
 constexpr int AP_MINBLK = VPB_AP_MINBLK;            // resident blocks per SM the registers are budgeted for
@@ -100,7 +100,10 @@ __device__ __forceinline__ void drain_crossers( const float4 * __restrict__ queu
   }
 }
 
-constexpr int AP_DRAIN_MIN = 24;        // fewer crossers than this wait for the next tile's
+#ifndef VPB_AP_DRAIN_MIN
+#define VPB_AP_DRAIN_MIN 24
+#endif
+constexpr int AP_DRAIN_MIN = VPB_AP_DRAIN_MIN;        // fewer crossers than this wait for the next tile's
 
 // p points at the first particle of the range this launch owns (np particles,
 // ntile tiles); idx_base is that particle's index in sp->p (mover indices).
