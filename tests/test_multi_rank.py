@@ -29,11 +29,13 @@ def test_two_rank_oracle_matches_one_rank_oracle_gloo():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("transport", ["put", "nccl"])
+@pytest.mark.parametrize("transport", ["put", "put-unfused", "nccl"])
 def test_two_gpus_match_two_rank_oracle(transport):
-    """put: ghost planes, current folds and migrating particles are stored by our
-    kernels into the neighbour's IPC-mapped mailbox over NVLink; nccl: the same
-    exchanges through ncclSend/ncclRecv.  Same bit-exact checks either way."""
+    """put: ghost planes and current folds are PACKED by the plane kernels straight
+    into the neighbour's IPC-mapped mailbox over NVLink (pack + transfer in one
+    kernel, unpack + wait in one kernel), migrating particles are forwarded by
+    k_put / k_get; put-unfused: every message through k_put / k_get; nccl: the
+    same exchanges through ncclSend/ncclRecv.  Same bit-exact checks either way."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")

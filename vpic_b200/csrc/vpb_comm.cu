@@ -95,6 +95,7 @@ struct Mailbox {
   std::vector<cudaIpcMemHandle_t> handle;
   std::vector<unsigned> sent, rcvd;            // per (rank, direction): messages put to / taken from that slot pair
   unsigned * d_done = nullptr;                 // block counters of the put kernel (2)
+  unsigned * d_done_many = nullptr;            // block counters for fused pack kernels (one per batched operation)
   int *    d_err = nullptr;                    // set by a receive that timed out
   size_t   bytes = 0;
 } MB;
@@ -232,6 +233,39 @@ bool put_sendrecv( int rank_lo, int rank_hi, const void * slo, size_t nslo, cons
 
 } // namespace
 
+// ---- fused exchanges: the caller's own kernels write into / read from the mailboxes ----
+// comm_link_reserve hands out, for one exchange with (rank_lo, rank_hi), the
+// mailbox slots that put_sendrecv would have used: where this rank's "lo" and
+// "hi" messages go in the neighbours' memory (dst, flag to publish, sequence
+// number) and where the neighbours' messages arrive in ours (src, flag to
+// wait for, sequence number).  The pack kernel stores the plane straight into
+// dst over NVLink and publishes; the unpack kernel acquires the flag and reads
+// src.  Returns false (nothing reserved) when the put transport is off, the
+// message does not fit a slot, or VPIC_B200_TRANSPORT=put-unfused.
+bool comm_link_reserve( int rank_lo, int rank_hi, size_t nbytes, CommLink * out ) {
+  static int unfused = -1;
+  if( unfused<0 ) { const char * e = getenv( "VPIC_B200_TRANSPORT" ); unfused = ( e && !strcmp( e, "put-unfused" ) ) ? 1 : 0; }
+  *out = CommLink();
+  if( !MB.on || unfused || nbytes>MB_SLOT ) return false;
+  const int W = g_world_size, me = g_world_rank;
+  const int peer[2] = { rank_lo, rank_hi };
+  for( int d=0; d<2; d++ ) if( peer[d]>=0 ) {
+    const unsigned k = MB.sent[2*peer[d]+d]++;
+    char * box = mailbox_of( peer[d] );
+    out->dst[d] = box + mb_slot_off( me, d, k&1 );
+    out->pub_flag[d] = reinterpret_cast<unsigned *>( box + mb_flag_off( W, me, d, k&1 ) );
+    out->pub_seq[d] = k+1;
+    const int dir = 1-d;                       // what arrives from rank_lo was its "hi" message
+    const unsigned j = MB.rcvd[2*peer[d]+dir]++;
+    out->src[d] = MB.mine + mb_slot_off( peer[d], dir, j&1 );
+    out->wait_flag[d] = reinterpret_cast<const unsigned *>( MB.mine + mb_flag_off( W, peer[d], dir, j&1 ) );
+    out->wait_seq[d] = j+1;
+  }
+  if( !MB.d_done_many ) { VPB_CUDA( cudaMalloc( &MB.d_done_many, sizeof(unsigned)*64 ) ); VPB_CUDA( cudaMemset( MB.d_done_many, 0, sizeof(unsigned)*64 ) ); }
+  out->done = MB.d_done_many;
+  return true;
+}
+
 // Pairwise exchange along one axis.  Messages to the same peer are matched in
 // issue order, so when both neighbours are the same rank (two ranks, periodic)
 // the peer's "low" message must be the first thing we receive from it, and it
@@ -278,6 +312,7 @@ void comm_shutdown() {
   for( char * q : MB.peer ) if( q ) cudaIpcCloseMemHandle( q );
   if( MB.mine ) cudaFree( MB.mine );
   if( MB.d_done ) cudaFree( MB.d_done );
+  if( MB.d_done_many ) cudaFree( MB.d_done_many );
   if( MB.d_err ) cudaFree( MB.d_err );
   MB = Mailbox();
 }

@@ -5,6 +5,7 @@
 //   ghost / boundary planes: src/field_advance/standard/{local,remote}.c
 // Compiled with -fmad=false: every expression rounds like the reference.
 #include "vpb_runtime.h"
+#include <cstdio>
 
 namespace vpb {
 
@@ -215,8 +216,36 @@ struct PlaneArgs {
   int plane;             // plane index the items live on (ghost / face)
   float w0, w1;          // weights (rw,lw) / sign / factor / (decay, drive)
   float cdt_dX, cdt_dY, cdt_dZ;
-  float * buf;           // packed face buffer
+  float * buf;           // packed face buffer (a local one, or a mailbox slot: the neighbour's for a pack, ours for an unpack)
+  // fused exchange (vpb_comm.cu): sync = 1: after the last block has stored its part of buf in the
+  // neighbour's mailbox, publish seq in *flag; sync = 2: wait until *flag has reached seq before reading buf
+  int sync; unsigned seq; unsigned * flag; unsigned * done;
 };
+
+__device__ __forceinline__ void plane_wait( const PlaneArgs & a ) {
+  if( a.sync==2 ) {
+    if( threadIdx.x==0 ) {
+      unsigned v; const long long t0 = clock64();
+      do {
+        asm volatile( "ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.flag) : "memory" );
+        if( (int)( v-a.seq )>=0 ) break;
+        if( clock64()-t0>1200000000000ll ) { printf( "[vpic_b200] fused exchange: plane %u never arrived (flag %u)\n", a.seq, v ); __trap(); }
+        __nanosleep( 64 );
+      } while( true );
+    }
+    __syncthreads();
+  }
+}
+__device__ __forceinline__ void plane_publish( const PlaneArgs & a, unsigned * counter ) {
+  if( a.sync==1 ) {
+    __threadfence_system();
+    __syncthreads();
+    if( threadIdx.x==0 && atomicAdd( counter, 1u )==gridDim.x-1 ) {
+      *counter = 0;
+      asm volatile( "st.release.sys.global.u32 [%0], %1;" :: "l"(a.flag), "r"(a.seq) : "memory" );
+    }
+  }
+}
 
 __device__ __forceinline__ void plane_op_item( float * __restrict__ f, const GridDev & g, const PlaneArgs & a, const int t ) {
   const int n3[3] = { g.nx, g.ny, g.nz };
@@ -283,7 +312,9 @@ __device__ __forceinline__ void plane_op_item( float * __restrict__ f, const Gri
 
 __global__ void __launch_bounds__(128)
 k_plane_op( float * __restrict__ f, GridDev g, PlaneArgs a ) {
+  plane_wait( a );
   plane_op_item( f, g, a, blockIdx.x*blockDim.x + threadIdx.x );
+  plane_publish( a, a.done );
 }
 
 // Several INDEPENDENT plane operations in one launch (blockIdx.y picks the
@@ -294,7 +325,10 @@ struct PlaneBatch { PlaneArgs a[PLANE_BATCH]; };
 
 __global__ void __launch_bounds__(128)
 k_plane_ops( float * __restrict__ f, GridDev g, PlaneBatch b ) {
-  plane_op_item( f, g, b.a[blockIdx.y], blockIdx.x*blockDim.x + threadIdx.x );
+  const PlaneArgs & a = b.a[blockIdx.y];
+  plane_wait( a );
+  plane_op_item( f, g, a, blockIdx.x*blockDim.x + threadIdx.x );
+  plane_publish( a, a.done );
 }
 
 static int plane_items( const GridDev & g, int X, int op ) {
@@ -364,6 +398,28 @@ void exchange_axis( FieldMirror * m, int X, int nfloat, float ** from_lo, float 
   if( rem_hi ) *from_hi = slo;
 }
 
+// Fused variant of exchange_axis for remote (other-rank) neighbours: reserve the
+// mailbox slots of this exchange so that the pack operations store straight into
+// the neighbours' memory and the unpack operations read straight from ours.
+// Returns false when the axis has no other-rank neighbour or the put transport
+// cannot take the message (then the caller packs locally and calls exchange_axis).
+static bool link_axis( FieldMirror * m, int X, int nfloat, CommLink * link ) {
+  const GridMirror * gm = m->grid;
+  const bool rem_lo = face_is_remote( gm, X, -1 ) && face_bc( gm, X, -1 )!=g_world_rank;
+  const bool rem_hi = face_is_remote( gm, X, +1 ) && face_bc( gm, X, +1 )!=g_world_rank;
+  if( !rem_lo && !rem_hi ) return false;
+  // a face that wraps onto this very rank next to a face on another rank: leave it to exchange_axis
+  if( ( face_is_remote( gm, X, -1 ) && !rem_lo ) || ( face_is_remote( gm, X, +1 ) && !rem_hi ) ) return false;
+  return comm_link_reserve( rem_lo ? face_bc( gm, X, -1 ) : -1, rem_hi ? face_bc( gm, X, +1 ) : -1, sizeof(float)*(size_t)nfloat, link );
+}
+static void as_publisher( PlaneArgs & a, const CommLink & l, int side, int slot ) {
+  a.buf = reinterpret_cast<float *>( l.dst[side] ); a.sync = 1; a.flag = l.pub_flag[side]; a.seq = l.pub_seq[side]; a.done = l.done + slot;
+}
+static void as_waiter( PlaneArgs & a, const CommLink & l, int side ) {
+  a.buf = const_cast<float *>( reinterpret_cast<const float *>( l.src[side] ) ); a.sync = 2;
+  a.flag = const_cast<unsigned *>( l.wait_flag[side] ); a.seq = l.wait_seq[side];
+}
+
 // remote.c:61-134 + local.c:50-122: fill every tangential-B ghost plane.
 void fill_ghost_tang_b( FieldMirror * m ) {
   const GridMirror * gm = m->grid; const GridDev & g = gm->dev; const vpb_grid_t * hg = gm->host;
@@ -377,6 +433,7 @@ void fill_ghost_tang_b( FieldMirror * m ) {
   // values that no ghost operation writes; (2) the exchanges, each axis in its
   // own set of face buffers; (3) every received plane is unpacked in one launch.
   PlaneQueue q( m );
+  CommLink link[3]; bool fused[3] = { false, false, false };
   for( int X=0; X<3; X++ ) {
     const int Y = (X+1)%3, Z = (X+2)%3;
     // local boundary conditions
@@ -399,15 +456,19 @@ void fill_ghost_tang_b( FieldMirror * m ) {
       }
       q.add( a );
     }
-    // remote (or periodic-to-self) neighbours
+    // remote (or periodic-to-self) neighbours; with the put transport the packs
+    // store straight into the neighbours' mailboxes and publish (fused[X])
     float * base = m->d_face + (size_t)X*4*m->face_floats;
-    if( face_is_remote( gm, X, -1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = -1; a.plane = 1;     a.buf = base;                  q.add( a ); }
-    if( face_is_remote( gm, X, +1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = +1; a.plane = n3[X]; a.buf = base + m->face_floats; q.add( a ); }
+    fused[X] = link_axis( m, X, plane_items( g, X, OP_PACK_B ), &link[X] );
+    if( face_is_remote( gm, X, -1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = -1; a.plane = 1;     a.buf = base;
+                                        if( fused[X] && link[X].dst[0] ) as_publisher( a, link[X], 0, 2*X );   q.add( a ); }
+    if( face_is_remote( gm, X, +1 ) ) { PlaneArgs a{}; a.op = OP_PACK_B; a.X = X; a.side = +1; a.plane = n3[X]; a.buf = base + m->face_floats;
+                                        if( fused[X] && link[X].dst[1] ) as_publisher( a, link[X], 1, 2*X+1 ); q.add( a ); }
   }
   q.flush();
   float * from[3][2] = {};
   for( int X=0; X<3; X++ ) {
-    if( !face_is_remote( gm, X, -1 ) && !face_is_remote( gm, X, +1 ) ) continue;
+    if( fused[X] || ( !face_is_remote( gm, X, -1 ) && !face_is_remote( gm, X, +1 ) ) ) continue;
     exchange_axis( m, X, plane_items( g, X, OP_PACK_B ), &from[X][0], &from[X][1], m->d_face + (size_t)X*4*m->face_floats );
   }
   for( int X=0; X<3; X++ ) {
@@ -415,8 +476,13 @@ void fill_ghost_tang_b( FieldMirror * m ) {
     float lw = d3[X];
     const float rw = (2.*d3[X])/(lw+d3[X]);
     lw = (lw-d3[X])/(lw+d3[X]);
-    if( from[X][0] ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = -1; a.plane = 0;       a.w0 = rw; a.w1 = lw; a.buf = from[X][0]; q.add( a ); }
-    if( from[X][1] ) { PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from[X][1]; q.add( a ); }
+    for( int sd=0; sd<2; sd++ ) {
+      const bool waits = fused[X] && link[X].src[sd];
+      if( !waits && !from[X][sd] ) continue;
+      PlaneArgs a{}; a.op = OP_UNPACK_GHOST_B; a.X = X; a.side = sd ? +1 : -1; a.plane = sd ? n3[X]+1 : 0; a.w0 = rw; a.w1 = lw; a.buf = from[X][sd];
+      if( waits ) as_waiter( a, link[X], sd );
+      q.add( a );
+    }
   }
   q.flush();
 }
@@ -584,16 +650,21 @@ void vpic_b200_synchronize_jf( vpb_field_array_t * fa ) {
     // (the two packs read, and the two folds write, different planes: one launch each;
     // the axes stay in sequence because edges shared by two faces are folded twice)
     PlaneQueue q( m );
-    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = -1; a.plane = 1;       a.buf = m->d_face;                  q.add( a ); }
-    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.buf = m->d_face + m->face_floats; q.add( a ); }
+    CommLink link; const bool fused = link_axis( m, X, nf, &link );
+    if( rem_lo ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = -1; a.plane = 1;       a.buf = m->d_face;
+                   if( fused && link.dst[0] ) as_publisher( a, link, 0, 0 ); q.add( a ); }
+    if( rem_hi ) { PlaneArgs a{}; a.op = OP_PACK_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.buf = m->d_face + m->face_floats;
+                   if( fused && link.dst[1] ) as_publisher( a, link, 1, 1 ); q.add( a ); }
     q.flush();
-    float * from_lo, * from_hi;
-    exchange_axis( m, X, nf, &from_lo, &from_hi );
+    float * from_lo = nullptr, * from_hi = nullptr;
+    if( !fused ) exchange_axis( m, X, nf, &from_lo, &from_hi );
     float rw = d3[X], lw = rw + d3[X];
     rw /= lw; lw = d3[X]/lw; lw += lw; rw += rw;
     // from the -X neighbour (its plane nX+1) -> our plane 1; from +X (its plane 1) -> our plane nX+1
-    if( from_lo ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = -1; a.plane = 1;       a.w0 = rw; a.w1 = lw; a.buf = from_lo; q.add( a ); }
-    if( from_hi ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi; q.add( a ); }
+    if( from_lo || ( fused && link.src[0] ) ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = -1; a.plane = 1;       a.w0 = rw; a.w1 = lw; a.buf = from_lo;
+                                                 if( fused ) as_waiter( a, link, 0 ); q.add( a ); }
+    if( from_hi || ( fused && link.src[1] ) ) { PlaneArgs a{}; a.op = OP_FOLD_J; a.X = X; a.side = +1; a.plane = n3[X]+1; a.w0 = rw; a.w1 = lw; a.buf = from_hi;
+                                                 if( fused ) as_waiter( a, link, 1 ); q.add( a ); }
     q.flush();
   }
   finish_write( m );

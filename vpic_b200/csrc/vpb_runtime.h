@@ -239,6 +239,13 @@ void sort_movers_by_index( SpeciesMirror * );
 void comm_exchange_faces( FieldMirror * m, int X, float * slo, float * shi, float * rlo, float * rhi, int nfloat );
 void comm_sendrecv( int rank_lo, int rank_hi, const void * slo, size_t nslo, const void * shi, size_t nshi,
                     void * rlo, size_t nrlo, void * rhi, size_t nrhi );   // device buffers, byte counts; rank<0 = no neighbour
+// Mailbox slots of one fused exchange (vpb_comm.cu: comm_link_reserve); index 0 = low side, 1 = high side.
+struct CommLink {
+  char * dst[2] = { nullptr, nullptr };  unsigned * pub_flag[2] = { nullptr, nullptr };        unsigned pub_seq[2] = { 0, 0 };
+  const char * src[2] = { nullptr, nullptr }; const unsigned * wait_flag[2] = { nullptr, nullptr }; unsigned wait_seq[2] = { 0, 0 };
+  unsigned * done = nullptr;             // zeroed block counters (64) for "last block publishes"
+};
+bool comm_link_reserve( int rank_lo, int rank_hi, size_t nbytes, CommLink * out );
 void comm_allsum_d( double * v, int n );
 bool comm_ready();
 void comm_shutdown();
