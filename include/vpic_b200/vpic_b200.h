@@ -117,6 +117,10 @@ int  vpic_b200_comm_ready( void );
    into the neighbours' IPC-mapped mailboxes over NVLink), 0 = ncclSend/ncclRecv
    (VPIC_B200_TRANSPORT=nccl, or the mailbox could not be exported). */
 int  vpic_b200_comm_transport( void );
+/* Diagnostic: right after sort_p, the number of particles that are out of voxel
+   order or outside the segment sp->partition gives their voxel (0 expected; -1 if
+   the device holds no partition).  Lets tests check sort_p at sizes no CPU oracle reaches. */
+long long vpic_b200_sort_violations( vpb_species_t * sp );
 void vpic_b200_finalize( void );
 void vpic_b200_set_coherence( int mode );
 void vpic_b200_set_deposit_mode( int mode );

@@ -1,0 +1,72 @@
+"""BASELINE configs[3]'s box at the size bench.py runs it (512x256x256 cells, 2 species
+x 32 ppc = 2^31 particles, periodic, one GPU): no CPU oracle finishes this in
+seconds, so the checks are the size-independent properties of the path.
+
+  * particle count conserved (periodic box), movers all consumed;
+  * sort_p: every particle inside the segment partition[] gives its voxel, voxels
+    ascending (device-side check, vpic_b200_sort_violations);
+  * charge conservation of the move_p / accumulator / unload chain: with rhob set
+    so that Gauss's law holds at t = 0, the rms of div E - rho/eps0 stays at
+    single-precision round-off over the steps (a deposit that lost or duplicated
+    a streak would show up at the 1e-2 level of the charge-density noise);
+  * total energy within 1e-3 over the steps.
+
+Needs about 120 GB of HBM; skipped on smaller devices."""
+import os
+import sys
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+N = (512, 256, 256)
+PPC = 32
+
+
+def test_full_size_box_conservation_properties():
+    import torch
+    if torch.cuda.get_device_properties(0).total_memory < 150e9:
+        pytest.skip("needs a 180 GB device")
+    import bench
+    from vpic_b200 import load_b200, b200_backend, B200Host
+    L = load_b200()
+    L.vpic_b200_init(0, 0, 1)
+    L.vpic_b200_set_coherence(1)
+    sim = None
+    try:
+        be = b200_backend()
+        sim, sps = bench.uniform_plasma(be, B200Host(), N, PPC, 4)           # sort every 4 steps
+        for k, (sp, vth, w) in enumerate(sps):
+            L.vpic_b200_load_uniform_maxwellian(sp, PPC, vth, w, 777 + k)
+        sim.initialize(full=True)                                            # rhob := eps0 div E - rhof
+        np0 = [sim.sp_struct(sp).np for sp, _, _ in sps]
+        assert np0 == [PPC * N[0] * N[1] * N[2]] * 2
+
+        def div_e_rms():
+            be.clear_rhof(sim.fa)
+            for sp in sim.species_in_list_order():
+                be.accumulate_rho_p(sim.fa, sp)
+            be.synchronize_rho(sim.fa)
+            be.compute_div_e_err(sim.fa)
+            return be.compute_rms_div_e_err(sim.fa)
+
+        e0 = sum(sim.energies())
+        err0 = div_e_rms()
+        for step in range(6):                                                # sort_p runs at steps 0 and 4
+            sim.advance()
+        for sp, _, _ in sps:                                                 # a sort of the state as it is now
+            be.sort_p(sp)
+            assert L.vpic_b200_sort_violations(sp) == 0
+        assert [sim.sp_struct(sp).np for sp, _, _ in sps] == np0
+        assert all(sim.sp_struct(sp).nm == 0 for sp, _, _ in sps)
+        err = div_e_rms()
+        e1 = sum(sim.energies())
+        # scale of the charge-density noise the error is measured against: rms rho of ONE species
+        # is about n0 q / sqrt(ppc) = 0.18 in these units (n0 = q = eps0 = 1); measured 9e-8 / 1.7e-7
+        print("rms div E error: %.3e at t=0, %.3e after 6 steps; total energy %.6e -> %.6e" % (err0, err, e0, e1))
+        assert err0 < 1e-5 and err < 1e-5
+        assert abs(e1 / e0 - 1) < 1e-3
+    finally:
+        if sim is not None:
+            bench.free_sim(L, sim)                                           # 70 GB of particles: give them back
+        L.vpic_b200_set_coherence(0)

@@ -218,6 +218,21 @@ void bin_indices( const int * keys, int n, int nbin, int * start, int * perm ) {
   VPB_CHECK_LAUNCH();
 }
 
+// Diagnostic for tests at sizes no CPU oracle reaches: particles out of voxel
+// order, or outside the segment partition[] gives their voxel.
+__global__ void __launch_bounds__(256)
+k_sort_check( const vpb_particle_t * __restrict__ p, int np, const int * __restrict__ partition, int nv, unsigned long long * __restrict__ bad ) {
+  const int i = blockIdx.x*blockDim.x + threadIdx.x;
+  if( i>=np ) return;
+  const int key = p[i].i;
+  bool wrong = key<0 || key>=nv;
+  if( !wrong ) {
+    const int b = partition[key], e = key+1<nv ? partition[key+1] : np;
+    wrong = i<b || i>=e || ( i>0 && p[i-1].i>key );
+  }
+  if( wrong ) atomicAdd( bad, 1ull );
+}
+
 // spare particle buffer shared by all species (swapped with the sorted species)
 static vpb_particle_t * g_alt = nullptr; static size_t g_alt_cap = 0;
 void release_sort_buffers() { if( g_alt ) cudaFree( g_alt ); g_alt = nullptr; g_alt_cap = 0; }
@@ -262,4 +277,21 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   m->partition_dev_valid = true;
   mark_dev_written( m );
   if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
+}
+
+// Number of particles that violate "sorted by voxel, partition[] consistent".
+// Meaningful right after sort_p (0 expected).  Test / diagnostic entry point.
+extern "C" long long vpic_b200_sort_violations( vpb_species_t * sp ) {
+  if( !sp ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  SpeciesMirror * m = mirror( sp );
+  to_device( m );
+  if( !m->partition_dev_valid ) return -1;
+  unsigned long long * d_bad = (unsigned long long *)scratch( sizeof(unsigned long long) );
+  VPB_CUDA( cudaMemsetAsync( d_bad, 0, sizeof(unsigned long long), r.stream ) );
+  if( m->np>0 ) { k_sort_check<<< div_up( m->np, 256 ), 256, 0, r.stream >>>( m->d_p, m->np, m->d_partition, m->grid->dev.nv, d_bad ); VPB_CHECK_LAUNCH(); r.launches++; }
+  unsigned long long bad = 0;
+  d2h( &bad, d_bad, sizeof(bad), r.stream );
+  VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+  return (long long)bad;
 }
