@@ -224,7 +224,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         if( fmaxf( fmaxf( fabsf( v3 ), fabsf( v4 ) ), fabsf( v5 ) )<=one ) {   // all six faces at once (move_p otherwise)
           T[2*loc] = make_float4( v3, v4, v5, r0.w );
           float j[12];
-          streak_currents( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
+          streak_currents_fast( j, q, v0, v1, v2, ux, uy, uz, q*ux*uy*uz*one_third );
           if( ii==cur ) {
 #           pragma unroll
             for( int m=0; m<12; m++ ) run[m] = __fmaf_rn( run[m], keepf, j[m] );
