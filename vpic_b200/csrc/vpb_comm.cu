@@ -23,7 +23,11 @@
 // bidirectional per neighbour pair (zero-byte messages still publish their
 // flag), which is what makes two parity slots enough: a rank cannot send
 // message k+2 before it has received k+1, which its neighbour sent after
-// consuming k.  NCCL remains for the bootstrap (all-gather of the IPC
+// consuming k.  The field exchanges go one step further (comm_link_reserve):
+// the plane kernels of vpb_fields.cu pack straight into the neighbour's slot
+// and publish, and unpack straight out of their own slot after acquiring the
+// flag -- no k_put / k_get and no staging buffer on that path.  NCCL remains
+// for the bootstrap (all-gather of the IPC
 // handles), the energy all-reduce and messages larger than a mailbox slot.
 // VPIC_B200_TRANSPORT=nccl selects the ncclSend/ncclRecv path for A/B runs.
 #include "vpb_runtime.h"
