@@ -27,17 +27,9 @@ print("launch %d: %d samples, %.0f M warp instructions" % (which, ts, ti / 1e6))
 print("%-18s %5s %6s %6s | long_sb wait short_sb branch lg mio | source" % ("file", "line", "smp%", "inst%"))
 for x in sorted(recs, key=lambda x: -x[3])[:top]:
     print("%-18s %5d %6.2f %6.2f | %5.0f %5.0f %5.0f %5.0f %5.0f %5.0f | %s" % (x[0], x[1], 100 * x[3] / ts, 100 * x[4] / ti, x[5], x[6], x[7], x[8], x[9], x[10], x[2]))
-# totals per stall reason and per region
+# totals per stall reason
 import collections
 tot = collections.Counter(); 
 for x in recs:
     tot["long_sb"] += x[5]; tot["wait"] += x[6]; tot["short_sb"] += x[7]; tot["branch"] += x[8]; tot["lg"] += x[9]; tot["mio+bar"] += x[10]
 print("stall totals (% of samples):", {k: round(100 * v / ts, 1) for k, v in tot.items()})
-reg = collections.Counter(); regi = collections.Counter()
-for x in recs:
-    f, l = x[0], x[1]
-    if f == "vpb_push.cuh": r = "move_p/neighbor (push.cuh 158-224)" if l >= 158 else ("commit/red (push.cuh 146-156)" if l >= 146 else ("load_interp" if l < 37 else ("streak_currents" if l < 57 else "boris/sqrt/div")))
-    elif f == "vpb_advance_p.cu": r = "drain (advance_p.cu <140)" if l < 140 else "main loop / tile io"
-    else: r = f
-    reg[r] += x[3]; regi[r] += x[4]
-for k in reg: print("  %-40s samples %5.1f %%  instructions %5.1f %%" % (k, 100 * reg[k] / ts, 100 * regi[k] / ti))
