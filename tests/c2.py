@@ -33,3 +33,24 @@ def run(s, steps):
     for k in ("ex", "ey", "ez", "cbx", "cby", "cbz"):
         h.update(np.ascontiguousarray(f[k]).tobytes())
     return np.array(en, dtype=np.float64), h.hexdigest()
+
+
+def build_waveguide(be, host=None, n=N):
+    """The sample/waveguide variant (sample/waveguide:27-52): PEC (metal) box, the -z
+    face absorbing, damp = 0.01; a smooth pulse in the middle of the box instead of
+    the deck's antenna, so the walls are reached within a few hundred steps."""
+    s = Simulation(be, host)
+    s.define_grid("metal", (0, 0, 0), tuple(float(k) for k in n), n, dt=float(np.float32(0.95 / np.sqrt(3.0))))
+    s.host.set_fbc(s.g, 2, -4)                   # BOUNDARY(0,0,-1) = face 2: absorb_fields
+    s.define_fields(damp=0.01)
+    f = s.fields(); g = s.grid_struct(s.g)
+    v = np.arange(g.nv)
+    x = (v % (g.nx + 2)).astype(np.float64); y = ((v // (g.nx + 2)) % (g.ny + 2)).astype(np.float64)
+    z = (v // ((g.nx + 2) * (g.ny + 2))).astype(np.float64)
+    r2 = ((x - 0.5 * n[0]) ** 2 + (y - 0.5 * n[1]) ** 2 + (z - 0.3 * n[2]) ** 2) / (0.08 * n[0]) ** 2
+    interior = (x >= 2) & (x <= n[0] - 1) & (y >= 2) & (y <= n[1] - 1) & (z >= 2) & (z <= n[2] - 1)
+    pulse = np.where(interior, np.exp(-r2), 0.0)
+    f["ex"] = (pulse * np.cos(0.3 * y)).astype(np.float32)
+    f["ey"] = (pulse * np.sin(0.2 * z)).astype(np.float32)
+    f["cbz"] = (0.5 * pulse * np.cos(0.25 * x)).astype(np.float32)
+    return s

@@ -43,3 +43,30 @@ def test_gpu_1000_steps_fields_bit_for_bit():
     print("energy rows, relative deviation:", np.abs(en - ge).max(axis=1) / ge.max())
     assert digest == gold["sha256_ex_ey_ez_cbx_cby_cbz"]
     assert np.abs(en - ge).max() <= 1e-11 * ge.max()      # 1.7e7 double additions in two different orders: measured 1.05e-12
+
+
+@pytest.mark.gpu
+def test_gpu_waveguide_variant_300_steps_fields_bit_for_bit():
+    """sample/waveguide's boundary set at 256^3: PEC walls (ghost copies, E_tang = 0),
+    the Higdon absorbing -z face and the TCA damping (damp = 0.01), 300 steps from a
+    pulse that reaches the walls: E and B bit for bit against the compiled reference."""
+    from vpic_b200 import b200_backend, load_b200, B200Host
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "c2_waveguide.json")))
+    L = load_b200()
+    L.vpic_b200_init(0, 0, 1)
+    L.vpic_b200_set_coherence(1)
+    try:
+        s = c2.build_waveguide(b200_backend(), B200Host())
+        be, en = s.be, [s.be.energy_f6(s.fa)]
+        for k in range(1, 301):
+            be.advance_b(s.fa, 0.5); be.advance_e(s.fa, 1.0); be.advance_b(s.fa, 0.5)
+            if k % c2.EVERY == 0:
+                en.append(be.energy_f6(s.fa))
+        L.vpic_b200_sync_to_host(s.fa)
+        _, digest = c2.run(s, 0)
+    finally:
+        L.vpic_b200_set_coherence(0)
+    en, ge = np.array(en), np.array(gold["energies"])
+    assert en[-1].sum() < 0.97 * en[0].sum()                 # the absorbing face and the damping took energy out
+    assert digest == gold["sha256_ex_ey_ez_cbx_cby_cbz"]
+    assert np.abs(en - ge).max() <= 1e-11 * ge.max()
