@@ -90,13 +90,20 @@ def close(a, b, rtol):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", default="oracle", choices=["oracle", "gpu"])
+    ap.add_argument("--mode", default="oracle", choices=["oracle", "gpu", "gpufull"])
     ap.add_argument("--steps", type=int, default=6)
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
+    if args.mode == "gpufull":
+        ok = check_gpu_full_size(rank, world, dist, torch)
+        flag = torch.tensor([1 if ok else 0]); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            print("multi_rank_check", args.mode, "world", world, "PASS" if flag.item() else "FAIL")
+        dist.destroy_process_group()
+        sys.exit(0 if flag.item() else 1)
     from oracle import harness as H
     from vpic_b200 import load_b200, b200_backend
     cases = [("periodic", (8, 6, 5), (world, 1, 1)), ("periodic", (6, 4 * world, 3), (1, world, 1)),
@@ -116,6 +123,63 @@ def main():
         print("multi_rank_check", args.mode, "world", world, "PASS" if flag.item() else "FAIL")
     dist.destroy_process_group()
     sys.exit(0 if flag.item() else 1)
+
+
+def check_gpu_full_size(rank, world, dist, torch):
+    """BASELINE configs[3] as bench.py runs it on N GPUs (512x256x256 cells and 2^31
+    particles PER GPU, slab decomposition, particles migrating every step): the
+    size-independent properties across the ranks -- global particle count conserved,
+    movers consumed, Gauss's law residual at round-off (a lost or doubled current
+    streak, a wrong jf fold or a dropped migrating particle shows at the 1e-2 level),
+    total energy to 1e-3."""
+    import ctypes as C
+    import bench
+    from vpic_b200 import load_b200, b200_backend, B200Host
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    if torch.cuda.get_device_properties(local).total_memory < 150e9:
+        print("skipped: needs 180 GB devices"); return True
+    L = load_b200()
+    L.vpic_b200_init(local, rank, world)
+    if not L.vpic_b200_comm_ready():
+        buf = (C.c_char * 128)()
+        if rank == 0:
+            L.vpic_b200_comm_unique_id(buf, 128)
+        box = [bytes(buf)]
+        dist.broadcast_object_list(box, src=0)
+        L.vpic_b200_comm_init(box[0], 128)
+    L.vpic_b200_set_coherence(1)
+    be = b200_backend()
+    sim, sps = bench.uniform_plasma(be, B200Host(), (512, 256, 256), 32, 4, topo=(world, 1, 1))
+    for k, (sp, vth, w) in enumerate(sps):
+        L.vpic_b200_load_uniform_maxwellian(sp, 32, vth, w, 4321 + 17 * k + 1000 * rank)
+    sim.initialize(full=True)
+
+    def total_np():
+        t = torch.tensor([sum(sim.sp_struct(sp).np for sp, _, _ in sps)], dtype=torch.int64)
+        dist.all_reduce(t); return int(t.item())
+
+    def div_e_rms():
+        be.clear_rhof(sim.fa)
+        for sp in sim.species_in_list_order():
+            be.accumulate_rho_p(sim.fa, sp)
+        be.synchronize_rho(sim.fa)
+        be.compute_div_e_err(sim.fa)
+        return be.compute_rms_div_e_err(sim.fa)
+
+    n0, e0, err0 = total_np(), sum(sim.energies()), div_e_rms()
+    moved = 0
+    for _ in range(5):
+        before = [sim.sp_struct(sp).np for sp, _, _ in sps]
+        sim.advance()
+        moved += sum(abs(sim.sp_struct(sp).np - b) for (sp, _, _), b in zip(sps, before))
+    n1, e1, err1 = total_np(), sum(sim.energies()), div_e_rms()
+    nm = sum(sim.sp_struct(sp).nm for sp, _, _ in sps)
+    ok = n0 == n1 == world * 2 * 32 * 512 * 256 * 256 and nm == 0 and err0 < 1e-5 and err1 < 1e-5 and abs(e1 / e0 - 1) < 1e-3
+    if rank == 0 or not ok:
+        print(f"rank {rank}: particles {n0} -> {n1}, movers left {nm}, rms div E error {err0:.3e} -> {err1:.3e}, "
+              f"energy {e0:.6e} -> {e1:.6e}, net np change on this rank {moved}")
+    bench.free_sim(L, sim)
+    return ok
 
 
 def with_cleaning(s):

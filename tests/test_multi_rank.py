@@ -40,3 +40,13 @@ def test_two_gpus_match_two_rank_oracle(transport):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     launch("gpu", VPIC_B200_TRANSPORT=transport)
+
+
+@pytest.mark.gpu
+def test_two_gpus_full_size_box_conservation_properties():
+    """2 x (512x256x256 cells, 2^31 particles): global count, Gauss's law residual and
+    energy across the ranks with particles migrating every step (put transport)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    launch("gpufull")
