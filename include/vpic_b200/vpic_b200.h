@@ -122,6 +122,9 @@ int  vpic_b200_comm_transport( void );
    the device holds no partition).  Lets tests check sort_p at sizes no CPU oracle reaches. */
 long long vpic_b200_sort_violations( vpb_species_t * sp );
 void vpic_b200_finalize( void );
+/* frees the grow-on-demand device caches (sort_p spare buffer, scratch, boundary_p
+   message buffers); objects and their mirrors stay valid */
+void vpic_b200_trim( void );
 void vpic_b200_set_coherence( int mode );
 void vpic_b200_set_deposit_mode( int mode );
 /* PARITY only: the reference's pipeline count (--tpp) whose summation order the

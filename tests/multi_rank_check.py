@@ -179,6 +179,7 @@ def check_gpu_full_size(rank, world, dist, torch):
         print(f"rank {rank}: particles {n0} -> {n1}, movers left {nm}, rms div E error {err0:.3e} -> {err1:.3e}, "
               f"energy {e0:.6e} -> {e1:.6e}, net np change on this rank {moved}")
     bench.free_sim(L, sim)
+    L.vpic_b200_trim()
     return ok
 
 

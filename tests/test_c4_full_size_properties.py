@@ -68,5 +68,6 @@ def test_full_size_box_conservation_properties():
         assert abs(e1 / e0 - 1) < 1e-3
     finally:
         if sim is not None:
-            bench.free_sim(L, sim)                                           # 70 GB of particles: give them back
+            bench.free_sim(L, sim)                                           # 70 GB of particles: give them back,
+        L.vpic_b200_trim()                                                   # and the 50 GB of sort / scratch caches
         L.vpic_b200_set_coherence(0)

@@ -283,6 +283,17 @@ void * vpic_b200_device_ptr( void * obj, int which ) {
   return nullptr;
 }
 
+// Give back the grow-on-demand device caches (sort_p's spare particle buffer, the
+// scratch arena, boundary_p's message buffers, the PARITY record buffers).  Mirrors
+// stay; the caches are re-grown by the next call that needs them.
+void vpic_b200_trim( void ) {
+  Runtime & r = rt();
+  if( !r.initialised ) return;
+  cudaStreamSynchronize( r.stream );
+  release_boundary_buffers(); release_sort_buffers(); release_parity_buffers();
+  if( r.d_scratch ) cudaFree( r.d_scratch ); r.d_scratch = nullptr; r.scratch_bytes = 0;
+}
+
 void vpic_b200_finalize( void ) {
   Runtime & r = rt();
   if( !r.initialised ) return;

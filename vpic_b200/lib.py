@@ -37,7 +37,7 @@ def load_b200():
         return L
     d, i, f = C.c_double, C.c_int, C.c_float
     sig = {
-        "vpic_b200_init": (i, [i, i, i]), "vpic_b200_finalize": (None, []),
+        "vpic_b200_init": (i, [i, i, i]), "vpic_b200_finalize": (None, []), "vpic_b200_trim": (None, []),
         "vpic_b200_set_world": (None, [i, i]), "vpic_b200_comm_unique_id": (i, [_P, i]),
         "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []), "vpic_b200_comm_transport": (i, []), "vpic_b200_sort_violations": (C.c_longlong, [_P]),
         "vpic_b200_set_coherence": (None, [i]), "vpic_b200_set_deposit_mode": (None, [i]),
