@@ -136,8 +136,11 @@ def check_gpu_full_size(rank, world, dist, torch):
     import bench
     from vpic_b200 import load_b200, b200_backend, B200Host
     local = int(os.environ.get("LOCAL_RANK", rank))
-    if torch.cuda.get_device_properties(local).total_memory < 150e9:
-        print("skipped: needs 180 GB devices"); return True
+    free_bytes, total_bytes = torch.cuda.mem_get_info(local)
+    enough = torch.tensor([1 if ( total_bytes >= 150e9 and free_bytes >= 125e9 ) else 0])
+    dist.all_reduce(enough, op=dist.ReduceOp.MIN)                     # every rank takes the same branch
+    if not enough.item():
+        print(f"rank {rank}: skipped, needs 125 GB free on a 180 GB device (free {free_bytes / 1e9:.0f} GB)"); return True
     L = load_b200()
     L.vpic_b200_init(local, rank, world)
     if not L.vpic_b200_comm_ready():
