@@ -154,6 +154,25 @@ void * vpic_b200_device_ptr( void * obj, int which );
    from a counter-based generator, directly on the device (no host copy). */
 void vpic_b200_load_uniform_maxwellian( vpb_species_t * sp, int ppc, float vth, float w, uint64_t seed );
 
+/* NO COUNTERPART IN THE REFERENCE.
+   energy_f (vacuum, one material) for callers that may not allocate (CUDA-graph
+   capture, tight serving loops): the per-block partial sums live in a file-scope
+   static device array instead of the cudaMalloc'ed scratch arena, so the call
+   performs no cudaMalloc / cudaFree and touches no runtime state.
+     d_en6       out, DEVICE pointer to 6 doubles (ex, ey, ez, cbx, cby, cbz energies, energy_f.c order)
+     d_field_soa in, DEVICE pointer to the field mirror's SoA planes = vpic_b200_device_ptr( fa, 0 )
+     nx, ny, nz  the grid's local cell counts (the planes' ghost layout follows from them)
+     eps_rmu6    HOST pointer: epsx, epsy, epsz, rmux, rmuy, rmuz of the material
+     scale       0.5 * eps0 * dV (what energy_f multiplies the sums with)
+     stream      cudaStream_t the two kernels are launched on (NULL = default stream)
+   Limit: nx*ny*nz <= 33 554 432 cells (384 KB of static device memory per GPU, held until
+   exit); larger grids return -2.  Returns 0, or -1 bad args, -2 too large, -3 CUDA error
+   (a message goes to stderr; the process is NOT terminated).  All calls share the one
+   array: calls that overlap on the GPU race; the first call on a device must be made
+   outside stream capture (it looks the array's device address up). */
+int vpic_b200_energy_f_noalloc( double * d_en6, const float * d_field_soa, int nx, int ny, int nz,
+                                const float * eps_rmu6, double scale, void * stream );
+
 /* ======================= Part 3: stand-alone host layer =================== */
 
 /* src/grid/grid_structors.c, partition.c:25-182, ops.c:18-211 */

@@ -48,6 +48,7 @@ def load_b200():
         "vpic_b200_launch_count": (C.c_longlong, []), "vpic_b200_transfer_bytes": (None, [C.POINTER(C.c_longlong)]), "vpic_b200_stream": (_P, []),
         "vpic_b200_device_ptr": (_P, [_P, i]),
         "vpic_b200_load_uniform_maxwellian": (None, [_P, i, f, f, C.c_uint64]),
+        "vpic_b200_energy_f_noalloc": (i, [_P, _P, i, i, i, C.POINTER(f), d, _P]),
         "vpic_b200_new_grid": (_P, []), "vpic_b200_delete_grid": (None, [_P]),
         "vpic_b200_partition_periodic_box": (None, [_P] + [d] * 6 + [i] * 6),
         "vpic_b200_partition_absorbing_box": (None, [_P] + [d] * 6 + [i] * 7),
