@@ -113,6 +113,14 @@ void vpic_b200_set_world( int world_rank, int world_size );
 int  vpic_b200_comm_unique_id( void * out, int nbytes );           /* returns bytes written */
 void vpic_b200_comm_init( const void * id_bytes, int nbytes );
 int  vpic_b200_comm_ready( void );
+/* The same transport WITHOUT NCCL (and therefore also with several ranks on one GPU): every rank
+   obtains its 80-byte mailbox record (cudaIpc handle), the host program all-gathers the records
+   (rank order), every rank installs the set.  Exchanges, migration and the all-reduce (summed in
+   rank order, so every rank gets the same bits) then run on our put kernels over peer memory.  A
+   host program built from the reference needs neither call: the first exchange bootstraps itself
+   over the program's own mp_allgather_i (src/util/mp/mp.h:76-79). */
+int  vpic_b200_comm_mailbox_record( void * out, int nbytes );      /* returns bytes written (80) */
+void vpic_b200_comm_init_handles( const void * all_records, int nbytes_each );
 /* 1 = face exchanges / particle migration use the put transport (kernels storing
    into the neighbours' IPC-mapped mailboxes over NVLink), 0 = ncclSend/ncclRecv
    (VPIC_B200_TRANSPORT=nccl, or the mailbox could not be exported). */
@@ -148,6 +156,12 @@ void * vpic_b200_stream( void );               /* cudaStream_t the kernels run o
    1 movers, 2 partition (species); 0 SoA planes (field); 0 coefficients
    (interpolator); 0 accumulator. */
 void * vpic_b200_device_ptr( void * obj, int which );
+
+/* src/vpic/advance.cc:78-101: drop the particles whose movers are still unprocessed after
+   num_comm_round boundary_p calls (voxel restored, charge accumulated to rhob, back-fill in
+   reverse mover order), for host programs whose particles live on the device; a program built
+   from the reference runs that loop itself on the host arrays.  Returns the particles removed. */
+int vpic_b200_drop_unprocessed_movers( vpb_species_t * sp_list, vpb_field_array_t * fa );
 
 /* Synthetic loader used by bench.py: fills sp with ppc particles per cell,
    uniform in each voxel, Maxwellian momenta (vth in units of c), weight w,

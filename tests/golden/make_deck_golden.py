@@ -14,7 +14,13 @@ against libvpic_b200.so and compares with these digests.
   lpi_c5     sample/lpi_2d_F6_test at BASELINE configs[4]'s size (96x1x549 cells,
              512 ppc per species as shipped), 20 steps, dumps every 10
 
-Usage: python tests/golden/make_deck_golden.py [harris] [lpi_small] [harris_c3] [lpi_c5]"""
+Multi-rank runs of the same reference programs (the reference itself on N ranks of the
+stand-in MPI, oracle/mprun.py): `harris@4` = sample/harris on 4 ranks, topology (1,4,1)
+(sample/harris:153-156); `lpi_small@4` = the LPI deck on 4 ranks, topology (4,1,1)
+(sample/lpi_2d_F6_test:279-281) -> tests/golden/<deck>_np<N>_outputs.json.  Every rank
+writes its own dump files; all of them are digested.
+
+Usage: python tests/golden/make_deck_golden.py [harris] [lpi_small] [harris_c3] [lpi_c5] [harris@2] [lpi_small@4] ..."""
 import hashlib
 import json
 import os
@@ -50,15 +56,25 @@ def digest_outputs(d):
 
 
 def main(names):
-    for deck in names or list(DECKS):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    from mprun import mprun
+    for name in names or list(DECKS):
+        deck, _, nranks = name.partition("@")
+        nranks = int(nranks or 1)
         exe = os.path.join(ROOT, "oracle", "_ref", f"deckrun_{deck}_ref")
-        with tempfile.TemporaryDirectory() as d:
-            subprocess.run([exe, "--tpp", "1"], cwd=d, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        with tempfile.TemporaryDirectory(dir=os.path.join(ROOT, ".scratch") if os.path.isdir(os.path.join(ROOT, ".scratch")) else None) as d:
+            if nranks == 1:
+                subprocess.run([exe, "--tpp", "1"], cwd=d, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            else:
+                rc, texts = mprun(nranks, [exe, "--tpp", "1"], cwd=d)
+                assert rc == 0, texts[0][-2000:]
             out = digest_outputs(d)
             energies = open(os.path.join(d, "energies")).read() if os.path.exists(os.path.join(d, "energies")) else None
-        json.dump({"deck": DECKS[deck], "files": out, "energies": energies},
-                  open(os.path.join(HERE, f"{deck}_outputs.json"), "w"), indent=1)
-        print(deck, len(out), "files")
+        tag = deck if nranks == 1 else f"{deck}_np{nranks}"
+        what = DECKS[deck] if nranks == 1 else DECKS[deck] + f"; the reference on {nranks} ranks of the stand-in MPI (oracle/mpi_stub, oracle/mprun.py)"
+        json.dump({"deck": what, "ranks": nranks, "files": out, "energies": energies},
+                  open(os.path.join(HERE, f"{tag}_outputs.json"), "w"), indent=1)
+        print(name, len(out), "files")
 
 
 if __name__ == "__main__":

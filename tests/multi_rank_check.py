@@ -69,18 +69,40 @@ def to_global(p, origin, ln, gn):
     return np.stack([x % gn[0], y % gn[1], z % gn[2]], 1)
 
 
-def build(be, kind, gn, topo, rank, ppc, seed, sort_interval=3):
+LOCALISED = False      # --localised: the plasma starts inside rank 0's brick only (quiet faces elsewhere)
+LOCALISED_LN = None    # that brick's cell counts (of the N-rank topology, also for the 1-rank comparison run)
+
+
+def build(be, kind, gn, topo, rank, ppc, seed, sort_interval=3, host=None):
     from common import make_sim
     ln = tuple(gn[a] // topo[a] for a in range(3))
     idx = (rank % topo[0], (rank // topo[0]) % topo[1], rank // (topo[0] * topo[1]))
     origin = tuple(idx[a] * ln[a] for a in range(3))
     L = tuple(0.5 * k for k in gn)
-    s = make_sim(be, None, kind=kind, n=gn, length=L, topo=topo, ppc=2 * ppc, sort_interval=sort_interval, max_np_factor=2.0, max_nm=4000)
+    s = make_sim(be, host, kind=kind, n=gn, length=L, topo=topo, ppc=2 * ppc, sort_interval=sort_interval, max_np_factor=2.0, max_nm=4000)
     for k, sp in enumerate(s.species):
         p, cells = global_particles(gn, ppc, 0.25, seed + k)
+        if LOCALISED:
+            keep = np.all(cells < np.array(LOCALISED_LN), axis=1)
+            p, cells = p[keep], cells[keep]
         s.set_particles(sp, local_slice(p, cells, origin, ln))
     analytic_fields(s, gn, origin)
     return s, origin, ln
+
+
+def case_list(world):
+    """(boundary kind, global cells, topology).  1-D splits along each axis; at 4 and 8 ranks also the
+    (2,2,1) and (2,2,2) bricks whose edges and corners need the x -> y -> z three-pass exchange
+    (src/field_advance/standard/remote.c:280-296; rank map src/grid/partition.c:3-23)."""
+    cases = [("periodic", (8, 6, 5), (world, 1, 1)), ("periodic", (6, 4 * world, 3), (1, world, 1)),
+             ("absorbing", (4 * world, 5, 4), (world, 1, 1)), ("metal", (6, 3, 2 * world), (1, 1, world))]
+    if world == 8:
+        cases = [("periodic", (16, 4, 3), (8, 1, 1)), ("absorbing", (4, 16, 3), (1, 8, 1))]
+    if world == 4:
+        cases += [("periodic", (8, 6, 3), (2, 2, 1)), ("absorbing", (6, 3, 8), (2, 1, 2)), ("metal", (5, 6, 6), (1, 2, 2))]
+    if world == 8:
+        cases += [("periodic", (6, 6, 6), (2, 2, 2)), ("absorbing", (8, 6, 4), (2, 2, 2)), ("metal", (6, 4, 6), (2, 2, 2))]
+    return cases
 
 
 def close(a, b, rtol):
@@ -92,7 +114,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mode", default="oracle", choices=["oracle", "gpu", "gpufull"])
     ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--localised", action="store_true",
+                    help="all particles start in rank 0's brick: with 3 or more ranks along an axis some neighbour pairs "
+                         "have nothing to exchange while others do (per-pair message decisions of boundary_p)")
     args = ap.parse_args()
+    global LOCALISED
+    LOCALISED = args.localised
     import torch
     import torch.distributed as dist
     dist.init_process_group("gloo")
@@ -106,10 +133,14 @@ def main():
         sys.exit(0 if flag.item() else 1)
     from oracle import harness as H
     from vpic_b200 import load_b200, b200_backend
-    cases = [("periodic", (8, 6, 5), (world, 1, 1)), ("periodic", (6, 4 * world, 3), (1, world, 1)),
-             ("absorbing", (4 * world, 5, 4), (world, 1, 1)), ("metal", (6, 3, 2 * world), (1, 1, world))]
+    cases = case_list(world)
+    if args.localised:
+        cases = [("periodic", (4 * world, 4, 3), (world, 1, 1)), ("absorbing", (4 * world, 5, 4), (world, 1, 1)),
+                 ("absorbing", (5, 3 * world, 4), (1, world, 1))]
     ok = True
     for kind, gn, topo in cases:
+        global LOCALISED_LN
+        LOCALISED_LN = tuple(gn[a] // topo[a] for a in range(3))
         H.set_world(rank, world)
         so, origin, ln = build(H.oracle_backend(), kind, gn, topo, rank, 6, 40)
         H.install_gloo_exchange(so)
@@ -242,12 +273,20 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch):
     L.vpic_b200_init(local % max(torch.cuda.device_count(), 1), rank, world)
     if not L.vpic_b200_comm_ready():
         import ctypes as C
-        buf = (C.c_char * 128)()
-        if rank == 0:
-            L.vpic_b200_comm_unique_id(buf, 128)
-        box = [bytes(buf)]
-        dist.broadcast_object_list(box, src=0)
-        L.vpic_b200_comm_init(box[0], 128)
+        if os.environ.get("VPB_TEST_BOOTSTRAP") == "handles":
+            # no NCCL at all: the mailboxes' cudaIpc records travel over gloo; works with several ranks on ONE GPU
+            rec = (C.c_char * 80)()
+            L.vpic_b200_comm_mailbox_record(rec, 80)
+            recs = [None] * world
+            dist.all_gather_object(recs, bytes(rec))
+            L.vpic_b200_comm_init_handles(b"".join(recs), 80)
+        else:
+            buf = (C.c_char * 128)()
+            if rank == 0:
+                L.vpic_b200_comm_unique_id(buf, 128)
+            box = [bytes(buf)]
+            dist.broadcast_object_list(box, src=0)
+            L.vpic_b200_comm_init(box[0], 128)
     want = 0 if os.environ.get("VPIC_B200_TRANSPORT") == "nccl" else 1
     if L.vpic_b200_comm_transport() != want:
         print(f"rank {rank}: transport {L.vpic_b200_comm_transport()} instead of {want}")

@@ -557,3 +557,25 @@ def test_hydro_moments(gpu, kind, deposit):
     finally:
         L.vpic_b200_set_coherence(0)
         L.vpic_b200_set_deposit_mode(0)
+
+
+def test_unprocessed_movers_are_dropped_like_the_reference(gpu):
+    """advance.cc:78-101: with num_comm_round = 0 every particle that reached a wall is still on
+    the mover list after the boundary_p loop; the driver drops them (voxel restored, charge to
+    rhob, reverse back-fill).  Survivor order bit-exact, rhob to float-atomic rounding."""
+    so, sg = pair(gpu, kind="absorbing", n=(6, 5, 4), ppc=12)
+    for s in (so, sg):
+        s.num_comm_round = 0
+        s.initialize()
+    dropped = 0
+    for _ in range(3):
+        before = sum(so.sp_struct(a).np for a in so.species)
+        so.advance(); sg.advance()
+        dropped += before - sum(so.sp_struct(a).np for a in so.species)
+        for a, b in zip(so.species, sg.species):
+            assert so.sp_struct(a).nm == 0 and sg.sp_struct(b).nm == 0
+            assert so.sp_struct(a).np == sg.sp_struct(b).np
+            assert same_bits(sg.particles(b), so.particles(a))
+        assert close(sg.fields()["rhob"], so.fields()["rhob"], 1e-5)
+        sg.fields()[:] = so.fields(); sg.interpolators()[:] = so.interpolators()
+    assert dropped > 0

@@ -42,6 +42,12 @@ namespace vpb {
 #ifndef VPB_AP_MINBLK
 #define VPB_AP_MINBLK 10
 #endif
+#ifndef VPB_AP_COMMIT_AT_TILE_END
+#define VPB_AP_COMMIT_AT_TILE_END 0
+#endif
+#ifndef VPB_HINT_STREAM
+#define VPB_HINT_STREAM 0     // 1: evict_first L2 policy on the tile's bulk load and bulk store
+#endif
 constexpr int AP_K      = VPB_AP_K;     // consecutive particles per lane
 constexpr int AP_NBUF   = VPB_AP_NBUF;  // tile buffers per warp: 2 = the next tile is loading while this one is pushed
 constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
@@ -132,8 +138,13 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     const uint32_t bytes = (uint32_t)( ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE )*32u;
     const uint32_t bar = smem_u32( &S.bar[b] ), dst = smem_u32( S.tile[b] );
     asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
+#if VPB_HINT_STREAM
+    asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                  :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar), "l"(l2_policy_evict_first()) : "memory" );
+#else
     asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                   :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
+#endif
   };
 
   uint32_t phase = 0;                          // bit b: parity the next wait on buffer b expects
@@ -270,13 +281,25 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         __syncwarp();
       }
     }
+#if VPB_AP_COMMIT_AT_TILE_END
+    // The lane's next tile lies total_warps tiles ahead, in other voxels: its open
+    // run ends here.  Committing it now instead of at the first particle of the
+    // next tile (about one tile time later, by when ~60 MB of particle stream have
+    // gone through L2) finds the voxel's accumulator sectors still in L2 from the
+    // commits of the neighbouring lanes.
+    if( keepf!=0.f ) { commit_currents( acc, cur, run ); keepf = 0.f; cur = -1; }
+#endif
     n_carry = qn;              // whatever is left rides along; its tile is written back now
     // write the tile back: generic-proxy writes -> async-proxy bulk store
     asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
     __syncwarp();
     if( lane==0 ) {
       const uint32_t bytes = (uint32_t)cnt*32u;
+#if VPB_HINT_STREAM
+      asm volatile( "cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" :: "l"(p + t0), "r"(smem_u32( T )), "r"(bytes), "l"(l2_policy_evict_first()) : "memory" );
+#else
       asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(smem_u32( T )), "r"(bytes) : "memory" );
+#endif
       asm volatile( "cp.async.bulk.commit_group;" ::: "memory" );
       if( AP_NBUF==1 ) asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer is reused at once
     }

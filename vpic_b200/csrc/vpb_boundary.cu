@@ -781,9 +781,14 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     const size_t S = sizeof(vpb_particle_injector_t);
     for( int X=0; X<3; X++ ) {
       const int lo = X, hi = X+3;
-      const int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
+      int rank_lo = gm->pkind[lo]==PK_REMOTE ? gm->fbc[lo] : -1, rank_hi = gm->pkind[hi]==PK_REMOTE ? gm->fbc[hi] : -1;
+      // Whether a pair of neighbours exchanges a payload is decided from the two
+      // counts BOTH of them hold after the count phase (ours to them, theirs to
+      // us), never from traffic on our other face: with three or more ranks along
+      // an axis the rank on the quiet side has no way to know about that.
+      if( n_send[lo]+n_recv[lo]==0 ) rank_lo = -1;
+      if( n_send[hi]+n_recv[hi]==0 ) rank_hi = -1;
       if( rank_lo<0 && rank_hi<0 ) continue;
-      if( n_send[lo]+n_send[hi]+n_recv[lo]+n_recv[hi]==0 ) continue;
       comm_sendrecv( rank_lo, rank_hi, B.send[lo], S*(size_t)n_send[lo], B.send[hi], S*(size_t)n_send[hi],
                      B.recv[lo], S*(size_t)n_recv[lo], B.recv[hi], S*(size_t)n_recv[hi] );
     }
@@ -839,4 +844,49 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   }
   if( sparse ) sparse_download( ss );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ma ); to_host( mf ); }
+}
+
+// What vpic_simulation::advance() does with movers that are still unprocessed
+// after num_comm_round calls of boundary_p (src/vpic/advance.cc:78-101): the
+// particle's voxel is restored (p.i >>= 3), its charge goes to rhob
+// (accumulate_rhob), it is removed with the usual back-fill, last mover first.
+// A host program built from the reference runs that loop itself on the host
+// arrays; this is the same thing for programs whose particles live on the
+// device (the stand-alone driver, bench.py).  Returns the particles removed.
+extern "C" int vpic_b200_drop_unprocessed_movers( vpb_species_t * sp_list, vpb_field_array_t * fa ) {
+  if( !sp_list ) return 0;
+  if( !fa || sp_list->g!=fa->g ) VPB_ERROR( "Bad args" );
+  Runtime & r = rt();
+  int dropped = 0;
+  FieldMirror * mf = nullptr;
+  for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
+    if( sp->nm<=0 ) continue;
+    SpeciesMirror * m = mirror( sp );
+    to_device( m );
+    if( m->nm<=0 ) continue;
+    if( !mf ) { mf = mirror( fa ); to_device( mf ); }
+    GridMirror * gm = particle_grid( m->grid );
+    GridDev g = gm->dev; g.neighbor = nullptr;                    // every exit is absorbed, whatever the table says
+    if( !B.d_int ) VPB_CUDA( cudaMalloc( &B.d_int, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ) ) );
+    VPB_CUDA( cudaMemsetAsync( B.d_int, 0, sizeof(int)*( 32 + 4*BND_MAX_SP + 8 ), r.stream ) );
+    BndFaces bf = {};
+    for( int f=0; f<6; f++ ) bf.kind[f] = PK_ABSORB;
+    bf.face_count = B.d_int;
+    if( !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
+    VPB_WARNING( "Removing %i particles associated with unprocessed %s movers (increase num_comm_round)", m->nm, sp->name );
+    const float q_r8V = sp->q*sp->g->r8V;
+    // single ordered block: the movers are few by construction, and rhob receives
+    // them one after the other like the host loop
+    k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16, true );
+    k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
+    VPB_CHECK_LAUNCH(); r.launches += 2;
+    dropped += m->nm;
+    m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
+    mark_dev_written( m );
+    sp->np = m->np;
+    movers_to_host( m );
+    if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
+  }
+  if( mf ) finish_write( mf );
+  return dropped;
 }

@@ -40,6 +40,9 @@ using namespace vpb;
 namespace {
 
 static std::set<const void *> & own_species() { static std::set<const void *> s; return s; }
+// field arrays that came out of vpic_b200_restore_fa: their f / mc arrays were
+// allocated by the host program's restore_data (MALLOC_ALIGNED), not by us
+static std::set<const void *> & restored_fas() { static std::set<const void *> s; return s; }
 
 void * alloc_aligned( size_t bytes, size_t align ) {
   void * p = nullptr;
@@ -415,6 +418,7 @@ void * vpic_b200_restore_fa( void ) {
   fa->params = p;
   void ** k = (void **)fa->kernel;
   for( size_t i=0; i<sizeof(vpb_field_advance_kernels_t)/sizeof(void *); i++ ) k[i] = restore_sym();
+  restored_fas().insert( fa );
   return fa;
 }
 
@@ -423,8 +427,15 @@ void vpic_b200_delete_fa( vpb_field_array_t * fa ) {
   if( unregister_object && register_object ) unregister_object( fa );
   vpic_b200_forget( fa );
   vpb_sfa_params_t * p = (vpb_sfa_params_t *)fa->params;
-  if( p ) { free( p->mc ); free( p ); }
-  free( fa->f ); free( fa );
+  // A restored array's f and mc are MALLOC_ALIGNED blocks of the host program
+  // (checkpt.c:424-425: the pointer sits inside a larger malloc block), so they
+  // go back through its FREE_ALIGNED; the structs themselves were plain malloc.
+  const bool restored = restored_fas().erase( fa )!=0;
+  if( restored && !util_free_aligned ) VPB_ERROR( "a restored field array needs the host program's util_free_aligned" );
+  auto release = [&]( void * a ) { if( !a ) return; if( restored ) util_free_aligned( &a ); else free( a ); };
+  unpin_host( fa->f );
+  if( p ) { release( p->mc ); free( p ); }
+  release( fa->f ); free( fa );
 }
 
 // field_advance.c: delete_field_array dispatches through the table

@@ -161,7 +161,7 @@ void to_host( SpeciesMirror * m ) {
   if( m->host->p && m->np>0 )
     d2h( m->host->p, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, r.stream );
   if( m->host->partition && m->partition_dev_valid )
-    d2h( m->host->partition, m->d_partition, sizeof(int)*(size_t)m->grid->dev.nv, r.stream );
+    d2h( m->host->partition, m->d_partition, sizeof(int)*( (size_t)m->grid->dev.nv + 1 ), r.stream );   // nv+1 entries (species_advance.c:138); [nv] = np
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   if( m->host->p ) m->host_valid = true;
 }
@@ -189,12 +189,14 @@ extern "C" {
 void vpic_b200_set_world( int world_rank, int world_size ) {
   g_world_size = world_size<1 ? 1 : world_size;
   g_world_rank = world_rank<0 ? 0 : world_rank;
+  g_world_explicit = true;
 }
 
 int vpic_b200_init( int device, int world_rank, int world_size ) {
   Runtime & r = rt();
   if( !r.initialised ) r.device = device<0 ? 0 : device;
   g_world_rank = world_rank; g_world_size = world_size<1 ? 1 : world_size;
+  g_world_explicit = true;
   ensure_init();
   return r.sm_count;
 }

@@ -3,9 +3,21 @@
 #include <cstdarg>
 #include <cstring>
 
+// A host program built from the reference carries its rank / size and its
+// message-passing layer (src/util/util_base.h:291-295, src/util/mp/mp.h:76-79);
+// weak, so that the library also loads on its own.  An unmodified deck never
+// calls vpic_b200_init / vpic_b200_comm_init: the library then takes rank and
+// size from these and bootstraps its NCCL communicator over the host program's
+// own allgather (vpb_comm.cu: need_comm).
+extern "C" {
+extern int _world_rank __attribute__((weak));
+extern int _world_size __attribute__((weak));
+}
+
 namespace vpb {
 
 int g_world_rank = 0, g_world_size = 1;
+bool g_world_explicit = false;     // vpic_b200_init / vpic_b200_set_world were called
 
 void fatal( const char * file, int line, const char * fmt, ... ) {
   // Reference convention: src/util/util_base.h:267-273
@@ -26,10 +38,18 @@ void ensure_init() {
   Runtime & r = rt();
   if( r.initialised ) return;
   int n = 0;
+  bool from_host_program = false;
+  if( !g_world_explicit && &_world_size && &_world_rank && _world_size>1 ) {
+    g_world_rank = _world_rank; g_world_size = _world_size; from_host_program = true;
+  }
   cudaError_t e = cudaGetDeviceCount( &n );
   if( e!=cudaSuccess || n<1 )
     VPB_ERROR( "libvpic_b200 needs a CUDA device (B200, sm_100a); none is usable (%s). "
                "There is no CPU fallback.", e==cudaSuccess ? "device count is 0" : cudaGetErrorString(e) );
+  if( from_host_program ) {          // one process per GPU: LOCAL_RANK if the launcher gives one, else rank modulo devices
+    const char * lr = getenv( "LOCAL_RANK" );
+    r.device = lr ? atoi( lr ) : g_world_rank;
+  }
   if( r.device>=n ) r.device = r.device % n;
   VPB_CUDA( cudaSetDevice( r.device ) );
   cudaDeviceProp prop; VPB_CUDA( cudaGetDeviceProperties( &prop, r.device ) );

@@ -21,6 +21,7 @@
 namespace vpb {
 
 extern int g_world_rank, g_world_size;
+extern bool g_world_explicit;
 
 [[noreturn]] void fatal( const char * file, int line, const char * fmt, ... );
 void warning( const char * file, int line, const char * fmt, ... );

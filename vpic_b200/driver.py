@@ -239,9 +239,8 @@ class Simulation:
         be.reduce_accumulator_array(self.aa)                          # :65-66
         for _ in range(self.num_comm_round):                          # :73-77
             be.boundary_p(self.pbc_list, self.sp_list_head, self.fa, self.aa)
-        for sp in self.species_in_list_order():                       # :78-101 (drop unprocessed movers)
-            if self.sp_struct(sp).nm:
-                raise RuntimeError("unprocessed particle movers left after boundary_p")
+        if any(self.sp_struct(sp).nm for sp in self.species):         # :78-101 (drop unprocessed movers into rhob)
+            self.drop_unprocessed_movers()
         be.clear_jf(self.fa)                                          # :107-110
         be.unload_accumulator_array(self.fa, self.aa)
         be.synchronize_jf(self.fa)
@@ -269,6 +268,24 @@ class Simulation:
             self.last_sync_err = be.synchronize_tang_e_norm_b(self.fa)
         be.load_interpolator_array(self.ia, self.fa)                  # :185
         g.step += 1                                                   # :187
+
+    def drop_unprocessed_movers(self):
+        """src/vpic/advance.cc:78-101: movers that num_comm_round boundary_p calls did not
+        finish are dropped -- voxel restored, charge to rhob, back-fill, last mover first."""
+        if self.be.kind == "b200":
+            self.be.L.vpic_b200_drop_unprocessed_movers(self.sp_list_head, self.fa)
+            return
+        fa = C.cast(self.fa, C.POINTER(abi.FieldArray)).contents
+        for sp in self.species_in_list_order():
+            s = self.sp_struct(sp)
+            p, pm = abi.as_array(s.p, s.max_np, abi.particle_dtype), self.movers(sp)
+            for k in range(s.nm - 1, -1, -1):
+                i = int(pm["i"][k])
+                p["i"][i] >>= 3
+                self.be.accumulate_rhob(fa.f, C.c_void_p(C.cast(s.p, C.c_void_p).value + 32 * i), self.g, s.q)
+                p[i] = p[s.np - 1]
+                s.np -= 1
+            s.nm = 0
 
     # ---- diagnostics: dump_energies (src/vpic/dump.cc:37-77) ----
     def energies(self):

@@ -39,7 +39,8 @@ def load_b200():
     sig = {
         "vpic_b200_init": (i, [i, i, i]), "vpic_b200_finalize": (None, []), "vpic_b200_trim": (None, []),
         "vpic_b200_set_world": (None, [i, i]), "vpic_b200_comm_unique_id": (i, [_P, i]),
-        "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []), "vpic_b200_comm_transport": (i, []), "vpic_b200_sort_violations": (C.c_longlong, [_P]),
+        "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []),
+        "vpic_b200_comm_mailbox_record": (i, [_P, i]), "vpic_b200_comm_init_handles": (None, [_P, i]), "vpic_b200_comm_transport": (i, []), "vpic_b200_sort_violations": (C.c_longlong, [_P]),
         "vpic_b200_set_coherence": (None, [i]), "vpic_b200_set_deposit_mode": (None, [i]),
         "vpic_b200_set_reference_pipelines": (None, [i]),
         "vpic_b200_abi_check": (i, [i] * 6),
@@ -48,6 +49,7 @@ def load_b200():
         "vpic_b200_launch_count": (C.c_longlong, []), "vpic_b200_transfer_bytes": (None, [C.POINTER(C.c_longlong)]), "vpic_b200_stream": (_P, []),
         "vpic_b200_device_ptr": (_P, [_P, i]),
         "vpic_b200_load_uniform_maxwellian": (None, [_P, i, f, f, C.c_uint64]),
+        "vpic_b200_drop_unprocessed_movers": (i, [_P, _P]),
         "vpic_b200_energy_f_noalloc": (i, [_P, _P, i, i, i, C.POINTER(f), d, _P]),
         "vpic_b200_new_grid": (_P, []), "vpic_b200_delete_grid": (None, [_P]),
         "vpic_b200_partition_periodic_box": (None, [_P] + [d] * 6 + [i] * 6),
@@ -106,6 +108,10 @@ class Backend:
             fn = getattr(lib, prefix + name)
             fn.restype, fn.argtypes = res, args
             setattr(self, name, fn)
+        if kind != "b200":         # host function of the reference (rho_p.cc:125-171), used by the driver's drop loop
+            fn = getattr(lib, prefix + "accumulate_rhob")
+            fn.restype, fn.argtypes = None, [_P, _P, _P, C.c_float]
+            self.accumulate_rhob = fn
         if kind == "oracle":
             for name, (res, args) in _FIELD_FUNCS.items():
                 fn = getattr(lib, prefix + name)
