@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-yee", action="store_true")
+    ap.add_argument("--no-c1", action="store_true", help="skip the BASELINE configs[0] leg (32^3 cells, 2 x 16 ppc, 100 steps)")
+    ap.add_argument("--no-decks", action="store_true", help="skip the deck_e2e leg (reference decks, RESIDENT + FAST under the reference's own driver)")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the N-rank parity check against the N-rank oracle")
     ap.add_argument("--breakdown", type=int, default=0, metavar="STEPS",
                     help="after the timed region: STEPS more steps with a device synchronize around every entry point, "
                          "reported as breakdown_ms (per step, this rank)")
@@ -246,15 +249,24 @@ def run_b200(args):
         out["breakdown_ms"] = breakdown(torch, sim, be, args.breakdown)
     free_sim(L, sim)
 
-    if rank == 0 and not args.no_yee:      # single-GPU sub-benchmark: a 1x1x1 topology for the duration
-        L.vpic_b200_set_world(0, 1)
+    if not args.no_yee:                    # every rank: 256^3 cells per GPU, slabs along x, ghost planes exchanged every call
+        out["yee"] = bench_yee(torch, L, be, host, stream, peak, rank=rank, world=world, barrier=barrier, dist=dist)
+    if not args.no_c1 and world == 1:
+        out["c1"] = bench_c1(torch, L, be, host, stream)
+    if world > 1 and not args.no_parity:
         try:
-            out["yee"] = bench_yee(torch, L, be, host, stream, peak)
-        finally:
-            L.vpic_b200_set_world(rank, world)
+            out["multi_rank_parity"] = multi_rank_parity(torch, dist, L, rank, world)
+        except Exception as e:
+            out["multi_rank_parity"] = {"ranks": world, "ok": False, "error": repr(e)}
+        L.vpic_b200_set_coherence(1)
     out["e2e"] = None
     if not args.no_e2e:                    # every rank: the decomposed problem with host arrays
         out["e2e"] = bench_e2e(torch, L, be, host, stream, args, rank, world, dist)
+    if rank == 0 and world == 1 and not args.no_decks:
+        try:
+            out["deck_e2e"] = deck_e2e()
+        except Exception as e:
+            out["deck_e2e"] = {"error": repr(e)}
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
             out["cpu_baseline"] = cpu_baseline(args)
@@ -297,17 +309,20 @@ def free_sim(L, sim):
     L.delete_field_array(sim.fa); L.vpic_b200_delete_grid(sim.g)
 
 
-def bench_yee(torch, L, be, host, stream, peak, n=(256, 256, 256), steps=50):
-    """BASELINE configs[1]: vacuum EM wave, periodic 256^3, field kernels only."""
+def bench_yee(torch, L, be, host, stream, peak, n=(256, 256, 256), steps=50, rank=0, world=1, barrier=lambda: None, dist=None):
+    """BASELINE configs[1]: vacuum EM wave, periodic, field kernels only -- 256^3 cells PER GPU, slabs along x
+    (sample/bench/fdtd_scaling's shape): at N > 1 every advance_e exchanges its tangential-B ghost planes with
+    both neighbours.  cell_updates_per_s is the whole job's (all ranks' cells / max-over-ranks time)."""
     import numpy as np
     from vpic_b200 import Simulation
     s = Simulation(be, host)
-    s.define_grid("periodic", (0, 0, 0), tuple(float(k) for k in n), n, dt=float(np.float32(0.95 / np.sqrt(3.0))))
+    gn = (n[0] * world, n[1], n[2])
+    s.define_grid("periodic", (0, 0, 0), tuple(float(k) for k in gn), gn, topo=(world, 1, 1), dt=float(np.float32(0.95 / np.sqrt(3.0))))
     s.define_fields(damp=0.0)
     f = s.fields(); g = s.grid_struct(s.g)
-    x = (np.arange(g.nv) % (g.nx + 2)).astype(np.float64)
-    f["ey"] = np.sin(2 * np.pi * (x - 1) / n[0]).astype(np.float32)
-    f["cbz"] = np.sin(2 * np.pi * (x - 0.5) / n[0]).astype(np.float32)
+    x = (np.arange(g.nv) % (g.nx + 2)).astype(np.float64) + rank * n[0]
+    f["ey"] = np.sin(2 * np.pi * (x - 1) / gn[0]).astype(np.float32)
+    f["cbz"] = np.sin(2 * np.pi * (x - 0.5) / gn[0]).astype(np.float32)
     ncell = n[0] * n[1] * n[2]
     res = {}
     for name, fn, bpc in (("advance_b", lambda: be.advance_b(s.fa, 0.5), 36.0),
@@ -315,18 +330,156 @@ def bench_yee(torch, L, be, host, stream, peak, n=(256, 256, 256), steps=50):
                           ("field_step", lambda: (be.advance_b(s.fa, 0.5), be.advance_e(s.fa, 1.0), be.advance_b(s.fa, 0.5)), 144.0)):
         for _ in range(3):
             fn()
-        torch.cuda.synchronize()
+        barrier(); torch.cuda.synchronize()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(steps):
             fn()
-        e1.record(stream); torch.cuda.synchronize()
+        e1.record(stream); torch.cuda.synchronize(); barrier()
         ms = e0.elapsed_time(e1) / steps
-        res[name] = {"cell_updates_per_s": ncell / (ms * 1e-3), "ms": ms, "GB/s": ncell * bpc / (ms * 1e-3) / 1e9,
+        if dist is not None:
+            t = torch.tensor([ms], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = t.item()
+        res[name] = {"cell_updates_per_s": world * ncell / (ms * 1e-3), "ms": ms, "GB/s_per_gpu": ncell * bpc / (ms * 1e-3) / 1e9,
                      "frac_of_hbm_peak": ncell * bpc / (ms * 1e-3) / 1e9 / peak, "bytes_per_cell": bpc}
-    res["workload"] = "vacuum, periodic %dx%dx%d (BASELINE configs[1])" % n
+    res["workload"] = "vacuum, periodic, %dx%dx%d cells per GPU x %d GPU(s), slabs along x (BASELINE configs[1] per GPU)" % (n + (world,))
+    res["n_gpus"] = world
     free_sim(L, s)
     return res
+
+
+def bench_c1(torch, L, be, host, stream, steps=100):
+    """BASELINE configs[0]: 32^3 cells, 2 species x 16 ppc, 100 steps, sort every 20.  One million
+    particles: the step is launch- and latency-bound, so the launches per step are reported next to the rate."""
+    import numpy as np
+    sim, sps = uniform_plasma(be, host, (32, 32, 32), 16, 20)
+    for k, (sp, vth, w) in enumerate(sps):
+        L.vpic_b200_load_uniform_maxwellian(sp, 16, vth, w, 77 + k)
+    sim.initialize()
+    np_total = sum(sim.sp_struct(sp).np for sp, _, _ in sps)
+    for _ in range(5):
+        sim.advance()
+    ms, launches = timed_steps(torch, sim, L, stream, steps, lambda: None)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sim.advance()
+    torch.cuda.synchronize()
+    wall = (time.perf_counter() - t0) / steps * 1e3
+    res = {"workload": "uniform plasma, periodic 32x32x32 cells, 2 species x 16 ppc, sort every 20 (BASELINE configs[0]), state resident in HBM",
+           "particles": np_total, "steps": steps, "pushes_per_s": np_total * steps / (ms * 1e-3), "ms_per_step_device": ms / steps,
+           "ms_per_step_wall": wall, "gpu_launches_per_step": launches / steps,
+           "bytes_per_push": 64.0 + 176.0 / 16, "note": "launch / host-round-trip bound: compare ms_per_step with gpu_launches_per_step"}
+    free_sim(L, sim)
+    return res
+
+
+def multi_rank_parity(torch, dist, L, rank, world):
+    """N > 1 only, outside every timed region (like cpu_baseline): the CUDA library on the N GPUs of this job
+    against the N-rank CPU oracle (the oracle is pinned bit for bit to the reference running on N ranks,
+    tests/multi_rank_ref_check.py), small seeded problems, per-step differential: np, voxel indices, particle
+    order and particle bits identical on every rank; fields / currents / rho within 5e-5 of the array maximum;
+    energies to 1e-6.  1-D slabs along x, y, z with periodic / absorbing / metal walls and, at 4 / 8 ranks, the
+    (2,2,1) ... (2,2,2) bricks.  The checker code is tests/multi_rank_check.py (same as the pytest suite)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import multi_rank_check as M
+    from oracle import harness as H
+    gloo = dist.new_group(backend="gloo")
+    cases = M.case_list(world)
+    ok, failed, steps = True, [], 4
+    t0 = time.perf_counter()
+    for kind, gn, topo in cases:
+        M.LOCALISED_LN = tuple(gn[a] // topo[a] for a in range(3))
+        H.set_world(rank, world)
+        so, origin, ln = M.build(H.oracle_backend(), kind, gn, topo, rank, 6, 40)
+        H.install_gloo_exchange(so, group=gloo)
+        good = M.check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=gloo)
+        flag = torch.tensor([1 if good else 0]); dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=gloo)
+        if not flag.item():
+            ok = False; failed.append(f"{kind} {gn} {topo}")
+        dist.barrier(group=gloo)
+    H.remove_exchange()
+    return {"ranks": world, "cases": len(cases), "steps_per_case": steps, "ok": ok, "failed": failed,
+            "topologies": [list(t) for _, _, t in cases], "seconds": round(time.perf_counter() - t0, 1),
+            "transport": "put (NVLink peer-memory mailboxes)" if L.vpic_b200_comm_transport() else "ncclSend/ncclRecv",
+            "criteria": "np, voxel indices, particle order and bits identical; fields / jf / rho <= 5e-5 of max per step; energies 1e-6"}
+
+
+DECKS = {   # name: (initial particles, steps, what)
+    "harris_c3": (26214400, 24, "sample/harris at BASELINE configs[2]'s size: 512x1x256 cells, 2 species x 100 ppc, PEC / reflecting x walls, "
+                                "div-clean + field / hydro dumps every 12 steps"),
+    "lpi_c5": (53968896, 20, "sample/lpi_2d_F6_test at BASELINE configs[4]'s size: 96x1x549 cells, 512 ppc per species, laser injection, "
+                             "absorbing field walls, maxwellian_reflux particle walls, dumps every 10 steps"),
+}
+
+
+def profile_table(text):
+    """The reference's own TIC/TOC table (src/util/profile/profile.c:12-60): the LAST table of the log, cumulative
+    column -> {stage: (seconds, calls)}."""
+    rows = {}
+    for line in text.splitlines():
+        parts = line.split("|")
+        if len(parts) == 3 and "%" in parts[2]:
+            f = parts[2].split()
+            try:
+                rows[parts[0].strip()] = (float(f[1]), float(f[2]))
+            except (IndexError, ValueError):
+                pass
+    return rows
+
+
+def deck_e2e():
+    """What a user of the reference gets: the reference's OWN program (deck/main.cc + vpic_simulation + the deck) with
+    libvpic_b200.so linked ahead of the reference library, RESIDENT coherence and the FAST deposit, against the same
+    deck on the reference's AVX2 build with all host threads.  The decks are the named-size ones of oracle/Makefile
+    (numbers changed by sed); the GPU variants carry three / four inserted sync lines (before a field dump; around the
+    LPI deck's laser injection).  Times come from the program's own TIC/TOC table and from the wall clock of the whole
+    process (host-side particle loading included -- identical on both sides)."""
+    cores = len(os.sched_getaffinity(0))
+    out = {"cpu_threads": cores, "cpu_build": "reference V4+V8 AVX2 (oracle/_ref/libvpic_ref_simd.so)",
+           "gpu_mode": "VPIC_B200_COHERENCE=resident VPIC_B200_DEPOSIT=fast, unmodified reference driver"}
+    import tempfile
+    stages = ("sort_p", "advance_p", "boundary_p", "unload_accumulator", "advance_b", "advance_e", "load_interpolator",
+              "clear_accumulators", "reduce_accumulators", "clear_jf", "synchronize_jf", "clear_rhof", "accumulate_rho_p",
+              "synchronize_rho", "compute_div_e_err", "compute_rms_div_e_err", "clean_div_e", "compute_div_b_err",
+              "compute_rms_div_b_err", "clean_div_b", "synchronize_tang_e_norm_b")
+    for deck, (npart, steps, what) in DECKS.items():
+        gpu_exe = os.path.join(ROOT, "oracle", "_ref", f"deckrun_{deck}_res_b200")
+        cpu_exe = os.path.join(ROOT, "oracle", "_ref", f"deckrun_{deck}_refsimd")
+        if not (os.path.exists(gpu_exe) and os.path.exists(cpu_exe)):
+            out[deck] = {"unavailable": "oracle/_ref executables not built (needs /root/reference at build time)"}
+            continue
+        res = {"workload": what, "particles": npart, "steps": steps}
+        for side, exe, argv, env in (("gpu", gpu_exe, ["--tpp", "1"], dict(VPIC_B200_COHERENCE="resident", VPIC_B200_DEPOSIT="fast", VPIC_B200_REPORT="1")),
+                                     ("cpu", cpu_exe, ["--tpp", str(cores)], {})):
+            with tempfile.TemporaryDirectory() as d:
+                e = dict(os.environ, **env)
+                e["LD_LIBRARY_PATH"] = ":".join(["/usr/local/cuda/lib64", e.get("LD_LIBRARY_PATH", "")])
+                t0 = time.perf_counter()
+                r = subprocess.run([exe] + argv, cwd=d, env=e, capture_output=True, text=True, timeout=1200)
+                wall = time.perf_counter() - t0
+                en = open(os.path.join(d, "energies")).read().splitlines() if os.path.exists(os.path.join(d, "energies")) else []
+            if r.returncode != 0:
+                res[side] = {"error": (r.stderr or r.stdout)[-300:]}
+                continue
+            tab = profile_table(r.stdout + r.stderr)
+            ap = tab.get("advance_p", (0.0, 0.0))
+            # our entry points return before their kernels finish (the time surfaces in the next call that
+            # synchronises), so only sums over stages are meaningful on the GPU side: the whole table = the step
+            # loop including user_diagnostics (dumps, and on the GPU the syncs before them)
+            loop = sum(v[0] for v in tab.values())
+            compute = sum(v[0] for k, v in tab.items() if k in stages)
+            res[side] = {"wall_s": round(wall, 2), "advance_p_s": ap[0], "advance_p_calls": ap[1],
+                         "pushes_per_s_advance_p": npart * steps / ap[0] if ap[0] > 0 else None,
+                         "step_stages_s": round(loop, 4), "pushes_per_s_step_stages": npart * steps / loop if loop > 0 else None,
+                         "hot_path_stages_s": round(compute, 4),
+                         "last_energies_line": en[-1] if en else None}
+        g, c = res.get("gpu", {}), res.get("cpu", {})
+        if g.get("step_stages_s") and c.get("step_stages_s"):
+            res["speedup_step_stages"] = round(c["step_stages_s"] / g["step_stages_s"], 2)
+            res["speedup_wall"] = round(c["wall_s"] / g["wall_s"], 2)
+            if g.get("hot_path_stages_s"):
+                res["speedup_hot_path_stages"] = round(c["hot_path_stages_s"] / g["hot_path_stages_s"], 2)
+        out[deck] = res
+    return out
 
 
 def bench_e2e(torch, L, be, host, stream, args, rank=0, world=1, dist=None, steps=3):

@@ -18,6 +18,7 @@ from vpic_b200.lib import Backend, _load       # noqa: E402
 ORACLE_LIB = os.path.join(_HERE, "liboracle.so")
 REF_SCALAR = os.path.join(_HERE, "_ref", "libvpic_ref_scalar.so")
 REF_SIMD = os.path.join(_HERE, "_ref", "libvpic_ref_simd.so")
+REF_SIMD512 = os.path.join(_HERE, "_ref", "libvpic_ref_simd512.so")      # V4 AVX2 + V16 AVX-512 (arch/intel/v16-knl flags)
 _P = C.c_void_p
 
 
@@ -34,16 +35,20 @@ def oracle_backend():
     return Backend("oracle", L, prefix="orc_")
 
 
+def _ref_path(simd):
+    return REF_SIMD512 if simd == "simd512" else REF_SIMD if simd else REF_SCALAR
+
+
 def have_ref(simd=False):
-    return os.path.exists(REF_SIMD if simd else REF_SCALAR)
+    return os.path.exists(_ref_path(simd))
 
 
 _ref_booted = {}
 
 
 def ref_backend(simd=False, tpp=1):
-    """The compiled reference.  One flavour (scalar or simd) per process."""
-    path = REF_SIMD if simd else REF_SCALAR
+    """The compiled reference.  One flavour (scalar, simd = V4+V8 AVX2, "simd512" = V4 AVX2 + V16 AVX-512) per process."""
+    path = _ref_path(simd)
     L = _load(path)
     if path not in _ref_booted:
         L.refshim_boot.argtypes = [C.c_int]
@@ -141,7 +146,7 @@ _ALLSUM_PROTO = C.CFUNCTYPE(None, C.POINTER(C.c_double), C.c_int)
 _exch_keepalive = []
 
 
-def install_gloo_exchange(sim):
+def install_gloo_exchange(sim, group=None):
     """Route the oracle's face / particle messages of `sim`'s grid through
     torch.distributed (gloo, CPU tensors).  A message sent out of the -X face
     carries tag 2*X and arrives on the receiver's +X side, and vice versa, like
@@ -171,16 +176,16 @@ def install_gloo_exchange(sim):
             return
         reqs = []
         if slo and sb[0] > 0:
-            reqs.append(dist.isend(view(slo, sb[0]).clone(), rank_lo[X], tag=2 * X))
+            reqs.append(dist.isend(view(slo, sb[0]).clone(), rank_lo[X], tag=2 * X, group=group))
         if shi and sb[1] > 0:
-            reqs.append(dist.isend(view(shi, sb[1]).clone(), rank_hi[X], tag=2 * X + 1))
+            reqs.append(dist.isend(view(shi, sb[1]).clone(), rank_hi[X], tag=2 * X + 1, group=group))
         bufs = []
         if rhi and rb[1] > 0:
             t = torch.empty(rb[1], dtype=torch.uint8); bufs.append((rhi, t))
-            reqs.append(dist.irecv(t, rank_hi[X], tag=2 * X))
+            reqs.append(dist.irecv(t, rank_hi[X], tag=2 * X, group=group))
         if rlo and rb[0] > 0:
             t = torch.empty(rb[0], dtype=torch.uint8); bufs.append((rlo, t))
-            reqs.append(dist.irecv(t, rank_lo[X], tag=2 * X + 1))
+            reqs.append(dist.irecv(t, rank_lo[X], tag=2 * X + 1, group=group))
         for r in reqs:
             r.wait()
         for ptr, t in bufs:
@@ -194,7 +199,7 @@ def install_gloo_exchange(sim):
 
     def allsum(v, n):                                   # mp_allsum_d of the rms / mismatch diagnostics
         t = torch.from_numpy(np.ctypeslib.as_array(v, shape=(n,)).copy())
-        dist.all_reduce(t)
+        dist.all_reduce(t, group=group)
         for k in range(n):
             v[k] = float(t[k])
 

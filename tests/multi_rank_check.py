@@ -265,7 +265,7 @@ def check_oracle(H, so, origin, ln, kind, gn, topo, rank, world, steps, dist):
     return ok
 
 
-def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch):
+def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None):
     from vpic_b200 import load_b200, b200_backend
     from common import same_bits
     L = load_b200()
@@ -278,14 +278,14 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch):
             rec = (C.c_char * 80)()
             L.vpic_b200_comm_mailbox_record(rec, 80)
             recs = [None] * world
-            dist.all_gather_object(recs, bytes(rec))
+            dist.all_gather_object(recs, bytes(rec), group=group)
             L.vpic_b200_comm_init_handles(b"".join(recs), 80)
         else:
             buf = (C.c_char * 128)()
             if rank == 0:
                 L.vpic_b200_comm_unique_id(buf, 128)
             box = [bytes(buf)]
-            dist.broadcast_object_list(box, src=0)
+            dist.broadcast_object_list(box, src=0, group=group)
             L.vpic_b200_comm_init(box[0], 128)
     want = 0 if os.environ.get("VPIC_B200_TRANSPORT") == "nccl" else 1
     if L.vpic_b200_comm_transport() != want:
@@ -330,7 +330,7 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch):
             if not close(hg[k], ho[k], 2e-5):
                 print(f"rank {rank} {kind} {topo}: hydro {k} differs"); ok = False
     eo = np.array(so.energies()); eg = np.array(sg.energies())
-    t = torch.from_numpy(eo.copy()); dist.all_reduce(t)
+    t = torch.from_numpy(eo.copy()); dist.all_reduce(t, group=group)
     if not np.allclose(eg, t.numpy(), rtol=1e-6):
         print(f"rank {rank} {kind} {topo}: energies differ", eg, t.numpy()); ok = False
     return ok

@@ -201,7 +201,10 @@ void synchronize_hydro_array( vpb_hydro_array_t * ha ) {
     if( from_lo ) launch_plane( m, HO_FOLD, X, 1,       lw, rw, const_cast<float *>( from_lo ) );
     if( from_hi ) launch_plane( m, HO_FOLD, X, n3[X]+1, lw, rw, const_cast<float *>( from_hi ) );
   }
-  finish_write( m );
+  // A hydro array exists for the dump that follows (dump.cc:227-229 reads ha->h right after
+  // this call): the host copy is made current in RESIDENT mode as well, so that unmodified
+  // dump code works without a vpic_b200_sync_to_host.
+  mark_dev_written( m ); to_host( m );
 }
 
 // Standalone construction (a reference build keeps its own new_hydro_array /
