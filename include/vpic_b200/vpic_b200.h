@@ -98,8 +98,16 @@ void vpic_b200_delete_hydro_array( vpb_hydro_array_t * ha );
 /* ======================= Part 2: control surface ========================== */
 
 enum { VPB_COHERENCE_STRICT = 0,   /* every call: host structs in, host structs out  */
-       VPB_COHERENCE_RESIDENT = 1  /* state lives on the device between calls; the
-                                      host syncs explicitly with the calls below     */ };
+       VPB_COHERENCE_RESIDENT = 1, /* state lives on the device between calls; the
+                                      host syncs explicitly with the calls below     */
+       VPB_COHERENCE_TRACKED = 2   /* STRICT, minus the uploads of arrays the host program has not
+                                      written since the library last saw them: after every upload /
+                                      download the array's pages are write-protected and a store
+                                      into them marks the array dirty (SIGSEGV handler, mprotect).
+                                      The host copy stays current after every call exactly as in
+                                      STRICT mode.  Not for programs that fill their arrays with
+                                      read()/fread(): system calls fail with EFAULT on protected
+                                      pages instead of faulting (vpb_track.cu).                  */ };
 enum { VPB_DEPOSIT_FAST = 0,       /* warp-reduced + atomics, FMA allowed            */
        VPB_DEPOSIT_PARITY = 1      /* reference summation order, bit-exact currents  */ };
 

@@ -201,3 +201,37 @@ def test_reference_decks_on_n_ranks_every_output_file_identical(tmp_path, deck, 
            if not os.path.exists(os.path.join(tmp_path, n))
            or hashlib.sha256(open(os.path.join(tmp_path, n), "rb").read()).hexdigest() != h]
     assert not bad, (len(bad), bad[:10])
+
+
+def test_reference_harris_deck_checkpoint_restore_continues_identically(tmp_path):
+    """N3: checkpoint -> --restore with the library underneath (deck/main.cc:71-91, the per-object restore
+    functions of src/species_advance/species_advance.c:16-41 and our vpic_b200_checkpt_fa / vpic_b200_restore_fa
+    for the field array, sfa.c:162-188).  Run 1 is the harris drop-in; it writes checkpt.<step>.0 every 24
+    steps.  Run 2 is a NEW process started with --restore checkpt.240 in an empty directory: the reference's
+    checkpoint service rebuilds every host object (our kernel table is restored by symbol name), the device
+    mirrors are rebuilt from them on first use, and the run continues to step 480.  Every dump file it writes
+    (steps 264 ... 480) and its energies lines must equal the uninterrupted CPU reference run's."""
+    import hashlib
+    import json
+    import shutil
+    exe = os.path.join(ROOT, "oracle", "_ref", "deckrun_harris_b200")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/deckrun_harris_b200 not built (needs /root/reference at build time)")
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "harris_outputs.json")))
+    env = deck_env(VPIC_B200_DEPOSIT="parity", VPIC_B200_COHERENCE="strict")
+    a, b = tmp_path / "run1", tmp_path / "run2"
+    a.mkdir(); b.mkdir()
+    r = subprocess.run([exe, "--tpp", "1"], cwd=a, env=env, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stderr[-2500:]
+    assert (a / "checkpt.240.0").exists()
+    shutil.copy(a / "checkpt.240.0", b / "checkpt.240.0")
+    r = subprocess.run([exe, "--tpp", "1", "--restore", "checkpt.240"], cwd=b, env=env, capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-2500:])
+    launches(r.stderr, 200 * 20)
+    later = {n: h for n, h in gold["files"].items() if n != "energies" and os.path.exists(b / n)}
+    assert len(later) >= 40, sorted(os.listdir(b))[:20]                    # 9 dump steps x (field + 2 hydro + 2 particle) files
+    bad = [n for n, h in later.items() if hashlib.sha256(open(b / n, "rb").read()).hexdigest() != h]
+    assert not bad, bad[:10]
+    cont = [l for l in open(b / "energies").read().splitlines() if l and not l.startswith("%")]
+    want = [l for l in gold["energies"].splitlines() if l and not l.startswith("%") and int(l.split()[0]) > 240]
+    assert cont and cont == want[-len(cont):] and len(cont) >= len(want) - 1

@@ -579,3 +579,135 @@ def test_unprocessed_movers_are_dropped_like_the_reference(gpu):
         assert close(sg.fields()["rhob"], so.fields()["rhob"], 1e-5)
         sg.fields()[:] = so.fields(); sg.interpolators()[:] = so.interpolators()
     assert dropped > 0
+
+
+@pytest.mark.parametrize("kind", ["periodic", "absorbing"])
+def test_lazy_sort_resident_mode_bit_exact_per_step(gpu, kind):
+    """RESIDENT coherence + FAST deposit: sort_p only orders indices (d_perm), the following advance_p
+    gathers through them while it pushes and writes the species' other buffer, and the advance_p before a
+    sort leaves the voxel keys for it.  Per-step differential against the oracle: particle order and bits,
+    np, partition[] after every sort; fields re-synchronised each step (FAST currents are tolerance-level)."""
+    L = load_b200()
+    so, sg = pair(gpu, kind=kind, n=(10, 7, 6), sort_interval=2, ppc=20, vth=0.3)
+    nv = so.grid_struct(so.g).nv
+    L.vpic_b200_set_coherence(1)
+    try:
+        so.initialize(); sg.initialize()
+        for step in range(7):
+            sorted_now = so.grid_struct(so.g).step % 2 == 0
+            so.advance(); sg.advance()
+            for obj in [sg.fa, sg.ia] + sg.species:
+                L.vpic_b200_sync_to_host(obj)
+            for a, b in zip(so.species, sg.species):
+                assert so.sp_struct(a).np == sg.sp_struct(b).np, step
+                assert same_bits(sg.particles(b), so.particles(a)), (kind, step)
+                if sorted_now and kind == "periodic":     # (boundary_p moved particles since: the device partition is stale and stays on the device)
+                    assert np.array_equal(sg.partition(b)[:nv], so.partition(a)[:nv]), (kind, step)
+            for k in ("ex", "ey", "ez", "cbx", "cby", "cbz"):
+                assert close(sg.fields()[k], so.fields()[k], 1e-4)
+            sg.fields()[:] = so.fields(); sg.interpolators()[:] = so.interpolators()
+            L.vpic_b200_sync_from_host(sg.fa); L.vpic_b200_sync_from_host(sg.ia)
+    finally:
+        L.vpic_b200_set_coherence(0)
+
+
+def test_lazy_sort_is_carried_out_when_something_else_reads_the_particles(gpu):
+    """sort_p in RESIDENT mode followed by a host read (no advance_p in between): the pending
+    permutation is applied before the download; order and partition[] as the oracle's."""
+    L = load_b200()
+    so, sg = pair(gpu, kind="periodic", n=(9, 8, 5), ppc=24)
+    nv = so.grid_struct(so.g).nv
+    L.vpic_b200_set_coherence(1)
+    try:
+        for a, b in zip(so.species, sg.species):
+            L.vpic_b200_sync_from_host(b)
+            so.be.sort_p(a); sg.be.sort_p(b)
+            ep = sg.be.energy_p(b, sg.ia)               # reads the particles on the device: sorted order or not, same sum terms
+            L.vpic_b200_sync_to_host(b)
+            assert same_bits(sg.particles(b), so.particles(a))
+            assert np.array_equal(sg.partition(b)[:nv], so.partition(a)[:nv])
+            assert L.vpic_b200_sort_violations(b) == 0
+            assert ep >= 0
+            # second sort of the same species after every particle was given a random voxel, with a removed
+            # tail and a crowded voxel
+            rng = np.random.default_rng(3)
+            for s, x in ((so, a), (sg, b)):
+                p = s.particles(x)
+                p["i"][:] = rng.permutation(p["i"]) if s is so else so.particles(a)["i"]
+                p["i"][: len(p) // 5] = p["i"][0]
+                s.sp_struct(x).np = len(p) - 37
+            L.vpic_b200_sync_from_host(b)
+            so.be.sort_p(a); sg.be.sort_p(b)
+            L.vpic_b200_sync_to_host(b)
+            assert same_bits(sg.particles(b), so.particles(a))
+            assert np.array_equal(sg.partition(b)[:nv], so.partition(a)[:nv])
+            assert L.vpic_b200_sort_violations(b) == 0
+    finally:
+        L.vpic_b200_set_coherence(0)
+
+
+def test_tracked_coherence_equals_strict_and_skips_clean_uploads(gpu):
+    """TRACKED = STRICT minus the uploads of host arrays the host program did not write (write-protected pages,
+    a store marks the array dirty).  Same deterministic run (PARITY deposit) in both modes with host writes to
+    fields and particles between steps: identical bits at the end, and far fewer bytes uploaded."""
+    L = load_b200()
+    import ctypes as C
+
+    def run(mode):
+        L.vpic_b200_set_coherence(mode)
+        L.vpic_b200_set_deposit_mode(1)
+        try:
+            s = make_sim(gpu, None, kind="periodic", n=(40, 36, 30), ppc=12, sort_interval=3)
+            for k, sp in enumerate(s.species):
+                random_particles(s, sp, 12, 0.2, 300 + k)
+            s.fields()[:] = random_fields(s, 9)
+            s.initialize()
+            b0 = (C.c_longlong * 2)(); L.vpic_b200_transfer_bytes(b0)
+            for step in range(6):
+                s.advance()
+                if step == 1:                                   # the host program edits its arrays in place
+                    s.fields()["ex"][1000:1400] += np.float32(0.01)
+                    s.particles(s.species[0])["ux"][7::1001] += np.float32(0.05)
+                if step == 3:
+                    s.fields()["cbz"][5000:5100] *= np.float32(1.5)
+                    s.particles(s.species[1])["dz"][11::977] = np.float32(0.25)
+            b1 = (C.c_longlong * 2)(); L.vpic_b200_transfer_bytes(b1)
+            out = (s.fields().copy(), [s.particles(sp).copy() for sp in s.species], s.energies())
+            for sp in s.species:
+                L.vpic_b200_delete_species(sp)
+            L.vpic_b200_delete_interpolator_array(s.ia); L.vpic_b200_delete_accumulator_array(s.aa)
+            L.delete_field_array(s.fa)
+            return out, b1[0] - b0[0], b1[1] - b0[1]
+        finally:
+            L.vpic_b200_set_coherence(0); L.vpic_b200_set_deposit_mode(0)
+
+    (f0, p0, e0), up0, down0 = run(0)
+    (f1, p1, e1), up1, down1 = run(2)
+    assert same_bits(f1, f0)
+    for a, b in zip(p0, p1):
+        assert same_bits(b, a)
+    assert e1 == e0
+    assert down1 == down0                      # the host copy is kept current exactly as in STRICT mode
+    assert up1 < 0.35 * up0, (up0, up1)       # ... but only what the host wrote goes up again
+
+
+def test_tracked_coherence_streamed_advance_p(gpu):
+    """The chunk-pipelined advance_p of host-resident particles (> 8M) in TRACKED mode: the second call finds
+    the array clean and runs only the download half; a host write in between is picked up."""
+    L = load_b200()
+    so, sg = pair(gpu, kind="periodic", n=(64, 64, 50), ppc=44, max_np_factor=1.05)
+    L.vpic_b200_set_coherence(2)
+    try:
+        for rnd in range(3):
+            if rnd == 2:                                        # host edit between calls
+                for s in (so, sg):
+                    s.particles(s.species[0])["uy"][3::100003] = np.float32(-0.125)
+            for s in (so, sg):
+                s.be.load_interpolator_array(s.ia, s.fa)
+                s.be.clear_accumulator_array(s.aa)
+                for sp in s.species_in_list_order():
+                    s.be.advance_p(sp, s.aa, s.ia)
+            for a, b in zip(so.species, sg.species):
+                assert same_bits(sg.particles(b), so.particles(a)), rnd
+    finally:
+        L.vpic_b200_set_coherence(0)

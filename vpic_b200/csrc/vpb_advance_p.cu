@@ -45,6 +45,12 @@ namespace vpb {
 #ifndef VPB_AP_COMMIT_AT_TILE_END
 #define VPB_AP_COMMIT_AT_TILE_END 0
 #endif
+#ifndef VPB_AP_REC
+#define VPB_AP_REC 0          // N > 0: the coefficient records of N consecutive voxels around the tile travel with the tile's bulk copy
+#endif
+#ifndef VPB_AP_PREF
+#define VPB_AP_PREF 0         // 1: the first coefficient record of the lane's NEXT tile is requested at the end of this tile
+#endif
 #ifndef VPB_HINT_STREAM
 #define VPB_HINT_STREAM 0     // 1: evict_first L2 policy on the tile's bulk load and bulk store
 #endif
@@ -63,6 +69,13 @@ struct __align__(128) WarpTile {
   // queue of particles that left their voxel: remaining displacement + index
   // (position, voxel, momentum and weight are still in the particle's slot)
   float4 q[AP_QCAP];                    // dispx, dispy, dispz, index relative to the launch's first particle
+#if VPB_AP_REC
+  // Interpolator records of the voxels [vwin, vwin+VPB_AP_REC) -- one voxel before the tile's first particle's
+  // and the ones that follow: a cell-sorted tile of 256 particles lives in ~9 consecutive voxels.  They arrive
+  // with the tile (second bulk copy on the same mbarrier), so a lane that changes voxel inside the window
+  // reads shared memory instead of waiting for an L2 / DRAM gather in the middle of its run.
+  float4 rec[VPB_AP_REC*6];
+#endif
   unsigned long long bar[AP_NBUF];      // mbarrier of each buffer's tile load
 };
 
@@ -77,12 +90,14 @@ template< class OnChip >
 __device__ __forceinline__ void drain_crossers( const float4 * __restrict__ queue, OnChip on_chip, int base, int n, int lane,
                                                 vpb_particle_t * __restrict__ p, int idx_base,
                                                 float * __restrict__ acc, vpb_particle_mover_t * __restrict__ pm,
-                                                int max_nm, int * __restrict__ counters, const GridDev & g, float qsp ) {
+                                                int max_nm, int * __restrict__ counters, const GridDev & g, float qsp,
+                                                int * __restrict__ keys = nullptr ) {
   if( lane>=n ) return;
   const int e = base + lane;
   const float4 qe = queue[e];
   const int rel = __float_as_int( qe.w );
   float4 * slot = on_chip( rel );
+  const bool off_chip = !slot;
   if( !slot ) slot = reinterpret_cast<float4 *>( p + rel );
   const float4 r0 = slot[0], r1 = slot[1];
   MoveState ms;
@@ -99,6 +114,7 @@ __device__ __forceinline__ void drain_crossers( const float4 * __restrict__ queu
   } while( status==1 );
   slot[0] = make_float4( ms.dx, ms.dy, ms.dz, __int_as_float( ms.i ) );
   slot[1] = make_float4( ms.ux, ms.uy, ms.uz, r1.w );       // reflections flip a momentum component
+  if( keys && off_chip ) keys[rel] = ms.i;                  // its tile's keys were written with the tile
   if( status==2 ) {
     const int k = atomicAdd( counters+0, 1 );
     if( k<max_nm ) reinterpret_cast<float4 *>( pm )[k] = make_float4( ms.dispx, ms.dispy, ms.dispz, __int_as_float( idx_base + rel ) );
@@ -113,11 +129,23 @@ constexpr int AP_DRAIN_MIN = VPB_AP_DRAIN_MIN;        // fewer crossers than thi
 
 // p points at the first particle of the range this launch owns (np particles,
 // ntile tiles); idx_base is that particle's index in sp->p (mover indices).
+//
+// GATHER: the launch that follows a lazy sort_p (vpb_sort.cu).  sort_p has only
+// computed the sorted order, perm[d] = index of the particle that belongs in
+// slot d; the tile for slots [t0, t0+cnt) is gathered from src[perm[..]] with
+// 256-bit loads instead of one bulk copy, pushed, and bulk-stored to p[t0..]
+// (the species' other buffer).  The sort's own 64 B per particle copy pass
+// disappears into the push's read and write.
+// KEYS: the launch before a sort_p also leaves every particle's final voxel
+// index in keys[] (4 B per particle), so that sort_p does not have to touch
+// the 32 B particle records to learn the keys.
+template< bool GATHER, bool KEYS >
 __global__ void __launch_bounds__( 32*AP_WARPS, AP_MINBLK )
 k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
              const float * __restrict__ ip, float * __restrict__ acc,
              vpb_particle_mover_t * __restrict__ pm, int max_nm, int * __restrict__ counters,
-             GridDev g, PushCoef c ) {
+             GridDev g, PushCoef c,
+             const vpb_particle_t * __restrict__ src, const int * __restrict__ perm, int * __restrict__ keys ) {
   __shared__ WarpTile s_all[AP_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   WarpTile & S = s_all[warp];
@@ -133,11 +161,22 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   __syncwarp();
 
   // one elected lane starts the bulk copy of a tile into buffer b
+#if VPB_AP_REC
+  int win0 = 0;                                // lane 0: first voxel of the record window of the tile being loaded
+#endif
   auto start_load = [&]( int tile, int b ) {
     const long long t0 = (long long)tile*AP_TILE;
     const uint32_t bytes = (uint32_t)( ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE )*32u;
     const uint32_t bar = smem_u32( &S.bar[b] ), dst = smem_u32( S.tile[b] );
+#if VPB_AP_REC
+    int wn = g.nv - win0; wn = wn<VPB_AP_REC ? wn : VPB_AP_REC;
+    const uint32_t rbytes = (uint32_t)wn*( IP_STRIDE*4u );
+    asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes + rbytes) : "memory" );
+    asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                  :: "r"(smem_u32( S.rec )), "l"(ip + (size_t)win0*IP_STRIDE), "r"(rbytes), "r"(bar) : "memory" );
+#else
     asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
+#endif
 #if VPB_HINT_STREAM
     asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
                   :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar), "l"(l2_policy_evict_first()) : "memory" );
@@ -163,14 +202,46 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   for( int k=0; k<12; k++ ) run[k] = 0.f;
   Interp f = {};
 
+#if VPB_AP_PREF
+  int nvox = -1;                               // voxel of the first particle this lane visits in its next tile
+#endif
+#if VPB_AP_REC
+  int vnext = 0;                               // lane 0: voxel of the first particle of this warp's next tile
+  if( !GATHER && lane==0 ) asm volatile( "ld.global.b32 %0, [%1];" : "=r"(vnext) : "l"( reinterpret_cast<const int *>( p + (long long)gw*AP_TILE ) + 3 ) );
+  int vwin = 0, nwin = 0;                      // the window in shared memory (warp uniform)
+#endif
   if( AP_NBUF>1 && lane==0 ) start_load( gw, 0 );
   for( int tile=gw; tile<ntile; tile+=total_warps ) {
     const long long t0 = (long long)tile*AP_TILE;
     const int cnt = ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE;
-    if( AP_NBUF==1 && lane==0 ) start_load( tile, 0 );
+#if VPB_AP_REC
+    if( !GATHER ) {
+      if( lane==0 ) { win0 = vnext>0 ? vnext-1 : 0; if( win0>=g.nv ) win0 = g.nv-1; }
+      vwin = __shfl_sync( 0xffffffffu, win0, 0 );
+      nwin = g.nv - vwin; nwin = nwin<VPB_AP_REC ? nwin : VPB_AP_REC;
+    }
+#endif
+    if( !GATHER && AP_NBUF==1 && lane==0 ) start_load( tile, 0 );
     float4 * __restrict__ T = S.tile[buf];
     auto on_chip = [&]( int rel ) -> float4 * { return ( rel>=t0 && rel<t0+cnt ) ? &T[ 2*(int)( rel-t0 ) ] : nullptr; };
-    {
+    if( GATHER ) {
+      // 32 consecutive slots per step: coalesced index loads, one 256-bit record load per lane
+      // (consecutive for the particles that did not move since the last sort), conflict-free stores
+      int sidx[AP_K];
+#     pragma unroll
+      for( int i=0; i<AP_K; i++ ) { const int d = 32*i + lane; sidx[i] = d<cnt ? __ldg( perm + t0 + d ) : -1; }
+#     pragma unroll
+      for( int i=0; i<AP_K; i++ ) {
+        const int d = 32*i + lane;
+        if( sidx[i]>=0 ) {
+          float4 a, b;
+          asm volatile( "ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(src + sidx[i]) );
+          T[2*d] = a; T[2*d+1] = b;
+        }
+      }
+      __syncwarp();
+    } else {
       const uint32_t bar = smem_u32( &S.bar[buf] );
       uint32_t ok;
       do {
@@ -190,6 +261,22 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
           start_load( tile+total_warps, buf^1 );
         }
       }
+#if VPB_AP_REC
+      if( !GATHER && k==AP_K/2 && lane==0 && tile+total_warps<ntile )
+        asm volatile( "ld.global.b32 %0, [%1];" : "=r"(vnext) : "l"( reinterpret_cast<const int *>( p + (long long)( tile+total_warps )*AP_TILE ) + 3 ) );
+#endif
+#if VPB_AP_PREF
+      if( !GATHER && k==AP_K/2 ) {
+        // Peek at the voxel of the particle this lane starts its NEXT tile with (4 bytes from global memory,
+        // half a tile ahead of its use).  When this tile is done the lane's coefficient registers are dead, so
+        // that record is requested right then and arrives while the tile is stored and the next one is loaded:
+        // the gather latency of the first particle of a tile (23 % of the ion launches' warp stall samples)
+        // is no longer exposed.
+        const long long tn = (long long)( tile+total_warps )*AP_TILE + lane*AP_K + ( lane & ( AP_K-1 ) );
+        nvox = -1;
+        if( tile+total_warps<ntile && tn<np ) asm volatile( "ld.global.b32 %0, [%1];" : "=r"(nvox) : "l"( reinterpret_cast<const int *>( p + tn ) + 3 ) );
+      }
+#endif
       // rotate the start of each lane's run so the 128-bit shared accesses of a
       // quarter warp spread over the banks
       const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
@@ -200,7 +287,21 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         const float4 r0 = T[2*loc], r1 = T[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
         float ux = r1.x, uy = r1.y, uz = r1.z;
+#if VPB_AP_REC
+        if( ii!=fvox ) {
+          const unsigned rv = (unsigned)( ii - vwin );
+          if( !GATHER && rv<(unsigned)nwin ) {
+            const float4 * q = S.rec + 6*rv;
+            const float4 a = q[0], b = q[1], cc = q[2], d = q[3]; const float2 e = *reinterpret_cast<const float2 *>( q+4 );
+            f.ex = a.x; f.dexdy = a.y; f.dexdz = a.z; f.d2exdydz = a.w; f.ey = b.x; f.deydz = b.y; f.deydx = b.z; f.d2eydzdx = b.w;
+            f.ez = cc.x; f.dezdx = cc.y; f.dezdy = cc.z; f.d2ezdxdy = cc.w; f.cbx = d.x; f.dcbxdx = d.y; f.cby = d.z; f.dcbydy = d.w;
+            f.cbz = e.x; f.dcbzdz = e.y;
+          } else f = load_interp( ip, ii );
+          fvox = ii;
+        }
+#else
         if( ii!=fvox ) { f = load_interp( ip, ii ); fvox = ii; }
+#endif
         if( ii!=cur ) {
           // A particle that strayed into this run since the last sort_p (the
           // lane's next particle is back in the run's voxel) deposits on its
@@ -261,7 +362,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
             __syncwarp();
             n_carry = qn;
           }
-          drain_crossers( S.q, on_chip, qn, 32, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
+          drain_crossers( S.q, on_chip, qn, 32, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp, KEYS ? keys : nullptr );
           __syncwarp();
         }
       }
@@ -277,7 +378,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       while( qn>0 ) {
         const int n = qn<32 ? qn : 32;
         qn -= n;
-        drain_crossers( S.q, on_chip, qn, n, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
+        drain_crossers( S.q, on_chip, qn, n, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp, KEYS ? keys : nullptr );
         __syncwarp();
       }
     }
@@ -289,6 +390,13 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     // commits of the neighbouring lanes.
     if( keepf!=0.f ) { commit_currents( acc, cur, run ); keepf = 0.f; cur = -1; }
 #endif
+    if( KEYS ) {
+      // the voxel index is the 4th word of every record of the tile: 32 consecutive keys per store
+      // (particles that left the domain carry 8*voxel+face and are boundary_p's, which invalidates the keys)
+      __syncwarp();
+#     pragma unroll
+      for( int i=0; i<AP_K; i++ ) { const int d = 32*i + lane; if( d<cnt ) keys[t0+d] = __float_as_int( T[2*d].w ); }
+    }
     n_carry = qn;              // whatever is left rides along; its tile is written back now
     // write the tile back: generic-proxy writes -> async-proxy bulk store
     asm volatile( "fence.proxy.async.shared::cta;" ::: "memory" );
@@ -304,13 +412,16 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
       if( AP_NBUF==1 ) asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer is reused at once
     }
     __syncwarp();
+#if VPB_AP_PREF
+    if( !GATHER && nvox>=0 && nvox!=fvox ) { f = load_interp( ip, nvox ); fvox = nvox; }
+#endif
     if( AP_NBUF>1 ) buf ^= 1;
   }
 
   if( qn>0 ) {                 // all tiles are stored: finish the stragglers in global memory
     if( lane==0 ) asm volatile( "cp.async.bulk.wait_group 0;" ::: "memory" );
     __syncwarp();
-    drain_crossers( S.q, []( int ) -> float4 * { return nullptr; }, 0, qn, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp );
+    drain_crossers( S.q, []( int ) -> float4 * { return nullptr; }, 0, qn, lane, p, idx_base, acc, pm, max_nm, counters, g, c.qsp, KEYS ? keys : nullptr );
   }
   if( keepf!=0.f ) commit_currents( acc, cur, run );
 }
@@ -321,11 +432,13 @@ using namespace vpb;
 
 namespace {
 
+template< bool GATHER, bool KEYS >
 int advance_p_blocks_per_sm() {
   static int blocks_per_sm = 0;
   if( !blocks_per_sm ) {
-    VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
-    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, k_advance_p, 32*AP_WARPS, 0 ) );
+    auto kern = k_advance_p<GATHER,KEYS>;
+    VPB_CUDA( cudaFuncSetAttribute( kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
+    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &blocks_per_sm, kern, 32*AP_WARPS, 0 ) );
     if( blocks_per_sm<1 ) VPB_ERROR( "k_advance_p does not fit on an SM" );
     // Ask for no more shared memory than the resident blocks use (tiles + 1 KB
     // per block that the driver reserves): what is left of the 256 KB is L1
@@ -333,22 +446,31 @@ int advance_p_blocks_per_sm() {
     int pct = (int)( ( (size_t)blocks_per_sm*( sizeof(WarpTile)*AP_WARPS + 1024 )*100 + 228*1024 - 1 )/( 228*1024 ) );
     if( const char * e = getenv( "VPIC_B200_AP_CARVEOUT" ) ) pct = atoi( e );
     if( pct>100 ) pct = 100;
-    VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, pct ) );
+    VPB_CUDA( cudaFuncSetAttribute( kern, cudaFuncAttributePreferredSharedMemoryCarveout, pct ) );
     int check = 0;
-    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &check, k_advance_p, 32*AP_WARPS, 0 ) );
-    if( check<blocks_per_sm ) VPB_CUDA( cudaFuncSetAttribute( k_advance_p, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
+    VPB_CUDA( cudaOccupancyMaxActiveBlocksPerMultiprocessor( &check, kern, 32*AP_WARPS, 0 ) );
+    if( check<blocks_per_sm ) VPB_CUDA( cudaFuncSetAttribute( kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared ) );
   }
   return blocks_per_sm;
 }
 
-void launch_advance_p( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, const PushCoef & c, int first, int count ) {
+// dst: the buffer the pushed particles are written to (= the buffer they are read from unless src / perm
+// say otherwise: the launch after a lazy sort_p); keys: receives the voxel of every particle, or nullptr
+template< bool GATHER, bool KEYS >
+void launch_advance_p_t( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, const PushCoef & c, vpb_particle_t * dst, int first, int count,
+                         const vpb_particle_t * src, const int * perm, int * keys ) {
   Runtime & r = rt();
   const int ntile = div_up( count, AP_TILE );
-  int nblock = r.sm_count*advance_p_blocks_per_sm();
+  int nblock = r.sm_count*advance_p_blocks_per_sm<GATHER,KEYS>();
   if( nblock>div_up( ntile, AP_WARPS ) ) nblock = div_up( ntile, AP_WARPS );
-  k_advance_p<<< nblock, 32*AP_WARPS, 0, r.stream >>>( ms->d_p + first, count, ntile, first, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
-                                                        ms->d_counters, ms->grid->dev, c );
+  k_advance_p<GATHER,KEYS><<< nblock, 32*AP_WARPS, 0, r.stream >>>( dst + first, count, ntile, first, mi->d, ma->d, ms->d_pm, (int)ms->cap_pm,
+                                                                     ms->d_counters, ms->grid->dev, c, src, perm, keys );
   VPB_CHECK_LAUNCH(); r.launches++;
+}
+
+void launch_advance_p( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, const PushCoef & c, int first, int count, int * keys = nullptr ) {
+  if( keys ) launch_advance_p_t<false,true >( ms, ma, mi, c, ms->d_p, first, count, nullptr, nullptr, keys );
+  else       launch_advance_p_t<false,false>( ms, ma, mi, c, ms->d_p, first, count, nullptr, nullptr, nullptr );
 }
 
 // STRICT coherence with host-resident particles: stream the array through the
@@ -362,6 +484,10 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
   vpb_species_t * sp = ms->host;
   if( r.coherence!=VPB_COHERENCE_STRICT || !sp->p || sp->np<2*AP_CHUNK || r.deposit_mode!=VPB_DEPOSIT_FAST ) return false;
   if( ms->dev_valid && !ms->host_valid ) return false;             // the device holds the only current copy
+  // TRACKED coherence: the host program has not written the particles since the library last saw them, so the
+  // device copy is current and only the download half of the pipeline runs
+  const bool clean = ms->dev_valid && ms->np==sp->np && ms->nm==sp->nm && track_clean( sp->p, sizeof(vpb_particle_t)*(size_t)sp->np );
+  if( clean ) materialize_sort( ms );
   ms->np = sp->np;
   pin_host( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
   static std::vector<cudaEvent_t> ev;
@@ -372,9 +498,11 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
   for( int k=0; k<nchunk; k++ ) {
     const int first = k*AP_CHUNK, count = ( ms->np-first<AP_CHUNK ) ? ms->np-first : AP_CHUNK;
     const size_t bytes = sizeof(vpb_particle_t)*(size_t)count;
-    h2d( ms->d_p + first, sp->p + first, bytes, r.copy_stream[0] );
-    VPB_CUDA( cudaEventRecord( ev[2*k], r.copy_stream[0] ) );
-    VPB_CUDA( cudaStreamWaitEvent( r.stream, ev[2*k], 0 ) );
+    if( !clean ) {
+      h2d( ms->d_p + first, sp->p + first, bytes, r.copy_stream[0] );
+      VPB_CUDA( cudaEventRecord( ev[2*k], r.copy_stream[0] ) );
+      VPB_CUDA( cudaStreamWaitEvent( r.stream, ev[2*k], 0 ) );
+    }
     launch_advance_p( ms, ma, mi, c, first, count );
     VPB_CUDA( cudaEventRecord( ev[2*k+1], r.stream ) );
     VPB_CUDA( cudaStreamWaitEvent( r.copy_stream[1], ev[2*k+1], 0 ) );
@@ -382,6 +510,8 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
   }
   VPB_CUDA( cudaStreamSynchronize( r.copy_stream[1] ) );
   ms->dev_valid = true; ms->host_valid = true; ms->partition_dev_valid = false;
+  ms->perm_pending = false; ms->keys_valid = false;
+  track_arm( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
   return true;
 }
 
@@ -405,11 +535,33 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   { const float a = fabsf( c.qdt_2mc ); c.guarded = ( a>=9.31322574615478515625e-10f && a<=1073741824.0f ) ? 0 : 1; }
   VPB_CUDA( cudaMemsetAsync( ms->d_counters, 0, sizeof(int)*2, r.stream ) );
   const bool streamed = advance_p_streamed( ms, ma, mi, c );
+  bool keys_written = false;
   if( !streamed ) {
-    to_device( ms );
+    const bool fast = r.deposit_mode==VPB_DEPOSIT_FAST;
+    to_device( ms, /*keep_lazy_sort=*/fast );
     if( ms->np>0 ) {
-      if( r.deposit_mode==VPB_DEPOSIT_PARITY ) advance_p_parity( ms, ma, mi, c );
-      else launch_advance_p( ms, ma, mi, c, 0, ms->np );
+      if( !fast ) advance_p_parity( ms, ma, mi, c );
+      else {
+        // The launch before a sort_p (advance.cc:25-29 sorts at the top of the step whose number is a multiple of
+        // sort_interval) also writes the voxel keys, so that a lazy sort_p need not read the particle records.
+        int * keys = nullptr;
+        if( r.coherence==VPB_COHERENCE_RESIDENT && sp->sort_interval>0 && ( ( hg->step+1 ) % sp->sort_interval )==0 ) {
+          if( ms->cap_keys<ms->cap_p ) {
+            VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+            if( ms->d_keys ) VPB_CUDA( cudaFree( ms->d_keys ) );
+            VPB_CUDA( cudaMalloc( &ms->d_keys, sizeof(int)*ms->cap_p ) ); ms->cap_keys = ms->cap_p;
+          }
+          keys = ms->d_keys;
+        }
+        if( ms->perm_pending ) {          // sort_p left the order in d_perm: gather through it, write the other buffer
+          vpb_particle_t * dst = sort_spare( ms->cap_p );
+          if( keys ) launch_advance_p_t<true,true >( ms, ma, mi, c, dst, 0, ms->np, ms->d_p, ms->d_perm, keys );
+          else       launch_advance_p_t<true,false>( ms, ma, mi, c, dst, 0, ms->np, ms->d_p, ms->d_perm, nullptr );
+          sort_swap_spare( ms );
+          ms->perm_pending = false;
+        } else launch_advance_p( ms, ma, mi, c, 0, ms->np, keys );
+        keys_written = keys!=nullptr;
+      }
     }
   }
   // The mover count is what the host driver reads next (advance.cc:73-101).
@@ -421,6 +573,7 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   if( ms->nm>1 ) sort_movers_by_index( ms );
   ms->movers_sorted = true;
   if( !streamed ) mark_dev_written( ms );
+  ms->keys_valid = keys_written && ms->nm==0;        // particles on the mover list carry 8*voxel+face, and boundary_p will move things
   mark_dev_written( ma );
   movers_to_host( ms );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ms ); to_host( ma ); }

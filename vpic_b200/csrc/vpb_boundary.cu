@@ -521,7 +521,9 @@ void release_boundary_buffers() {
 // that back-fills their holes, and writes those holes plus what it appends.
 // With the particle arrays living in host memory (STRICT) only those rows
 // travel; the rest of the device copy is left stale and marked invalid.
-struct SparseSpecies { SpeciesMirror * m; int np0, nm0; size_t off; };
+struct SparseSpecies { SpeciesMirror * m; int np0, nm0; size_t off;
+                       bool was_clean;    // TRACKED coherence: the whole device copy was current on entry (the host did not write the array)
+                     };
 
 static void sparse_reserve( size_t rows ) {
   const size_t bytes = rows*( sizeof(vpb_particle_t) + sizeof(int) ) + 256;
@@ -542,6 +544,7 @@ static void sparse_upload( std::vector<SparseSpecies> & ss ) {
   size_t total = 0;
   for( SparseSpecies & s : ss ) {
     SpeciesMirror * m = s.m; const vpb_species_t * sp = m->host;
+    s.was_clean = m->dev_valid && m->np==sp->np && track_clean( sp->p, sizeof(vpb_particle_t)*(size_t)sp->np );
     m->np = sp->np; m->nm = sp->nm; s.np0 = sp->np; s.nm0 = sp->nm; s.off = total; total += (size_t)sp->nm;
     if( m->nm>(int)m->cap_pm ) VPB_ERROR( "species \"%s\": nm=%d exceeds max_nm=%zu", sp->name, m->nm, m->cap_pm );
     if( m->nm>0 && !sp->pm ) VPB_ERROR( "species \"%s\" has movers but no mover array", sp->name );
@@ -600,8 +603,11 @@ static void sparse_download( std::vector<SparseSpecies> & ss ) {
     const int kept = s.np0 - s.nm0;
     for( int k=0; k<s.nm0; k++ ) if( hi[k]<kept ) sp->p[hi[k]] = hr[k];
     sp->np = m->np;
-    // only the rows above are current on the device: the host copy is the valid one
+    // only the rows above are current on the device: the host copy is the valid one ...
     m->host_valid = true; m->dev_valid = false; m->partition_dev_valid = false;
+    // ... unless the device copy was known to be complete on entry (TRACKED): then both are, and the array
+    // (which the patch loop above wrote with CPU stores) is write-protected again
+    if( s.was_clean ) { m->dev_valid = true; m->keys_valid = false; track_arm( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np ); }
   }
 }
 
@@ -654,7 +660,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   std::vector<SparseSpecies> ss;
   for( vpb_species_t * sp=sp_list; sp; sp=sp->next ) {
     SpeciesMirror * m = mirror( sp );
-    if( sparse ) { SparseSpecies s = { m, 0, 0, 0 }; ss.push_back( s ); } else to_device( m );
+    if( sparse ) { SparseSpecies s = { m, 0, 0, 0, false }; ss.push_back( s ); } else to_device( m );
     sps.push_back( m );
     if( sp->id<0 || sp->id>=BND_MAX_SP ) VPB_ERROR( "species id %d is outside the device boundary handler's range", sp->id );
   }

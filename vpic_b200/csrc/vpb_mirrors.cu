@@ -36,12 +36,14 @@ void to_device( InterpMirror * m ) {
   if( !m->host->i ) { if( m->dev_valid ) return; VPB_ERROR( "interpolator array has neither host nor device data" ); }
   static_assert( sizeof(vpb_interpolator_t)==sizeof(float)*IP_HOST, "host interpolator layout" );
   const int nv = m->grid->dev.nv;
+  if( m->dev_valid && track_clean( m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv ) ) return;   // TRACKED: the host did not write it
   if( !m->d_stage ) VPB_CUDA( cudaMalloc( &m->d_stage, sizeof(float)*IP_HOST*(size_t)nv ) );
   pin_host( m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv );
   h2d( m->d_stage, m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv, r.stream );
   k_interp_restride<<< div_up( 5LL*nv, 256 ), 256, 0, r.stream >>>( m->d, IP_STRIDE, m->d_stage, IP_HOST, nv );
   VPB_CHECK_LAUNCH(); r.launches++;
   m->dev_valid = true;
+  track_arm( m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv );
 }
 
 void to_host( InterpMirror * m ) {
@@ -54,6 +56,7 @@ void to_host( InterpMirror * m ) {
   d2h( m->host->i, m->d_stage, sizeof(vpb_interpolator_t)*(size_t)nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
+  track_arm( m->host->i, sizeof(vpb_interpolator_t)*(size_t)nv );
 }
 
 // ---- accumulator -----------------------------------------------------------
@@ -82,9 +85,12 @@ void to_device( AccMirror * m ) {
   if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
   if( !m->host->a ) { if( m->dev_valid ) return; VPB_ERROR( "accumulator array has neither host nor device data" ); }
   static_assert( sizeof(vpb_accumulator_t)==sizeof(float)*ACC_STRIDE, "device accumulator layout == host layout" );
-  pin_host( m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv );
-  h2d( m->d, m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, r.stream );
+  const size_t bytes = sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv;
+  if( m->dev_valid && track_clean( m->host->a, bytes ) ) return;
+  pin_host( m->host->a, bytes );
+  h2d( m->d, m->host->a, bytes, r.stream );
   m->dev_valid = true;
+  track_arm( m->host->a, bytes );
 }
 
 void to_host( AccMirror * m ) {
@@ -93,6 +99,7 @@ void to_host( AccMirror * m ) {
   d2h( m->host->a, m->d, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv, r.stream );
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
   m->host_valid = true;
+  track_arm( m->host->a, sizeof(vpb_accumulator_t)*(size_t)m->grid->dev.nv );
 }
 
 // ---- species ---------------------------------------------------------------
@@ -118,6 +125,7 @@ SpeciesMirror * mirror( vpb_species_t * sp ) {
     vpb_particle_t * n; size_t cap = (size_t)sp->max_np;
     VPB_CUDA( cudaMalloc( &n, sizeof(vpb_particle_t)*cap ) );
     if( m->d_p ) {
+      materialize_sort( m );
       if( m->dev_valid && m->np>0 )
         VPB_CUDA( cudaMemcpyAsync( n, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, cudaMemcpyDeviceToDevice, r.stream ) );
       VPB_CUDA( cudaStreamSynchronize( r.stream ) );
@@ -133,10 +141,19 @@ SpeciesMirror * mirror( vpb_species_t * sp ) {
   return m;
 }
 
-void to_device( SpeciesMirror * m ) {
+void to_device( SpeciesMirror * m, bool keep_lazy_sort ) {
   Runtime & r = rt();
-  if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) return;
+  if( m->dev_valid && ( r.coherence!=VPB_COHERENCE_STRICT || !m->host_valid ) ) {
+    if( !keep_lazy_sort ) materialize_sort( m );
+    return;
+  }
   if( !m->host->p ) { if( m->dev_valid ) return; VPB_ERROR( "species \"%s\" has neither host nor device particles", m->host->name ); }
+  if( m->dev_valid && m->np==m->host->np && m->nm==m->host->nm && m->nm==0 &&
+      track_clean( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->np ) ) {    // TRACKED: the host did not write the particles
+    if( !keep_lazy_sort ) materialize_sort( m );
+    return;
+  }
+  m->perm_pending = false; m->keys_valid = false;      // the host copy replaces whatever the device held
   m->np = m->host->np; m->nm = m->host->nm;
   pin_host( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np );
   if( m->np>0 )
@@ -152,18 +169,20 @@ void to_device( SpeciesMirror * m ) {
     unsorted:;
   }
   m->dev_valid = true; m->partition_dev_valid = false;
+  track_arm( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np );
 }
 
 void to_host( SpeciesMirror * m ) {
   Runtime & r = rt();
   if( !m->dev_valid || m->host_valid ) return;
+  materialize_sort( m );
   m->host->np = m->np;
   if( m->host->p && m->np>0 )
     d2h( m->host->p, m->d_p, sizeof(vpb_particle_t)*(size_t)m->np, r.stream );
   if( m->host->partition && m->partition_dev_valid )
     d2h( m->host->partition, m->d_partition, sizeof(int)*( (size_t)m->grid->dev.nv + 1 ), r.stream );   // nv+1 entries (species_advance.c:138); [nv] = np
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-  if( m->host->p ) m->host_valid = true;
+  if( m->host->p ) { m->host_valid = true; track_arm( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np ); }
 }
 
 // The mover list and its count are what the host driver reads after advance_p
@@ -202,8 +221,10 @@ int vpic_b200_init( int device, int world_rank, int world_size ) {
 }
 
 void vpic_b200_set_coherence( int mode ) {
-  if( mode!=VPB_COHERENCE_STRICT && mode!=VPB_COHERENCE_RESIDENT ) VPB_ERROR( "Bad args" );
-  rt().coherence = mode;
+  if( mode!=VPB_COHERENCE_STRICT && mode!=VPB_COHERENCE_RESIDENT && mode!=VPB_COHERENCE_TRACKED ) VPB_ERROR( "Bad args" );
+  // TRACKED is STRICT for every entry point; the difference lives in to_device (skips clean arrays)
+  rt().coherence = mode==VPB_COHERENCE_TRACKED ? VPB_COHERENCE_STRICT : mode;
+  track_enable( mode==VPB_COHERENCE_TRACKED );
 }
 
 void vpic_b200_set_deposit_mode( int mode ) {
@@ -257,7 +278,7 @@ void vpic_b200_forget( void * obj ) {
   Runtime & r = rt();
   if( !r.initialised ) return;
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-  if( r.species.count( obj ) ) { auto m = r.species[obj]; unpin_host( m->host->p ); cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
+  if( r.species.count( obj ) ) { auto m = r.species[obj]; unpin_host( m->host->p ); release_lazy_sort( m ); cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
   if( r.fields.count( obj )  ) { auto m = r.fields[obj]; unpin_host( m->host->f ); cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
   if( r.interps.count( obj ) ) { auto m = r.interps[obj]; unpin_host( m->host->i ); cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
   if( r.accs.count( obj )    ) { auto m = r.accs[obj]; unpin_host( m->host->a ); cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }
@@ -277,6 +298,7 @@ void vpic_b200_grid_changed( const void * grid ) {
 }
 
 void * vpic_b200_device_ptr( void * obj, int which ) {
+  if( auto m = VPB_FIND( species, obj ) ) materialize_sort( m );
   if( auto m = VPB_FIND( species, obj ) ) return which==0 ? (void *)m->d_p : which==1 ? (void *)m->d_pm : (void *)m->d_partition;
   if( auto m = VPB_FIND( fields,  obj ) ) return (void *)m->d;
   if( auto m = VPB_FIND( interps, obj ) ) return (void *)m->d;

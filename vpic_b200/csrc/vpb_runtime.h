@@ -161,6 +161,14 @@ struct SpeciesMirror {
   bool dev_valid = false, host_valid = true;
   bool partition_dev_valid = false;
   const vpb_particle_t * registered_p = nullptr; size_t registered_bytes = 0;
+  // Lazy sort_p (RESIDENT coherence + FAST deposit, vpb_sort.cu): the sort has been carried out on
+  // indices only -- slot d of the sorted order is d_p[ d_perm[d] ] -- and the next advance_p gathers
+  // through d_perm while it pushes.  Anything else that looks at the particles first makes the order
+  // real (materialize_sort, called from to_device / to_host).
+  int * d_perm = nullptr; size_t cap_perm = 0; bool perm_pending = false;
+  // Voxel index of every particle as the last advance_p left it (written by the launch that precedes
+  // a sort_p); valid until anything else moves, adds or removes particles (mark_dev_written).
+  int * d_keys = nullptr; size_t cap_keys = 0; bool keys_valid = false;
 };
 
 struct Runtime {
@@ -191,6 +199,13 @@ void ensure_init();
 void pin_host( const void * ptr, size_t bytes );   // page-lock a host array the host program owns (idempotent, best effort)
 void unpin_host( const void * ptr );
 void unpin_all();
+// write tracking of host arrays (vpb_track.cu; coherence mode TRACKED = STRICT + skipping uploads of arrays the host did not write)
+bool track_enabled();
+void track_enable( bool on );
+void track_arm( const void * p, size_t bytes );      // host array == device mirror right now: write-protect it
+bool track_clean( const void * p, size_t bytes );    // not written by the host program since it was armed
+void track_disarm( const void * p );                 // give the pages back (before freeing / resizing, or forgetting the object)
+void track_forget_all();
 void * scratch( size_t bytes );        // grow-only device scratch
 void * pinned( size_t bytes );         // grow-only pinned host scratch
 
@@ -213,10 +228,15 @@ void release( HydroMirror * m );
 void to_device( FieldMirror * m );   void to_host( FieldMirror * m );
 void to_device( InterpMirror * m );  void to_host( InterpMirror * m );
 void to_device( AccMirror * m );     void to_host( AccMirror * m );
-void to_device( SpeciesMirror * m ); void to_host( SpeciesMirror * m );
+void to_device( SpeciesMirror * m, bool keep_lazy_sort = false ); void to_host( SpeciesMirror * m );
+void materialize_sort( SpeciesMirror * m );            // carry out a pending lazy sort_p (no-op otherwise)
+vpb_particle_t * sort_spare( size_t min_particles );   // the spare particle buffer shared by all species
+void sort_swap_spare( SpeciesMirror * m );             // m->d_p <-> the spare buffer (after an out-of-place pass)
+void release_lazy_sort( SpeciesMirror * m );
 void to_device( HydroMirror * m );   void to_host( HydroMirror * m );
 void movers_to_host( SpeciesMirror * m );
 template<class M> inline void mark_dev_written( M * m ) { m->dev_valid = true; m->host_valid = false; }
+inline void mark_dev_written( SpeciesMirror * m ) { m->dev_valid = true; m->host_valid = false; m->keys_valid = false; }
 // In STRICT mode every entry point finishes by pushing what it wrote back.
 template<class M> inline void finish_write( M * m ) {
   mark_dev_written( m );

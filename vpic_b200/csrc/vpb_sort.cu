@@ -162,20 +162,33 @@ template<int E> __device__ __forceinline__ void warp_bitonic_regs( int (&x)[E], 
   }
 }
 
-template<int E> __device__ __forceinline__ void
+// GATHER: copy the particles to their final places; otherwise (lazy sort_p) only write the
+// ordered indices to out_perm -- the next advance_p gathers through them.
+template<int E, bool GATHER> __device__ __forceinline__ void
 fix_gather_regs( const int * __restrict__ perm, int b, int n, int lane,
-                 const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
+                 const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out, int * __restrict__ out_perm ) {
   int x[E];
 # pragma unroll
   for( int k=0; k<E; k++ ) x[k] = 32*k+lane<n ? perm[b+32*k+lane] : 0x7fffffff;
-  warp_bitonic_regs<E>( x, lane );
+  // The atomic slots were handed out to whole warps of a (nearly) sorted array: most segments arrive already
+  // ascending (one or two contiguous groups in order).  One neighbour compare per element finds out and
+  // skips the sorting network (which is what made this kernel issue-bound).
+  bool ok = true;
 # pragma unroll
-  for( int k=0; k<E; k++ ) if( 32*k+lane<n ) copy_particle( out, b+32*k+lane, in, x[k] );
+  for( int k=0; k<E; k++ ) {
+    const int nxt = __shfl_down_sync( 0xffffffffu, x[k], 1 );
+    const int wrap = __shfl_sync( 0xffffffffu, k+1<E ? x[k+1<E ? k+1 : k] : 0x7fffffff, 0 );
+    ok = ok && x[k]<=( lane==31 ? wrap : nxt );
+  }
+  if( !__all_sync( 0xffffffffu, ok ) ) warp_bitonic_regs<E>( x, lane );
+# pragma unroll
+  for( int k=0; k<E; k++ ) if( 32*k+lane<n ) { if( GATHER ) copy_particle( out, b+32*k+lane, in, x[k] ); else out_perm[b+32*k+lane] = x[k]; }
 }
 
+template<bool GATHER>
 __global__ void __launch_bounds__(32*FIX_WARPS)
 k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch,
-                   const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
+                   const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out, int * __restrict__ out_perm ) {
   __shared__ int s[FIX_WARPS][FIX_SMEM];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int v = blockIdx.x*FIX_WARPS + w;
@@ -184,9 +197,9 @@ k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __r
   if( n<=0 ) return;
   // Segments up to 32*FIX_E indices sort in registers, with a network sized for
   // the segment (ne is warp uniform); lane l of slot k then holds rank 32k+l.
-  if( n<=32 )       { fix_gather_regs<1>( perm, b, n, lane, in, out ); return; }
-  if( n<=64 )       { fix_gather_regs<2>( perm, b, n, lane, in, out ); return; }
-  if( n<=32*FIX_E ) { fix_gather_regs<FIX_E>( perm, b, n, lane, in, out ); return; }
+  if( n<=32 )       { fix_gather_regs<1,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
+  if( n<=64 )       { fix_gather_regs<2,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
+  if( n<=32*FIX_E ) { fix_gather_regs<FIX_E,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
   int n2 = 64; while( n2<n ) n2 <<= 1;
   int * a;
   if( n2<=FIX_SMEM ) a = s[w];
@@ -194,7 +207,14 @@ k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __r
   for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
   __threadfence_block(); __syncwarp();
   bitonic_mem( a, n2, lane );
-  for( int t=lane; t<n; t+=32 ) copy_particle( out, b+t, in, a[t] );
+  for( int t=lane; t<n; t+=32 ) { if( GATHER ) copy_particle( out, b+t, in, a[t] ); else out_perm[b+t] = a[t]; }
+}
+
+// out[d] = in[ perm[d] ]: carries out a lazy sort that no advance_p consumed
+__global__ void __launch_bounds__(256)
+k_sort_apply_perm( const int * __restrict__ perm, int np, const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
+  const int d = blockIdx.x*blockDim.x + threadIdx.x;
+  if( d<np ) copy_particle( out, d, in, perm[d] );
 }
 
 __global__ void __launch_bounds__(256)
@@ -237,24 +257,67 @@ k_sort_check( const vpb_particle_t * __restrict__ p, int np, const int * __restr
 static vpb_particle_t * g_alt = nullptr; static size_t g_alt_cap = 0;
 void release_sort_buffers() { if( g_alt ) cudaFree( g_alt ); g_alt = nullptr; g_alt_cap = 0; }
 
+vpb_particle_t * sort_spare( size_t min_particles ) {
+  if( g_alt_cap<min_particles ) {
+    VPB_CUDA( cudaStreamSynchronize( rt().stream ) );
+    if( g_alt ) VPB_CUDA( cudaFree( g_alt ) );
+    VPB_CUDA( cudaMalloc( &g_alt, sizeof(vpb_particle_t)*min_particles ) );
+    g_alt_cap = min_particles;
+  }
+  return g_alt;
+}
+
+void sort_swap_spare( SpeciesMirror * m ) {
+  vpb_particle_t * t = m->d_p; size_t tc = m->cap_p;
+  m->d_p = g_alt; m->cap_p = g_alt_cap; g_alt = t; g_alt_cap = tc;
+}
+
+void materialize_sort( SpeciesMirror * m ) {
+  if( !m->perm_pending ) return;
+  Runtime & r = rt();
+  m->perm_pending = false;
+  if( m->np<=0 ) return;
+  vpb_particle_t * out = sort_spare( m->cap_p );
+  k_sort_apply_perm<<< div_up( m->np, 256 ), 256, 0, r.stream >>>( m->d_perm, m->np, m->d_p, out );
+  VPB_CHECK_LAUNCH(); r.launches++;
+  sort_swap_spare( m );
+  m->keys_valid = false;                 // d_keys is in the old order
+}
+
+void release_lazy_sort( SpeciesMirror * m ) {
+  if( m->d_perm ) cudaFree( m->d_perm );
+  if( m->d_keys ) cudaFree( m->d_keys );
+  m->d_perm = m->d_keys = nullptr; m->cap_perm = m->cap_keys = 0; m->perm_pending = m->keys_valid = false;
+}
+
+static int lazy_sort_enabled() {
+  static int on = -1;
+  if( on<0 ) { const char * e = getenv( "VPIC_B200_LAZY_SORT" ); on = ( e && e[0]=='0' ) ? 0 : 1; }
+  return on;
+}
+
 } // namespace vpb
 
 using namespace vpb;
 
+// sort_p_pipeline.c:221-371.  Two ways to the same result:
+//  * immediate (STRICT coherence, PARITY deposit): histogram of the particles' voxels, scan, index scatter,
+//    per-voxel ordering fused with the particle copy into the spare buffer;
+//  * lazy (RESIDENT coherence + FAST deposit): the same up to the per-voxel ordering, which writes the ordered
+//    INDICES only (d_perm); the particle copy is left to the next advance_p, which reads through d_perm and
+//    writes the other buffer while it pushes (k_advance_p<GATHER>), so the sort's 64 B per particle copy pass
+//    costs nothing.  If the preceding advance_p left the voxel keys (d_keys), the 32 B records are not read
+//    here at all.  Whatever else touches the particles first carries the permutation out (materialize_sort).
 extern "C" void sort_p( vpb_species_t * sp ) {
   if( !sp ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
   SpeciesMirror * m = mirror( sp );
-  to_device( m );
+  const bool lazy = r.coherence==VPB_COHERENCE_RESIDENT && r.deposit_mode==VPB_DEPOSIT_FAST && lazy_sort_enabled();
+  to_device( m );                        // (a sort still pending from an earlier call is carried out here)
   sp->last_sorted = sp->g->step;
   const GridDev & g = m->grid->dev;
   const int np = m->np, nv = g.nv;
-  if( g_alt_cap<m->cap_p ) {
-    VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-    if( g_alt ) VPB_CUDA( cudaFree( g_alt ) );
-    VPB_CUDA( cudaMalloc( &g_alt, sizeof(vpb_particle_t)*m->cap_p ) );
-    g_alt_cap = m->cap_p;
-  }
+  if( !lazy ) sort_spare( m->cap_p );
   // scratch: keys[np] perm[np] count[nv+1] next[nv+1] tiles big[2np]
   const size_t npa = ( (size_t)np + 31 ) & ~(size_t)31, nva = ( (size_t)nv + 1 + 31 ) & ~(size_t)31;
   const size_t ntile = (size_t)div_up( nv+1, SCAN_TILE ) + 32;
@@ -262,20 +325,33 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   int * keys = base, * perm = keys + npa, * count = perm + npa, * next = count + nva, * tiles = next + nva, * big = tiles + ntile;
   VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nv+1 ), r.stream ) );
   if( np>0 ) {
-    k_sort_hist<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, np, keys, count );
+    if( lazy && m->keys_valid && m->d_keys ) {       // the keys are already there: 4 B per particle instead of 32
+      keys = m->d_keys;
+      k_hist_keys<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, count );
+    } else k_sort_hist<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, np, keys, count );
     VPB_CHECK_LAUNCH(); r.launches++;
   }
   exclusive_scan( count, m->d_partition, next, tiles, nv+1 );
   if( np>0 ) {
     k_sort_scatter_idx<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, next, perm );
-    k_sort_fix_gather<<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt );
+    if( lazy ) {
+      if( m->cap_perm<m->cap_p ) {
+        VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+        if( m->d_perm ) VPB_CUDA( cudaFree( m->d_perm ) );
+        VPB_CUDA( cudaMalloc( &m->d_perm, sizeof(int)*m->cap_p ) ); m->cap_perm = m->cap_p;
+      }
+      k_sort_fix_gather<false><<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, nullptr, m->d_perm );
+      m->perm_pending = true;
+    } else {
+      k_sort_fix_gather<true><<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt, nullptr );
+      sort_swap_spare( m );            // swap the species buffer with the spare
+    }
     VPB_CHECK_LAUNCH(); r.launches += 2;
-    // swap the species buffer with the spare
-    vpb_particle_t * t = m->d_p; size_t tc = m->cap_p;
-    m->d_p = g_alt; m->cap_p = g_alt_cap; g_alt = t; g_alt_cap = tc;
   }
   m->partition_dev_valid = true;
+  const bool keep = m->perm_pending;
   mark_dev_written( m );
+  m->perm_pending = keep;
   if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
 }
 
