@@ -36,8 +36,11 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", default="512x256x256", help="cells per GPU")
     ap.add_argument("--ppc", type=int, default=32, help="particles per cell per species")
-    ap.add_argument("--sort-interval", default="8", help="steps between sorts: one value, or electron,ion (species_t::sort_interval is per species)")
+    ap.add_argument("--sort-interval", default="3,12", help="steps between sorts: one value, or electron,ion (species_t::sort_interval is per "
+                    "species; the thermal electrons leave their cells 10 x faster than the ions and the lazy sort_p is cheap)")
     ap.add_argument("--e2e-cells", default="256x128x128")
+    ap.add_argument("--e2e-sort-interval", default="8", help="sort cadence of the e2e leg (host-resident particles: every sort_p is a full "
+                    "download of the species, so the cheap lazy sort of the resident path does not apply)")
     ap.add_argument("--cpu-cells", default="128x128x64", help="box of the bounded CPU sample (same physics and ppc)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="cpu_baseline leg: keep stepping the sample for about this long")
     ap.add_argument("--no-cpu", action="store_true")
@@ -414,19 +417,26 @@ DECKS = {   # name: (initial particles, steps, what)
 }
 
 
-def profile_table(text):
-    """The reference's own TIC/TOC table (src/util/profile/profile.c:12-60): the LAST table of the log, cumulative
-    column -> {stage: (seconds, calls)}."""
-    rows = {}
+def profile_table(text, column=2):
+    """The reference's own TIC/TOC table (src/util/profile/profile.c:12-60), the LAST one of the log ->
+    {stage: (seconds, calls)}.  column 2 = cumulative since the start, column 1 = since the previous table
+    (the last status interval: steady state, without the first calls' allocations and CUDA start-up)."""
+    tables, rows = [], {}
     for line in text.splitlines():
         parts = line.split("|")
-        if len(parts) == 3 and "%" in parts[2]:
-            f = parts[2].split()
+        if len(parts) == 3 and "Operation" in parts[0]:
+            rows = {}; tables.append(rows)
+        elif len(parts) == 3 and "%" in parts[2] and tables:
+            f = parts[column].split()
             try:
                 rows[parts[0].strip()] = (float(f[1]), float(f[2]))
             except (IndexError, ValueError):
                 pass
-    return rows
+    # the program prints one more table when it ends, with an empty "since last update" column
+    for rows in reversed(tables):
+        if rows.get("advance_p", (0.0, 0.0))[1] > 0:
+            return rows
+    return tables[-1] if tables else {}
 
 
 def deck_e2e():
@@ -464,6 +474,9 @@ def deck_e2e():
                 res[side] = {"error": (r.stderr or r.stdout)[-300:]}
                 continue
             tab = profile_table(r.stdout + r.stderr)
+            last = profile_table(r.stdout + r.stderr, column=1)
+            last_steps = last.get("advance_p", (0.0, 0.0))[1] / 2.0                 # two species
+            last_loop = sum(v[0] for k, v in last.items() if k != "user_diagnostics")
             ap = tab.get("advance_p", (0.0, 0.0))
             # our entry points return before their kernels finish (the time surfaces in the next call that
             # synchronises), so only sums over stages are meaningful on the GPU side: the whole table = the step
@@ -474,6 +487,10 @@ def deck_e2e():
                          "pushes_per_s_advance_p": npart * steps / ap[0] if ap[0] > 0 else None,
                          "step_stages_s": round(loop, 4), "pushes_per_s_step_stages": npart * steps / loop if loop > 0 else None,
                          "hot_path_stages_s": round(compute, 4),
+                         # the last status interval alone, dumps excluded: the steady-state step
+                         "steady_steps": last_steps, "steady_ms_per_step": round(last_loop / last_steps * 1e3, 3) if last_steps else None,
+                         "steady_pushes_per_s": npart * last_steps / last_loop if last_loop > 0 and last_steps else None,
+                         "stages_s": {k: v[0] for k, v in sorted(tab.items(), key=lambda kv: -kv[1][0])[:8]},
                          "last_energies_line": en[-1] if en else None}
         g, c = res.get("gpu", {}), res.get("cpu", {})
         if g.get("step_stages_s") and c.get("step_stages_s"):
@@ -481,6 +498,8 @@ def deck_e2e():
             res["speedup_wall"] = round(c["wall_s"] / g["wall_s"], 2)
             if g.get("hot_path_stages_s"):
                 res["speedup_hot_path_stages"] = round(c["hot_path_stages_s"] / g["hot_path_stages_s"], 2)
+            if g.get("steady_ms_per_step") and c.get("steady_ms_per_step"):
+                res["speedup_steady_step"] = round(c["steady_ms_per_step"] / g["steady_ms_per_step"], 2)
         out[deck] = res
     return out
 
@@ -493,7 +512,7 @@ def bench_e2e(torch, L, be, host, stream, args, rank=0, world=1, dist=None, step
     n = dims(args.e2e_cells)
     L.vpic_b200_set_coherence(mode)        # 2 = TRACKED (STRICT + write tracking of the host arrays), 0 = STRICT
     try:
-        sim, sps = uniform_plasma(be, host, n, args.ppc, args.sort_interval, topo=(world, 1, 1), host_arrays=True)
+        sim, sps = uniform_plasma(be, host, n, args.ppc, args.e2e_sort_interval, topo=(world, 1, 1), host_arrays=True)
         for k, (sp, vth, w) in enumerate(sps):
             L.vpic_b200_load_uniform_maxwellian(sp, args.ppc, vth, w, 99 + k + 1000 * rank)   # lands in the host arrays (STRICT)
         sim.initialize()
@@ -516,7 +535,7 @@ def bench_e2e(torch, L, be, host, stream, args, rank=0, world=1, dist=None, step
                "h2d_bytes_per_step": int((b1[0] - b0[0]) / steps), "d2h_bytes_per_step": int((b1[1] - b0[1]) / steps),
                "ms_per_step": dt / steps * 1e3,
                "coherence": "tracked" if mode == 2 else "strict",
-               "workload": f"same physics, {args.e2e_cells} cells per GPU x 2 species x {args.ppc} ppc resident in HOST memory "
+               "workload": f"same physics, {args.e2e_cells} cells per GPU x 2 species x {args.ppc} ppc, sort every {args.e2e_sort_interval}, resident in HOST memory "
                            f"(the reference's posix_memalign arrays, page-locked by the library on first use); every entry point "
                            f"takes host structs in and leaves host structs current: the step's results (particles, movers, fields) "
                            f"are read back by every call.  "

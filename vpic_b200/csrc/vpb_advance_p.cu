@@ -42,18 +42,6 @@ namespace vpb {
 #ifndef VPB_AP_MINBLK
 #define VPB_AP_MINBLK 10
 #endif
-#ifndef VPB_AP_COMMIT_AT_TILE_END
-#define VPB_AP_COMMIT_AT_TILE_END 0
-#endif
-#ifndef VPB_AP_REC
-#define VPB_AP_REC 0          // N > 0: the coefficient records of N consecutive voxels around the tile travel with the tile's bulk copy
-#endif
-#ifndef VPB_AP_PREF
-#define VPB_AP_PREF 0         // 1: the first coefficient record of the lane's NEXT tile is requested at the end of this tile
-#endif
-#ifndef VPB_HINT_STREAM
-#define VPB_HINT_STREAM 0     // 1: evict_first L2 policy on the tile's bulk load and bulk store
-#endif
 constexpr int AP_K      = VPB_AP_K;     // consecutive particles per lane
 constexpr int AP_NBUF   = VPB_AP_NBUF;  // tile buffers per warp: 2 = the next tile is loading while this one is pushed
 constexpr int AP_TILE   = 32*AP_K;      // particles per warp tile
@@ -69,13 +57,6 @@ struct __align__(128) WarpTile {
   // queue of particles that left their voxel: remaining displacement + index
   // (position, voxel, momentum and weight are still in the particle's slot)
   float4 q[AP_QCAP];                    // dispx, dispy, dispz, index relative to the launch's first particle
-#if VPB_AP_REC
-  // Interpolator records of the voxels [vwin, vwin+VPB_AP_REC) -- one voxel before the tile's first particle's
-  // and the ones that follow: a cell-sorted tile of 256 particles lives in ~9 consecutive voxels.  They arrive
-  // with the tile (second bulk copy on the same mbarrier), so a lane that changes voxel inside the window
-  // reads shared memory instead of waiting for an L2 / DRAM gather in the middle of its run.
-  float4 rec[VPB_AP_REC*6];
-#endif
   unsigned long long bar[AP_NBUF];      // mbarrier of each buffer's tile load
 };
 
@@ -161,29 +142,13 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   __syncwarp();
 
   // one elected lane starts the bulk copy of a tile into buffer b
-#if VPB_AP_REC
-  int win0 = 0;                                // lane 0: first voxel of the record window of the tile being loaded
-#endif
   auto start_load = [&]( int tile, int b ) {
     const long long t0 = (long long)tile*AP_TILE;
     const uint32_t bytes = (uint32_t)( ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE )*32u;
     const uint32_t bar = smem_u32( &S.bar[b] ), dst = smem_u32( S.tile[b] );
-#if VPB_AP_REC
-    int wn = g.nv - win0; wn = wn<VPB_AP_REC ? wn : VPB_AP_REC;
-    const uint32_t rbytes = (uint32_t)wn*( IP_STRIDE*4u );
-    asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes + rbytes) : "memory" );
-    asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                  :: "r"(smem_u32( S.rec )), "l"(ip + (size_t)win0*IP_STRIDE), "r"(rbytes), "r"(bar) : "memory" );
-#else
     asm volatile( "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory" );
-#endif
-#if VPB_HINT_STREAM
-    asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                  :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar), "l"(l2_policy_evict_first()) : "memory" );
-#else
     asm volatile( "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                   :: "r"(dst), "l"(p + t0), "r"(bytes), "r"(bar) : "memory" );
-#endif
   };
 
   uint32_t phase = 0;                          // bit b: parity the next wait on buffer b expects
@@ -202,25 +167,10 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   for( int k=0; k<12; k++ ) run[k] = 0.f;
   Interp f = {};
 
-#if VPB_AP_PREF
-  int nvox = -1;                               // voxel of the first particle this lane visits in its next tile
-#endif
-#if VPB_AP_REC
-  int vnext = 0;                               // lane 0: voxel of the first particle of this warp's next tile
-  if( !GATHER && lane==0 ) asm volatile( "ld.global.b32 %0, [%1];" : "=r"(vnext) : "l"( reinterpret_cast<const int *>( p + (long long)gw*AP_TILE ) + 3 ) );
-  int vwin = 0, nwin = 0;                      // the window in shared memory (warp uniform)
-#endif
   if( AP_NBUF>1 && lane==0 ) start_load( gw, 0 );
   for( int tile=gw; tile<ntile; tile+=total_warps ) {
     const long long t0 = (long long)tile*AP_TILE;
     const int cnt = ( np - t0 < AP_TILE ) ? (int)( np - t0 ) : AP_TILE;
-#if VPB_AP_REC
-    if( !GATHER ) {
-      if( lane==0 ) { win0 = vnext>0 ? vnext-1 : 0; if( win0>=g.nv ) win0 = g.nv-1; }
-      vwin = __shfl_sync( 0xffffffffu, win0, 0 );
-      nwin = g.nv - vwin; nwin = nwin<VPB_AP_REC ? nwin : VPB_AP_REC;
-    }
-#endif
     if( !GATHER && AP_NBUF==1 && lane==0 ) start_load( tile, 0 );
     float4 * __restrict__ T = S.tile[buf];
     auto on_chip = [&]( int rel ) -> float4 * { return ( rel>=t0 && rel<t0+cnt ) ? &T[ 2*(int)( rel-t0 ) ] : nullptr; };
@@ -261,22 +211,6 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
           start_load( tile+total_warps, buf^1 );
         }
       }
-#if VPB_AP_REC
-      if( !GATHER && k==AP_K/2 && lane==0 && tile+total_warps<ntile )
-        asm volatile( "ld.global.b32 %0, [%1];" : "=r"(vnext) : "l"( reinterpret_cast<const int *>( p + (long long)( tile+total_warps )*AP_TILE ) + 3 ) );
-#endif
-#if VPB_AP_PREF
-      if( !GATHER && k==AP_K/2 ) {
-        // Peek at the voxel of the particle this lane starts its NEXT tile with (4 bytes from global memory,
-        // half a tile ahead of its use).  When this tile is done the lane's coefficient registers are dead, so
-        // that record is requested right then and arrives while the tile is stored and the next one is loaded:
-        // the gather latency of the first particle of a tile (23 % of the ion launches' warp stall samples)
-        // is no longer exposed.
-        const long long tn = (long long)( tile+total_warps )*AP_TILE + lane*AP_K + ( lane & ( AP_K-1 ) );
-        nvox = -1;
-        if( tile+total_warps<ntile && tn<np ) asm volatile( "ld.global.b32 %0, [%1];" : "=r"(nvox) : "l"( reinterpret_cast<const int *>( p + tn ) + 3 ) );
-      }
-#endif
       // rotate the start of each lane's run so the 128-bit shared accesses of a
       // quarter warp spread over the banks
       const int loc = lane*AP_K + ( ( k + lane ) & ( AP_K-1 ) );
@@ -287,21 +221,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         const float4 r0 = T[2*loc], r1 = T[2*loc+1];
         const float dx = r0.x, dy = r0.y, dz = r0.z; const int ii = __float_as_int( r0.w );
         float ux = r1.x, uy = r1.y, uz = r1.z;
-#if VPB_AP_REC
-        if( ii!=fvox ) {
-          const unsigned rv = (unsigned)( ii - vwin );
-          if( !GATHER && rv<(unsigned)nwin ) {
-            const float4 * q = S.rec + 6*rv;
-            const float4 a = q[0], b = q[1], cc = q[2], d = q[3]; const float2 e = *reinterpret_cast<const float2 *>( q+4 );
-            f.ex = a.x; f.dexdy = a.y; f.dexdz = a.z; f.d2exdydz = a.w; f.ey = b.x; f.deydz = b.y; f.deydx = b.z; f.d2eydzdx = b.w;
-            f.ez = cc.x; f.dezdx = cc.y; f.dezdy = cc.z; f.d2ezdxdy = cc.w; f.cbx = d.x; f.dcbxdx = d.y; f.cby = d.z; f.dcbydy = d.w;
-            f.cbz = e.x; f.dcbzdz = e.y;
-          } else f = load_interp( ip, ii );
-          fvox = ii;
-        }
-#else
         if( ii!=fvox ) { f = load_interp( ip, ii ); fvox = ii; }
-#endif
         if( ii!=cur ) {
           // A particle that strayed into this run since the last sort_p (the
           // lane's next particle is back in the run's voxel) deposits on its
@@ -382,14 +302,6 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         __syncwarp();
       }
     }
-#if VPB_AP_COMMIT_AT_TILE_END
-    // The lane's next tile lies total_warps tiles ahead, in other voxels: its open
-    // run ends here.  Committing it now instead of at the first particle of the
-    // next tile (about one tile time later, by when ~60 MB of particle stream have
-    // gone through L2) finds the voxel's accumulator sectors still in L2 from the
-    // commits of the neighbouring lanes.
-    if( keepf!=0.f ) { commit_currents( acc, cur, run ); keepf = 0.f; cur = -1; }
-#endif
     if( KEYS ) {
       // the voxel index is the 4th word of every record of the tile: 32 consecutive keys per store
       // (particles that left the domain carry 8*voxel+face and are boundary_p's, which invalidates the keys)
@@ -403,18 +315,11 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     __syncwarp();
     if( lane==0 ) {
       const uint32_t bytes = (uint32_t)cnt*32u;
-#if VPB_HINT_STREAM
-      asm volatile( "cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" :: "l"(p + t0), "r"(smem_u32( T )), "r"(bytes), "l"(l2_policy_evict_first()) : "memory" );
-#else
       asm volatile( "cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(p + t0), "r"(smem_u32( T )), "r"(bytes) : "memory" );
-#endif
       asm volatile( "cp.async.bulk.commit_group;" ::: "memory" );
       if( AP_NBUF==1 ) asm volatile( "cp.async.bulk.wait_group.read 0;" ::: "memory" );   // the tile buffer is reused at once
     }
     __syncwarp();
-#if VPB_AP_PREF
-    if( !GATHER && nvox>=0 && nvox!=fvox ) { f = load_interp( ip, nvox ); fvox = nvox; }
-#endif
     if( AP_NBUF>1 ) buf ^= 1;
   }
 

@@ -43,6 +43,12 @@ void on_segv( int sig, siginfo_t * si, void * ctx ) {
     if( t.armed && a>=t.lo && a<t.hi ) {
       t.dirty = 1; t.armed = 0;
       mprotect( (void *)t.lo, t.hi-t.lo, PROT_READ|PROT_WRITE );     // async-signal-safe
+      // a neighbouring array that shares a page with this one just lost the protection of that page:
+      // it can no longer vouch for itself either
+      for( int j=0; j<n; j++ ) {
+        Tracked & o = g_tr[j];
+        if( o.armed && o.lo<t.hi && t.lo<o.hi ) { o.dirty = 1; o.armed = 0; mprotect( (void *)o.lo, o.hi-o.lo, PROT_READ|PROT_WRITE ); }
+      }
       return;                                                        // the faulting store is retried
     }
   }
@@ -109,7 +115,13 @@ bool track_clean( const void * p, size_t bytes ) {
 void track_disarm( const void * p ) {
   Tracked * t = p ? find( p ) : nullptr;
   if( !t ) return;
-  if( t->armed ) { t->armed = 0; mprotect( (void *)t->lo, t->hi-t->lo, PROT_READ|PROT_WRITE ); }
+  if( t->armed ) {
+    t->armed = 0; mprotect( (void *)t->lo, t->hi-t->lo, PROT_READ|PROT_WRITE );
+    for( int j=0; j<g_ntr; j++ ) {          // neighbours sharing a page (see on_segv)
+      Tracked & o = g_tr[j];
+      if( o.armed && o.lo<t->hi && t->lo<o.hi ) { o.dirty = 1; o.armed = 0; mprotect( (void *)o.lo, o.hi-o.lo, PROT_READ|PROT_WRITE ); }
+    }
+  }
   t->dirty = 1;
 }
 
