@@ -246,7 +246,12 @@ def run_b200(args):
                                                                              if world > 1 and L.vpic_b200_comm_transport() else "ncclSend/ncclRecv")},
            "roofline": roofline, "gpu_launches": int(launches), "clocks": sampler.summary(),
            "sort_p": {"ms_per_call": sort_ms / max(sort_calls, 1), "calls": sort_calls, "share_of_step": round(sort_ms / ms, 4),
-                      "GB/s": (np_total / 2 * 68.0 / (sort_ms / max(sort_calls, 1) * 1e-3) / 1e9) if sort_calls else None,
+                      "mode": "lazy" if os.environ.get("VPIC_B200_LAZY_SORT", "1") != "0" else "immediate",
+                      # lazy: the call orders indices only (key histogram, scan, index scatter, per-voxel ordering: ~20 B per
+                      # particle); the 64 B per particle copy rides in the next advance_p launch (k_advance_p<GATHER>) and is
+                      # inside roofline's advance_p time.  immediate (VPIC_B200_LAZY_SORT=0): the whole 68 B/particle sort.
+                      "GB/s_of_68B_per_particle": (np_total / 2 * 68.0 / (sort_ms / max(sort_calls, 1) * 1e-3) / 1e9)
+                                                  if sort_calls and os.environ.get("VPIC_B200_LAZY_SORT", "1") == "0" else None,
                       "bytes_per_particle": 68.0}}
     if args.breakdown:
         out["breakdown_ms"] = breakdown(torch, sim, be, args.breakdown)
