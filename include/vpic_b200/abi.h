@@ -146,6 +146,16 @@ typedef struct vpb_hydro_array {
   vpb_grid_t  *g;
 } vpb_hydro_array_t;
 
+/* ---- Langevin collision operator: src/collision/langevin.h:6-13 ---------- */
+
+typedef struct vpb_langevin {
+  vpb_species_t * sp;
+  void          * rp;        /* rng_pool_t * of the host program (not used on the device: counter-based generator) */
+  float kT;
+  float nu;
+  int   interval;
+} vpb_langevin_t;
+
 /* ---- fields: src/field_advance/field_advance.h:152-229 ------------------- */
 
 typedef int16_t vpb_material_id;

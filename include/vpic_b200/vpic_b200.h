@@ -84,6 +84,16 @@ void vpic_b200_clean_div_b( vpb_field_array_t * fa );                 /* clean_d
    src/species_advance/standard/rho_p.cc:22-112). */
 void accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp );
 
+/* Langevin thermostat: src/collision/langevin.h:14-15, pipeline/langevin_pipeline.c:44-112.
+   u = decay u + drive N(0,1) per momentum component, decay = exp(-nu dt interval),
+   drive = sqrt( (1 - exp(-2 nu dt interval)) kT / (m c) ); applied when step % interval == 0.  The reference's
+   apply_langevin (langevin.c:12-24, the function its collision_op_t holds) calls this symbol, so a program that
+   links the library ahead of the reference runs its langevin() operators on the device.  The normal deviates
+   come from a counter-based generator keyed by (seed, rank, species id, step, particle index) instead of the
+   host program's rng_pool: same distribution, different stream -- statistical parity, not bit parity. */
+void apply_langevin_pipeline( vpb_langevin_t * l );
+void vpic_b200_set_collision_seed( uint64_t seed );   /* default 0x5eed */
+
 /* Hydro moments for the dump path.
    Replace src/species_advance/species_advance.h accumulate_hydro_p
    (standard/hydro_p.c:26-167) and src/sf_interface/sf_interface.h:214-225

@@ -262,3 +262,19 @@ static void orc_half_step( vpb_species_t * sp, const vpb_interpolator_array_t * 
 }
 void orc_uncenter_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia ) { orc_half_step( sp, ia, 1 ); }
 void orc_center_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia ) { orc_half_step( sp, ia, 0 ); }
+
+/* src/collision/langevin.c:12-24 + pipeline/langevin_pipeline.c:20-42, 44-112 (single pipeline: the whole
+   array in order).  The reference draws frandn(rng) per component; here the deviates are an input. */
+void orc_apply_langevin( vpb_langevin_t * l, const float * normals ) {
+  vpb_species_t * sp = l->sp;
+  if( l->interval<1 || ( sp->g->step % l->interval ) ) return;
+  float nudt = l->nu * (float)l->interval * sp->g->dt;
+  float decay = exp( -nudt );
+  float drive = sqrt( ( -expm1( -2*nudt )*l->kT )/( sp->m*sp->g->cvac ) );
+  vpb_particle_t * p = sp->p;
+  for( int i=0; i<sp->np; i++ ) {
+    p[i].ux = decay*p[i].ux + drive*( normals ? normals[3*i+0] : 0.f );
+    p[i].uy = decay*p[i].uy + drive*( normals ? normals[3*i+1] : 0.f );
+    p[i].uz = decay*p[i].uz + drive*( normals ? normals[3*i+2] : 0.f );
+  }
+}

@@ -113,6 +113,10 @@ void orc_boundary_p_pbc( vpb_particle_bc_t * pbc_list, vpb_species_t * sp_list, 
 /* a deterministic handler for tests (params: int[6] hit counters or NULL) */
 int  orc_fixture_bounce_handler( void * params, vpb_species_t * sp, vpb_particle_t * p, vpb_particle_mover_t * pm,
                                  vpb_particle_injector_t * pi, int max_pi, int face );
+/* src/collision/pipeline/langevin_pipeline.c:20-42, 99-108: u = decay u + drive n for every momentum
+   component; normals = 3 deviates per particle in particle order (what frandn would have returned),
+   or NULL for zeros (the deterministic part).  Returns nothing when step % interval != 0, like the reference. */
+void orc_apply_langevin( vpb_langevin_t * l, const float * normals );
 void orc_accumulate_rhob( vpb_field_t * f, const vpb_particle_t * p, const vpb_grid_t * g, float qsp );
 
 /* Material coefficient table, src/field_advance/standard/sfa.c:55-151.

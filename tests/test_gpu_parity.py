@@ -620,8 +620,7 @@ def test_lazy_sort_is_carried_out_when_something_else_reads_the_particles(gpu):
     L.vpic_b200_set_coherence(1)
     try:
         for a, b in zip(so.species, sg.species):
-            L.vpic_b200_sync_from_host(b)
-            so.be.sort_p(a); sg.be.sort_p(b)
+            so.be.sort_p(a); sg.be.sort_p(b)            # (first touch of the species: the host particles go up)
             ep = sg.be.energy_p(b, sg.ia)               # reads the particles on the device: sorted order or not, same sum terms
             L.vpic_b200_sync_to_host(b)
             assert same_bits(sg.particles(b), so.particles(a))
@@ -631,10 +630,11 @@ def test_lazy_sort_is_carried_out_when_something_else_reads_the_particles(gpu):
             # second sort of the same species after every particle was given a random voxel, with a removed
             # tail and a crowded voxel
             rng = np.random.default_rng(3)
+            vox = rng.permutation(so.particles(a)["i"])
+            vox[: len(vox) // 5] = vox[0]
             for s, x in ((so, a), (sg, b)):
                 p = s.particles(x)
-                p["i"][:] = rng.permutation(p["i"]) if s is so else so.particles(a)["i"]
-                p["i"][: len(p) // 5] = p["i"][0]
+                p["i"][:] = vox
                 s.sp_struct(x).np = len(p) - 37
             L.vpic_b200_sync_from_host(b)
             so.be.sort_p(a); sg.be.sort_p(b)
@@ -711,3 +711,61 @@ def test_tracked_coherence_streamed_advance_p(gpu):
                 assert same_bits(sg.particles(b), so.particles(a)), rnd
     finally:
         L.vpic_b200_set_coherence(0)
+
+
+def test_langevin_operator_on_the_device(gpu):
+    """N4 (first piece): the Langevin thermostat as a device kernel behind the reference's own symbol
+    apply_langevin_pipeline (src/collision/pipeline/langevin_pipeline.c:44-112).  The arithmetic
+    u = decay u + drive n is the reference's; the deviates come from a counter-based generator, so parity is
+    bit-exact for the deterministic part (kT = 0, and the interval gate) and statistical for the rest: mean,
+    variance and kurtosis of each component, independence between components and between neighbouring
+    particles, and the relaxation of <u^2> towards kT/(m c) at the rate the operator's own decay / drive give."""
+    import ctypes as C
+    from vpic_b200 import abi
+    L = load_b200()
+    L.apply_langevin_pipeline.restype, L.apply_langevin_pipeline.argtypes = None, [C.c_void_p]
+    OL = H.oracle_backend().L
+    OL.orc_apply_langevin.restype, OL.orc_apply_langevin.argtypes = None, [C.c_void_p, C.c_void_p]
+    so, sg = pair(gpu, kind="periodic", n=(40, 32, 20), ppc=16)
+    a, b = so.species[0], sg.species[0]
+    lo, lg = abi.Langevin(a, None, 0.0, 3.0, 2), abi.Langevin(b, None, 0.0, 3.0, 2)
+    for step in range(3):
+        so.grid_struct(so.g).step = step; sg.grid_struct(sg.g).step = step
+        OL.orc_apply_langevin(C.byref(lo), None)
+        L.apply_langevin_pipeline(C.byref(lg))
+        assert same_bits(sg.particles(b), so.particles(a)), step
+    n, m = sg.sp_struct(b).np, sg.sp_struct(b).m
+    assert n >= 400000
+    # resampling limit: nu dt >> 1
+    kT = 0.04
+    lg.kT, lg.nu, lg.interval = kT, 400.0, 1
+    sg.grid_struct(sg.g).step = 5
+    L.apply_langevin_pipeline(C.byref(lg))
+    p = sg.particles(b)
+    u = np.stack([p["ux"], p["uy"], p["uz"]]).astype(np.float64)
+    s2 = kT / m
+    assert np.all(np.abs(u.mean(1)) < 5 * np.sqrt(s2 / n))
+    assert np.all(np.abs(u.var(1) / s2 - 1) < 5 * np.sqrt(2.0 / n))
+    assert np.all(np.abs((u ** 4).mean(1) / (3 * s2 ** 2) - 1) < 5 * np.sqrt(96.0 / 9 / n))          # normal kurtosis
+    c = np.corrcoef(u)
+    assert np.all(np.abs(c[np.triu_indices(3, 1)]) < 5 / np.sqrt(n))                               # components independent
+    assert abs(np.corrcoef(u[0, :-1], u[0, 1:])[0, 1]) < 5 / np.sqrt(n)                            # neighbouring particles independent
+    same_positions = all(np.array_equal(p[k], so.particles(a)[k]) for k in ("dx", "dy", "dz", "i", "w"))
+    assert same_positions
+    # a different step gives different deviates; the same step the same ones (counter-based)
+    u_first = u.copy()
+    sg.grid_struct(sg.g).step = 6
+    L.apply_langevin_pipeline(C.byref(lg))
+    p = sg.particles(b)
+    assert abs(np.corrcoef(u_first[0], p["ux"].astype(np.float64))[0, 1]) < 5 / np.sqrt(n)
+    # relaxation: a hot population cools towards kT at the operator's own rate
+    lg.kT, lg.nu = 0.01, 0.8
+    nudt = np.float32(lg.nu) * np.float32(sg.grid_struct(sg.g).dt)
+    decay, drive2 = float(np.exp(-np.float64(nudt))), float(-np.expm1(-2 * np.float64(nudt)) * lg.kT / m)
+    want = float((p["ux"].astype(np.float64) ** 2).mean())
+    for step in range(7, 27):
+        sg.grid_struct(sg.g).step = step
+        L.apply_langevin_pipeline(C.byref(lg))
+        want = decay ** 2 * want + drive2
+        got = float((sg.particles(b)["ux"].astype(np.float64) ** 2).mean())
+        assert abs(got / want - 1) < 6 * np.sqrt(2.0 / n) * np.sqrt(step - 5), (step, got, want)

@@ -240,3 +240,48 @@ def test_hydro_moments(kind):
         for k in ho.dtype.names[:14]:
             assert same_bits(ho[k], hr[k]), k
         assert np.abs(ho["rho"]).max() > 0 and np.abs(ho["txx"]).max() > 0
+
+
+def ref_langevin(rb, sp, kT, nu, interval, seed=7):
+    """The reference's own langevin() collision operator on species sp (src/collision/langevin.c:62-89) and its rng pool."""
+    L = rb.L
+    L.new_rng_pool.restype, L.new_rng_pool.argtypes = C.c_void_p, [C.c_int, C.c_int, C.c_int]
+    L.langevin.restype, L.langevin.argtypes = C.c_void_p, [C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_int]
+    L.apply_collision_op_list.restype, L.apply_collision_op_list.argtypes = None, [C.c_void_p]
+    rp = L.new_rng_pool(64, seed, 0)
+    return L.langevin(kT, nu, sp, rp, interval)
+
+
+def test_langevin_operator_deterministic_part_and_statistics():
+    """src/collision/pipeline/langevin_pipeline.c: with kT = 0 the operator is the pure decay u *= exp(-nu dt interval)
+    (the deviates are multiplied by a zero drive): oracle == reference bit for bit, also for the interval gate.
+    With kT > 0 the reference's result must have the moments the oracle's arithmetic gives with its own deviates."""
+    from vpic_b200 import abi
+    so, sr = pair(kind="periodic", n=(12, 10, 8))
+    a, b = so.species[0], sr.species[0]
+    lo = abi.Langevin(C.cast(a, C.c_void_p).value if not isinstance(a, int) else a, None, 0.0, 3.0, 2)
+    cop = ref_langevin(sr.be, b, 0.0, 3.0, 2)
+    OL = H.oracle_backend().L
+    OL.orc_apply_langevin.restype, OL.orc_apply_langevin.argtypes = None, [C.c_void_p, C.c_void_p]
+    for step in range(3):                                 # steps 0 and 2 apply, step 1 is gated off
+        so.grid_struct(so.g).step = step; sr.grid_struct(sr.g).step = step
+        before = so.particles(a).copy()
+        OL.orc_apply_langevin(C.byref(lo), None)
+        sr.be.L.apply_collision_op_list(cop)
+        assert same_bits(so.particles(a), sr.particles(b)), step
+        assert (step == 1) == same_bits(so.particles(a), before)
+    # statistics: thermostat at kT with nu dt >> 1 resamples the momenta: variance kT/(m c) per component
+    kT, nu = 0.04, 400.0
+    cop = ref_langevin(sr.be, b, kT, nu, 1, seed=11)
+    so.grid_struct(so.g).step = 4; sr.grid_struct(sr.g).step = 4
+    sr.be.L.apply_collision_op_list(cop)
+    n = so.sp_struct(a).np
+    rng = np.random.default_rng(2)
+    normals = rng.standard_normal(3 * n).astype(np.float32)
+    lo.kT, lo.nu, lo.interval = kT, nu, 1
+    OL.orc_apply_langevin(C.byref(lo), normals.ctypes.data_as(C.c_void_p))
+    m = so.sp_struct(a).m
+    for k in ("ux", "uy", "uz"):
+        for arr in (so.particles(a)[k], sr.particles(b)[k]):
+            assert abs(arr.mean()) < 5 * np.sqrt(kT / m / n)
+            assert abs(arr.var() / (kT / m) - 1) < 5 * np.sqrt(2.0 / n)

@@ -95,6 +95,10 @@ ParticleBC._fields_ = [("params", C.c_void_p), ("interact", C.c_void_p), ("delet
                        ("id", C.c_int64), ("next", C.POINTER(ParticleBC))]
 
 
+class Langevin(C.Structure):        # src/collision/langevin.h:6-13
+    _fields_ = [("sp", C.c_void_p), ("rp", C.c_void_p), ("kT", C.c_float), ("nu", C.c_float), ("interval", C.c_int)]
+
+
 class FieldArray(C.Structure):      # field_advance.h:223-229
     _fields_ = [("f", C.POINTER(Field)), ("g", C.POINTER(Grid)), ("params", C.c_void_p),
                 ("kernel", FieldAdvanceKernels * 1)]

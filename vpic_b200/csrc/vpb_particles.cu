@@ -100,6 +100,25 @@ k_load_maxwellian( vpb_particle_t * __restrict__ p, long long np, int ppc, GridD
   pp[1] = make_float4( vth*r1*cosf( a1 ), vth*r1*sinf( a1 ), vth*r2*cosf( a2 ), w );
 }
 
+// Langevin thermostat: u = decay u + drive N(0,1), three independent normal deviates per particle from a
+// counter-based generator (splitmix64 of (key, step, particle index): any particle's deviates can be
+// regenerated from its index alone, nothing to store, nothing shared between threads).
+__global__ void __launch_bounds__(256)
+k_langevin( vpb_particle_t * __restrict__ p, int np, float decay, float drive, uint64_t key, uint64_t step ) {
+  const int n = blockIdx.x*blockDim.x + threadIdx.x;
+  if( n>=np ) return;
+  const uint64_t h0 = splitmix64( key ^ splitmix64( step*0x9e3779b97f4a7c15ull + (uint64_t)n ) );
+  const uint64_t h1 = splitmix64( h0 ), h2 = splitmix64( h1 ), h3 = splitmix64( h2 );
+  const float r1 = sqrtf( -2.f*logf( u01( h0 ) ) ), r2 = sqrtf( -2.f*logf( u01( h1 ) ) );
+  const float a1 = 6.2831853f*u01( h2 ), a2 = 6.2831853f*u01( h3 );
+  float4 * q = reinterpret_cast<float4 *>( p + n ) + 1;
+  float4 u = *q;
+  u.x = decay*u.x + drive*( r1*cosf( a1 ) );
+  u.y = decay*u.y + drive*( r1*sinf( a1 ) );
+  u.z = decay*u.z + drive*( r2*cosf( a2 ) );
+  *q = u;
+}
+
 // Movers come out of advance_p in atomic-append order; the reference's order
 // (single pipeline) is ascending particle index, and boundary_p's back-fill
 // makes the final particle order depend on it.  Bitonic sort of the 16 B
@@ -211,6 +230,31 @@ static void half_step( vpb_species_t * sp, const vpb_interpolator_array_t * ia, 
 }
 void center_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia )   { half_step( sp, ia, false ); }
 void uncenter_p( vpb_species_t * sp, const vpb_interpolator_array_t * ia ) { half_step( sp, ia, true ); }
+
+// ---- Langevin thermostat (src/collision/pipeline/langevin_pipeline.c:20-42, 44-112) ----------------
+static uint64_t g_collision_seed = 0x5eedull;
+void vpic_b200_set_collision_seed( uint64_t seed ) { g_collision_seed = seed; }
+
+void apply_langevin_pipeline( vpb_langevin_t * l ) {
+  if( !l || !l->sp || !l->sp->g ) VPB_ERROR( "Bad args" );
+  vpb_species_t * sp = l->sp;
+  if( l->interval<1 || ( sp->g->step % l->interval ) ) return;                   // langevin_pipeline.c:47-51
+  Runtime & r = rt();
+  SpeciesMirror * ms = mirror( sp );
+  to_device( ms );
+  // langevin_pipeline.c:99-108 (float nudt; exp / expm1 / sqrt in double, rounded to float)
+  const float nudt = l->nu*(float)l->interval*sp->g->dt;
+  const float decay = (float)exp( -(double)nudt );
+  const float drive = (float)sqrt( ( -expm1( -2*(double)nudt )*l->kT )/( sp->m*sp->g->cvac ) );
+  if( ms->np>0 ) {
+    const uint64_t key = g_collision_seed ^ ( (uint64_t)(unsigned)g_world_rank<<48 ) ^ ( (uint64_t)(unsigned)sp->id<<40 );
+    k_langevin<<< div_up( ms->np, 256 ), 256, 0, r.stream >>>( ms->d_p, ms->np, decay, drive, key, (uint64_t)sp->g->step );
+    VPB_CHECK_LAUNCH(); r.launches++;
+  }
+  const bool keys = ms->keys_valid;            // momenta only: voxels, order and keys are untouched
+  finish_write( ms );
+  ms->keys_valid = keys;
+}
 
 void vpic_b200_load_uniform_maxwellian( vpb_species_t * sp, int ppc, float vth, float w, uint64_t seed ) {
   if( !sp || ppc<1 ) VPB_ERROR( "Bad args" );
