@@ -31,7 +31,7 @@ sys.path.insert(0, ROOT)
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=12)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", default="512x256x256", help="cells per GPU")
@@ -95,7 +95,14 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-NCU_DRAM_BYTES_PER_PUSH = 71.4   # measured, profiles/r1h_summary.md
+def measured_traffic():
+    """DRAM bytes per push of k_advance_p measured with ncu on THIS benchmark command at its full size
+    (tools/traffic_from_ncu.py from the launch CSV committed next to it), or None."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r2_fullsize_traffic.json")))
+    except Exception:
+        return None
+
 
 
 def dims(s):
@@ -144,6 +151,17 @@ class EventTimer:
         n = len(self.pairs)
         self.pairs = []
         return t, n
+
+
+def since_sort(launch_ms, first_step, sort_interval):
+    si = [int(x) for x in str(sort_interval).split(",")]
+    cad = {"electron": si[0], "ion": si[-1]}
+    out = {}
+    for j, ms in enumerate(launch_ms):
+        sp = "ion" if j % 2 == 0 else "electron"
+        k = (first_step + j // 2) % cad[sp] if cad[sp] > 0 else -1
+        out.setdefault(sp, {}).setdefault(k, []).append(ms)
+    return {sp: {str(k): round(sum(v) / len(v), 3) for k, v in sorted(d.items())} for sp, d in out.items()}
 
 
 def timed_steps(torch, sim, L, stream, steps, dist_barrier):
@@ -216,19 +234,25 @@ def run_b200(args):
     # roofline of the dominant kernel (advance_p): SURVEY 8d algorithmic bytes
     peak, peak_src = peaks()
     bytes_per_push = 64.0 + 176.0 / args.ppc
+    tr = measured_traffic()
     ach = np_total * args.steps * bytes_per_push / (ap_ms * 1e-3) / 1e9
     roofline = {"kernel": "k_advance_p", "bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(ach / peak, 4),
-                # ncu dram__bytes_read.sum + dram__bytes_write.sum of k_advance_p (profiles/r1h_summary.md:
-                # 71.4 B/push averaged over the ion and electron launches at 128^3), scaled to this launch size
-                "traffic": round(NCU_DRAM_BYTES_PER_PUSH * np_total / 2 / 1e9, 3), "traffic_unit": "GB per launch",
+                # ncu dram__bytes_read.sum + dram__bytes_write.sum of k_advance_p per launch, captured on this very command
+                # (512x256x256, default sort cadence; mean of the ion and electron launches of one electron sort interval)
+                "traffic": (round(tr["B_per_push"] * np_total / 2 / 1e9, 3) if tr and args.cells == "512x256x256" and args.ppc == 32 else None),
+                "traffic_unit": "GB per launch", "traffic_source": (tr or {}).get("source"),
+                "traffic_B_per_push": ({k: round(tr[k], 1) for k in ("ion_B_per_push", "electron_B_per_push")} if tr else None),
                 "achieved_unit_per_launch_GB": round(bytes_per_push * np_total / 2 / 1e9, 3), "peak_source": peak_src,
                 "bytes_per_push": bytes_per_push, "ms_per_launch": ap_ms / max(ap_calls, 1),
                 "pushes_per_s_kernel_only": np_total * args.steps / (ap_ms * 1e-3),
                 "share_of_step": round(ap_ms / ms, 4),
                 # advance() walks the species list head first (the species defined last): ion, electron, ion ...
                 "ms_per_launch_by_species": {"ion": sum(tm.last[0::2]) / max(len(tm.last[0::2]), 1),
-                                             "electron": sum(tm.last[1::2]) / max(len(tm.last[1::2]), 1)}}
+                                             "electron": sum(tm.last[1::2]) / max(len(tm.last[1::2]), 1)},
+                # launch time against the number of steps since the species' last sort_p (0 = the launch that gathers
+                # through the lazy sort's permutation): what the strays cost, and what the folded-in copy costs
+                "ms_by_steps_since_sort": since_sort(tm.last, args.warmup, args.sort_interval)}
     out = {"metric": "particle_pushes_per_sec", "value": value, "unit": "pushes/s", "n_gpus": world,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",

@@ -318,6 +318,16 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   const GridDev & g = m->grid->dev;
   const int np = m->np, nv = g.nv;
   if( !lazy ) sort_spare( m->cap_p );
+  else if( np>0 ) {
+    // everything the lazy path will ever need is allocated at the species' first sort (start-up), not in the
+    // middle of a run: the key array the advance_p before the next sort fills, and the spare particle buffer
+    if( m->cap_keys<m->cap_p ) {
+      VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+      if( m->d_keys ) VPB_CUDA( cudaFree( m->d_keys ) );
+      VPB_CUDA( cudaMalloc( &m->d_keys, sizeof(int)*m->cap_p ) ); m->cap_keys = m->cap_p; m->keys_valid = false;
+    }
+    sort_spare( m->cap_p );
+  }
   // scratch: keys[np] perm[np] count[nv+1] next[nv+1] tiles big[2np]
   const size_t npa = ( (size_t)np + 31 ) & ~(size_t)31, nva = ( (size_t)nv + 1 + 31 ) & ~(size_t)31;
   const size_t ntile = (size_t)div_up( nv+1, SCAN_TILE ) + 32;
