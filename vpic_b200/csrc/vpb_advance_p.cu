@@ -167,6 +167,15 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
   for( int k=0; k<12; k++ ) run[k] = 0.f;
   Interp f = {};
 
+  // GATHER: the source indices of the tile's slots, requested one tile ahead (the loads of the NEXT tile's
+  // indices are issued when this tile's pushes are done and land while it is stored)
+  int sidx[GATHER ? AP_K : 1];
+  auto load_indices = [&]( int tile ) {
+    const long long t0 = (long long)tile*AP_TILE;
+#   pragma unroll
+    for( int i=0; i<( GATHER ? AP_K : 1 ); i++ ) { const long long d = t0 + 32*i + lane; sidx[i] = ( tile<ntile && d<np ) ? __ldg( perm + d ) : -1; }
+  };
+  if( GATHER ) load_indices( gw );
   if( AP_NBUF>1 && lane==0 ) start_load( gw, 0 );
   for( int tile=gw; tile<ntile; tile+=total_warps ) {
     const long long t0 = (long long)tile*AP_TILE;
@@ -175,21 +184,24 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
     float4 * __restrict__ T = S.tile[buf];
     auto on_chip = [&]( int rel ) -> float4 * { return ( rel>=t0 && rel<t0+cnt ) ? &T[ 2*(int)( rel-t0 ) ] : nullptr; };
     if( GATHER ) {
-      // 32 consecutive slots per step: coalesced index loads, one 256-bit record load per lane
-      // (consecutive for the particles that did not move since the last sort), conflict-free stores
-      int sidx[AP_K];
-#     pragma unroll
-      for( int i=0; i<AP_K; i++ ) { const int d = 32*i + lane; sidx[i] = d<cnt ? __ldg( perm + t0 + d ) : -1; }
+      // 32 consecutive slots per step: coalesced index loads, then every particle record goes from global to
+      // shared memory as two 16-byte asynchronous copies (cp.async: no registers, no wait between them -- with
+      // plain loads each record's shared store waited for its own load, eight exposed latencies per tile, and
+      // the launch was 26 % slower than a push of the same particles in place); consecutive lanes fill
+      // consecutive 32 B of the tile, and read consecutive records for the particles that did not move since
+      // the last sort.
 #     pragma unroll
       for( int i=0; i<AP_K; i++ ) {
         const int d = 32*i + lane;
         if( sidx[i]>=0 ) {
-          float4 a, b;
-          asm volatile( "ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(src + sidx[i]) );
-          T[2*d] = a; T[2*d+1] = b;
+          const uint32_t dst = smem_u32( &T[2*d] );
+          const char * s8 = reinterpret_cast<const char *>( src + sidx[i] );
+          asm volatile( "cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst),      "l"(s8)      : "memory" );
+          asm volatile( "cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst+16u),  "l"(s8+16)   : "memory" );
         }
       }
+      asm volatile( "cp.async.commit_group;" ::: "memory" );
+      asm volatile( "cp.async.wait_group 0;" ::: "memory" );
       __syncwarp();
     } else {
       const uint32_t bar = smem_u32( &S.bar[buf] );
@@ -302,6 +314,7 @@ k_advance_p( vpb_particle_t * __restrict__ p, int np, int ntile, int idx_base,
         __syncwarp();
       }
     }
+    if( GATHER ) load_indices( tile+total_warps );
     if( KEYS ) {
       // the voxel index is the 4th word of every record of the tile: 32 consecutive keys per store
       // (particles that left the domain carry 8*voxel+face and are boundary_p's, which invalidates the keys)

@@ -93,25 +93,36 @@ void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n ) {
 
 // ---- sort kernels ----------------------------------------------------------
 
+// One thread per particle and chunk, SORT_CHUNKS chunks of 256 consecutive particles per block: with one chunk
+// per block the 262 144 tiny blocks of a 67 M particle species were bound by the block launch rate (228 us for
+// the key histogram against 45 us of traffic), not by their atomics.
+constexpr int SORT_CHUNKS = 16;
+
 __global__ void __launch_bounds__(256)
 k_sort_hist( const vpb_particle_t * __restrict__ p, int np, int * __restrict__ keys, int * __restrict__ count ) {
-  const int i = blockIdx.x*blockDim.x + threadIdx.x;
-  const int key = i<np ? p[i].i : -1;
-  if( i<np ) keys[i] = key;
-  const unsigned m = __match_any_sync( 0xffffffffu, key );
-  if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+  for( int c=0; c<SORT_CHUNKS; c++ ) {
+    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
+    if( i - threadIdx.x>=np ) return;
+    const int key = i<np ? p[i].i : -1;
+    if( i<np ) keys[i] = key;
+    const unsigned m = __match_any_sync( 0xffffffffu, key );
+    if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+  }
 }
 
 __global__ void __launch_bounds__(256)
 k_sort_scatter_idx( const int * __restrict__ keys, int np, int * __restrict__ next, int * __restrict__ perm ) {
-  const int i = blockIdx.x*blockDim.x + threadIdx.x;
-  const int key = i<np ? keys[i] : -1;
-  const unsigned m = __match_any_sync( 0xffffffffu, key );
-  const int lane = threadIdx.x & 31, leader = __ffs( m )-1;
-  int base = 0;
-  if( key>=0 && lane==leader ) base = atomicAdd( next + key, __popc( m ) );
-  base = __shfl_sync( 0xffffffffu, base, leader );
-  if( key>=0 ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = i;
+  for( int c=0; c<SORT_CHUNKS; c++ ) {
+    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
+    if( i - threadIdx.x>=np ) return;
+    const int key = i<np ? keys[i] : -1;
+    const unsigned m = __match_any_sync( 0xffffffffu, key );
+    const int lane = threadIdx.x & 31, leader = __ffs( m )-1;
+    int base = 0;
+    if( key>=0 && lane==leader ) base = atomicAdd( next + key, __popc( m ) );
+    base = __shfl_sync( 0xffffffffu, base, leader );
+    if( key>=0 ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = (int)i;
+  }
 }
 
 // Ascending sort of every voxel's segment of perm[].  One warp per voxel.
@@ -132,7 +143,7 @@ __device__ __forceinline__ void copy_particle( vpb_particle_t * __restrict__ out
 // Segments of <= 32*FIX_E indices sort in registers (a bitonic network of 32,
 // 64 or 128 elements, chosen per segment), larger ones fall back to the
 // bitonic sorts in shared or global memory.
-constexpr int FIX_E = 4;
+constexpr int FIX_E = 4, FIX_REP = 8;
 
 // Bitonic sort of 32*E ints held E per lane (element index 32k+lane): strides
 // of 32 and up exchange registers of one lane, shorter strides use shuffles.
@@ -191,23 +202,27 @@ k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __r
                    const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out, int * __restrict__ out_perm ) {
   __shared__ int s[FIX_WARPS][FIX_SMEM];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int v = blockIdx.x*FIX_WARPS + w;
-  if( v>=nv ) return;
-  const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
-  if( n<=0 ) return;
-  // Segments up to 32*FIX_E indices sort in registers, with a network sized for
-  // the segment (ne is warp uniform); lane l of slot k then holds rank 32k+l.
-  if( n<=32 )       { fix_gather_regs<1,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
-  if( n<=64 )       { fix_gather_regs<2,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
-  if( n<=32*FIX_E ) { fix_gather_regs<FIX_E,GATHER>( perm, b, n, lane, in, out, out_perm ); return; }
-  int n2 = 64; while( n2<n ) n2 <<= 1;
-  int * a;
-  if( n2<=FIX_SMEM ) a = s[w];
-  else a = big_scratch + 2*(size_t)b;     // window of n2 < 2n ints starting at 2b: windows of different voxels are disjoint
-  for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
-  __threadfence_block(); __syncwarp();
-  bitonic_mem( a, n2, lane );
-  for( int t=lane; t<n; t+=32 ) { if( GATHER ) copy_particle( out, b+t, in, a[t] ); else out_perm[b+t] = a[t]; }
+  // FIX_REP consecutive voxels per warp (a block per 4 voxels was launch-rate bound like the kernels above)
+  for( int rep=0; rep<FIX_REP; rep++ ) {
+    const int v = ( blockIdx.x*FIX_REP + rep )*FIX_WARPS + w;
+    if( v>=nv ) return;
+    const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
+    if( n<=0 ) continue;
+    // Segments up to 32*FIX_E indices sort in registers, with a network sized for
+    // the segment (ne is warp uniform); lane l of slot k then holds rank 32k+l.
+    if( n<=32 )       { fix_gather_regs<1,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
+    if( n<=64 )       { fix_gather_regs<2,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
+    if( n<=32*FIX_E ) { fix_gather_regs<FIX_E,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
+    int n2 = 64; while( n2<n ) n2 <<= 1;
+    int * a;
+    if( n2<=FIX_SMEM ) a = s[w];
+    else a = big_scratch + 2*(size_t)b;     // window of n2 < 2n ints starting at 2b: windows of different voxels are disjoint
+    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+    __threadfence_block(); __syncwarp();
+    bitonic_mem( a, n2, lane );
+    for( int t=lane; t<n; t+=32 ) { if( GATHER ) copy_particle( out, b+t, in, a[t] ); else out_perm[b+t] = a[t]; }
+    __syncwarp();
+  }
 }
 
 // out[d] = in[ perm[d] ]: carries out a lazy sort that no advance_p consumed
@@ -219,10 +234,13 @@ k_sort_apply_perm( const int * __restrict__ perm, int np, const vpb_particle_t *
 
 __global__ void __launch_bounds__(256)
 k_hist_keys( const int * __restrict__ keys, int n, int * __restrict__ count ) {
-  const int i = blockIdx.x*blockDim.x + threadIdx.x;
-  const int key = i<n ? keys[i] : -1;
-  const unsigned m = __match_any_sync( 0xffffffffu, key );
-  if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+  for( int c=0; c<SORT_CHUNKS; c++ ) {
+    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
+    if( i - threadIdx.x>=n ) return;
+    const int key = i<n ? keys[i] : -1;
+    const unsigned m = __match_any_sync( 0xffffffffu, key );
+    if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+  }
 }
 
 void bin_indices( const int * keys, int n, int nbin, int * start, int * perm ) {
@@ -232,9 +250,9 @@ void bin_indices( const int * keys, int n, int nbin, int * start, int * perm ) {
   int * base = (int *)scratch( sizeof(int)*( 2*nba + ntile + 64 ) );
   int * count = base, * next = count + nba, * tiles = next + nba;
   VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nbin+1 ), r.stream ) );
-  if( n>0 ) { k_hist_keys<<< div_up(n,256), 256, 0, r.stream >>>( keys, n, count ); r.launches++; }
+  if( n>0 ) { k_hist_keys<<< div_up(n,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, n, count ); r.launches++; }
   exclusive_scan( count, start, next, tiles, nbin+1 );
-  if( n>0 ) { k_sort_scatter_idx<<< div_up(n,256), 256, 0, r.stream >>>( keys, n, next, perm ); r.launches++; }
+  if( n>0 ) { k_sort_scatter_idx<<< div_up(n,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, n, next, perm ); r.launches++; }
   VPB_CHECK_LAUNCH();
 }
 
@@ -337,23 +355,23 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   if( np>0 ) {
     if( lazy && m->keys_valid && m->d_keys ) {       // the keys are already there: 4 B per particle instead of 32
       keys = m->d_keys;
-      k_hist_keys<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, count );
-    } else k_sort_hist<<< div_up(np,256), 256, 0, r.stream >>>( m->d_p, np, keys, count );
+      k_hist_keys<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, np, count );
+    } else k_sort_hist<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( m->d_p, np, keys, count );
     VPB_CHECK_LAUNCH(); r.launches++;
   }
   exclusive_scan( count, m->d_partition, next, tiles, nv+1 );
   if( np>0 ) {
-    k_sort_scatter_idx<<< div_up(np,256), 256, 0, r.stream >>>( keys, np, next, perm );
+    k_sort_scatter_idx<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, np, next, perm );
     if( lazy ) {
       if( m->cap_perm<m->cap_p ) {
         VPB_CUDA( cudaStreamSynchronize( r.stream ) );
         if( m->d_perm ) VPB_CUDA( cudaFree( m->d_perm ) );
         VPB_CUDA( cudaMalloc( &m->d_perm, sizeof(int)*m->cap_p ) ); m->cap_perm = m->cap_p;
       }
-      k_sort_fix_gather<false><<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, nullptr, m->d_perm );
+      k_sort_fix_gather<false><<< div_up(nv,FIX_WARPS*FIX_REP), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, nullptr, m->d_perm );
       m->perm_pending = true;
     } else {
-      k_sort_fix_gather<true><<< div_up(nv,FIX_WARPS), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt, nullptr );
+      k_sort_fix_gather<true><<< div_up(nv,FIX_WARPS*FIX_REP), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt, nullptr );
       sort_swap_spare( m );            // swap the species buffer with the spare
     }
     VPB_CHECK_LAUNCH(); r.launches += 2;
