@@ -147,6 +147,9 @@ int  vpic_b200_comm_transport( void );
    order or outside the segment sp->partition gives their voxel (0 expected; -1 if
    the device holds no partition).  Lets tests check sort_p at sizes no CPU oracle reaches. */
 long long vpic_b200_sort_violations( vpb_species_t * sp );
+/* Diagnostic: how many sort_p calls of this process read the 4-byte voxel keys the
+   preceding advance_p wrote (and boundary_p patched) instead of the particle records. */
+long long vpic_b200_sorts_from_keys( void );
 void vpic_b200_finalize( void );
 /* frees the grow-on-demand device caches (sort_p spare buffer, scratch, boundary_p
    message buffers); objects and their mirrors stay valid */

@@ -117,6 +117,9 @@ def main():
     ap.add_argument("--localised", action="store_true",
                     help="all particles start in rank 0's brick: with 3 or more ranks along an axis some neighbour pairs "
                          "have nothing to exchange while others do (per-pair message decisions of boundary_p)")
+    ap.add_argument("--resident", action="store_true",
+                    help="gpu mode: RESIDENT coherence with sort_interval 2 -- the lazy sort_p (index order + gather in "
+                         "advance_p) with the voxel keys that boundary_p patches where it removes and appends particles")
     args = ap.parse_args()
     global LOCALISED
     LOCALISED = args.localised
@@ -142,12 +145,12 @@ def main():
         global LOCALISED_LN
         LOCALISED_LN = tuple(gn[a] // topo[a] for a in range(3))
         H.set_world(rank, world)
-        so, origin, ln = build(H.oracle_backend(), kind, gn, topo, rank, 6, 40)
+        so, origin, ln = build(H.oracle_backend(), kind, gn, topo, rank, 6, 40, sort_interval=2 if args.resident else 3)
         H.install_gloo_exchange(so)
         if args.mode == "oracle":
             ok &= check_oracle(H, so, origin, ln, kind, gn, topo, rank, world, args.steps, dist)
         else:
-            ok &= check_gpu(H, so, kind, gn, topo, rank, world, args.steps, dist, torch)
+            ok &= check_gpu(H, so, kind, gn, topo, rank, world, args.steps, dist, torch, resident=args.resident)
         dist.barrier()
     flag = torch.tensor([1 if ok else 0]); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
@@ -265,7 +268,7 @@ def check_oracle(H, so, origin, ln, kind, gn, topo, rank, world, steps, dist):
     return ok
 
 
-def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None):
+def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None, resident=False):
     from vpic_b200 import load_b200, b200_backend
     from common import same_bits
     L = load_b200()
@@ -293,11 +296,14 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
         return False
     if rank == 0:
         print("transport:", "put (NVLink peer-memory mailboxes)" if want else "ncclSend/ncclRecv")
-    L.vpic_b200_set_coherence(0)
-    sg, origin, ln = build(b200_backend(), kind, gn, topo, rank, 6, 40)
+    L.vpic_b200_set_coherence(1 if resident else 0)
+    keys0 = L.vpic_b200_sorts_from_keys()
+    sg, origin, ln = build(b200_backend(), kind, gn, topo, rank, 6, 40, sort_interval=2 if resident else 3)
     for s in (so, sg):
         with_cleaning(s)
     sg.fields()[:] = so.fields(); sg.interpolators()[:] = so.interpolators()      # rhof / rhob: float atomics
+    if resident:
+        L.vpic_b200_sync_from_host(sg.fa); L.vpic_b200_sync_from_host(sg.ia)
     ok = True
     for k in ("div_b", "sync0", "sync1"):        # div_e is rounding noise here: rhob was just chosen to cancel it
         if not np.isclose(sg.init_report[k], so.init_report[k], rtol=1e-4, atol=1e-12):
@@ -305,6 +311,9 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
     nv = so.grid_struct(so.g).nv
     for step in range(steps):
         so.advance(); sg.advance()
+        if resident:
+            for obj in [sg.fa, sg.ia] + sg.species:
+                L.vpic_b200_sync_to_host(obj)
         for k in ("ex", "ey", "ez", "cbx", "cby", "cbz", "jfx", "jfy", "jfz", "rhob", "rhof", "tcax", "tcay", "tcaz"):
             if not close(sg.fields()[k], so.fields()[k], 5e-5):
                 print(f"rank {rank} {kind} {topo} step {step}: field {k} differs"); ok = False
@@ -319,11 +328,14 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
                 # positions of migrated particles depend on currents only through E,B of later steps; with the
                 # per-step re-synchronisation below they must be bit-identical
                 print(f"rank {rank} {kind} {topo} step {step}: particle bits differ"); ok = False
-            sg.particles(b)[:] = po
+            if not resident:
+                sg.particles(b)[:] = po
         if not ok:
             break
         sg.fields()[:] = so.fields()
         sg.interpolators()[:] = so.interpolators()
+        if resident:                                  # (the particles stay where they are: the device copy, its keys and order)
+            L.vpic_b200_sync_from_host(sg.fa); L.vpic_b200_sync_from_host(sg.ia)
     for a, b in zip(so.species, sg.species):      # dump_hydro's three calls; the node planes shared with the neighbour rank travel over NCCL
         ho, hg = so.hydro_moments(a), sg.hydro_moments(b)
         for k in ho.dtype.names[:14]:
@@ -333,6 +345,14 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
     t = torch.from_numpy(eo.copy()); dist.all_reduce(t, group=group)
     if not np.allclose(eg, t.numpy(), rtol=1e-6):
         print(f"rank {rank} {kind} {topo}: energies differ", eg, t.numpy()); ok = False
+    if resident:
+        # every sort after the first of each species read the voxel keys (sort_interval 2: steps 2, 4, ...), although
+        # boundary_p moved particles in and out in between
+        want = len(sg.species) * ((steps - 1) // 2)
+        got = L.vpic_b200_sorts_from_keys() - keys0
+        if got < want:
+            print(f"rank {rank} {kind} {topo}: {got} sorts took the key array, expected {want}"); ok = False
+        L.vpic_b200_set_coherence(0)
     return ok
 
 

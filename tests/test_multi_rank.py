@@ -116,3 +116,14 @@ def test_ranks_sharing_one_gpu_match_the_n_rank_oracle(nproc, extra):
     peer stores land in the same HBM instead of crossing NVLink."""
     launch("gpu", nproc=nproc, extra=extra, timeout=1500, VPIC_B200_TRANSPORT="put", VPB_TEST_BOOTSTRAP="handles",
            VPIC_B200_PUT_TIMEOUT_S="120")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nproc", [2, 4])
+def test_ranks_sharing_one_gpu_resident_lazy_sort_match_the_n_rank_oracle(nproc):
+    """RESIDENT coherence, sort every second step: sort_p orders indices only, advance_p gathers through them and
+    leaves the voxel keys for the next sort, and boundary_p -- which removes the emigrants (back-fill) and appends
+    the immigrants -- patches those keys instead of invalidating them.  Particle order, voxels and bits against
+    the N-rank oracle after every step."""
+    launch("gpu", nproc=nproc, extra=("--resident",), timeout=1500, VPIC_B200_TRANSPORT="put", VPB_TEST_BOOTSTRAP="handles",
+           VPIC_B200_PUT_TIMEOUT_S="120")

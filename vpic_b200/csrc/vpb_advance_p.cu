@@ -428,7 +428,7 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
   }
   VPB_CUDA( cudaStreamSynchronize( r.copy_stream[1] ) );
   ms->dev_valid = true; ms->host_valid = true; ms->partition_dev_valid = false;
-  ms->perm_pending = false; ms->keys_valid = false;
+  ms->perm_pending = false; ms->keys_valid = ms->keys_patchable = false;
   track_arm( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
   return true;
 }
@@ -491,7 +491,11 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   if( ms->nm>1 ) sort_movers_by_index( ms );
   ms->movers_sorted = true;
   if( !streamed ) mark_dev_written( ms );
-  ms->keys_valid = keys_written && ms->nm==0;        // particles on the mover list carry 8*voxel+face, and boundary_p will move things
+  // Particles on the mover list carry 8*voxel+face: their keys are wrong until boundary_p has removed them, which
+  // patches d_keys at the holes it fills and the records it appends (k_keys_patch).  A mover that did not fit the
+  // list (cnt[1]) is in that state for good.
+  ms->keys_valid     = keys_written && ms->nm==0 && !cnt[1];
+  ms->keys_patchable = keys_written && ms->nm>0  && !cnt[1];
   mark_dev_written( ma );
   movers_to_host( ms );
   if( r.coherence==VPB_COHERENCE_STRICT ) { to_host( ms ); to_host( ma ); }

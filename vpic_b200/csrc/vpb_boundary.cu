@@ -192,6 +192,17 @@ k_bnd_backfill( vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __
   reinterpret_cast<float4 *>( p + hole )[1] = b;
 }
 
+// advance_p wrote the voxel key of every particle for the lazy sort_p (vpb_sort.cu) before boundary_p moved things:
+// refresh the keys of the records boundary_p wrote -- the holes a tail particle filled (movers, n>0: the indices
+// pm[k].i below new_np) or the records appended by the injection (pm==nullptr: the range [first,first+n)).
+__global__ void __launch_bounds__(256)
+k_keys_patch( int * __restrict__ keys, const vpb_particle_t * __restrict__ p, const vpb_particle_mover_t * __restrict__ pm, int n, int first, int new_np ) {
+  const int k = blockIdx.x*blockDim.x + threadIdx.x;
+  if( k>=n ) return;
+  const int i = pm ? pm[k].i : first + k;
+  if( i<new_np ) keys[i] = p[i].i;
+}
+
 struct BndInject {
   const vpb_particle_injector_t * recv[7];
   int start[8];                        // prefix sums of the counts: local handler injectors, then faces 0..5
@@ -665,6 +676,12 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     if( sp->id<0 || sp->id>=BND_MAX_SP ) VPB_ERROR( "species id %d is outside the device boundary handler's range", sp->id );
   }
   if( sparse ) sparse_upload( ss );
+  // species whose voxel keys (written by advance_p for the lazy sort_p) are worth keeping current
+  std::vector<char> patch( sps.size(), 0 );
+  if( !sparse ) for( size_t k=0; k<sps.size(); k++ ) {
+    const SpeciesMirror * m = sps[k];
+    patch[k] = ( m->keys_valid || m->keys_patchable ) && m->d_keys && m->cap_keys>=m->cap_p;
+  }
   GridMirror * gm = particle_grid( sps[0]->grid );
   const GridDev & g = gm->dev;
   bool any_remote = false;
@@ -718,7 +735,8 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     bf.custom = B.custom;
   }
   bool touched_rhob = false;
-  for( SpeciesMirror * m : sps ) {
+  for( size_t ks=0; ks<sps.size(); ks++ ) {
+    SpeciesMirror * m = sps[ks];
     if( m->nm<=0 ) continue;
     if( !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     const vpb_species_t * sp = m->host;
@@ -733,6 +751,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     }
     k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
     VPB_CHECK_LAUNCH(); r.launches += 2;
+    if( patch[ks] ) { k_keys_patch<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_keys, m->d_p, m->d_pm, m->nm, 0, m->np-m->nm ); r.launches++; }
     if( any_absorb ) touched_rhob = true;
     m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
     mark_dev_written( m );
@@ -829,10 +848,16 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
     d2h( h_cnt, B.d_int+32, sizeof(h_cnt), r.stream );
     VPB_CUDA( cudaStreamSynchronize( r.stream ) );
     if( h_cnt[3*BND_MAX_SP] ) VPB_WARNING( "Dropped %d received particles of unknown species", h_cnt[3*BND_MAX_SP] );
-    for( SpeciesMirror * m : sps ) {
+    for( size_t ks=0; ks<sps.size(); ks++ ) {
+      SpeciesMirror * m = sps[ks];
       const int id = m->host->id;
+      if( patch[ks] && h_cnt[id]>0 ) {
+        if( m->cap_keys<m->cap_p ) patch[ks] = 0;            // the particle array grew past the key array
+        else { k_keys_patch<<< div_up( h_cnt[id], 256 ), 256, 0, r.stream >>>( m->d_keys, m->d_p, nullptr, h_cnt[id], m->np, m->np+h_cnt[id] ); r.launches++; }
+      }
       m->np += h_cnt[id];
       const int app = h_cnt[BND_MAX_SP+id], drop = h_cnt[2*BND_MAX_SP+id];
+      if( drop ) patch[ks] = 0;                              // a particle stuck with 8*voxel+face and no mover
       if( drop ) VPB_WARNING( "%i particles were not completed moved to their final location this timestep for species \"%s\"", drop, m->host->name );
       m->nm += app - drop;
       if( app-drop>0 ) m->movers_sorted = false;
@@ -842,7 +867,10 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   }
   if( touched_rhob ) mark_dev_written( mf );
 
-  for( SpeciesMirror * m : sps ) {
+  VPB_CHECK_LAUNCH();
+  for( size_t ks=0; ks<sps.size(); ks++ ) {
+    SpeciesMirror * m = sps[ks];
+    if( patch[ks] ) { m->keys_valid = m->nm==0; m->keys_patchable = m->nm>0; }
     m->host->np = m->np;
     if( m->nm>1 && !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     movers_to_host( m );
@@ -886,9 +914,12 @@ extern "C" int vpic_b200_drop_unprocessed_movers( vpb_species_t * sp_list, vpb_f
     k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16, true );
     k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
     VPB_CHECK_LAUNCH(); r.launches += 2;
+    const bool patch = m->keys_patchable && m->d_keys && m->cap_keys>=m->cap_p;
+    if( patch ) { k_keys_patch<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_keys, m->d_p, m->d_pm, m->nm, 0, m->np-m->nm ); VPB_CHECK_LAUNCH(); r.launches++; }
     dropped += m->nm;
     m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
     mark_dev_written( m );
+    m->keys_valid = patch;
     sp->np = m->np;
     movers_to_host( m );
     if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );

@@ -153,7 +153,7 @@ void to_device( SpeciesMirror * m, bool keep_lazy_sort ) {
     if( !keep_lazy_sort ) materialize_sort( m );
     return;
   }
-  m->perm_pending = false; m->keys_valid = false;      // the host copy replaces whatever the device held
+  m->perm_pending = false; m->keys_valid = m->keys_patchable = false;      // the host copy replaces whatever the device held
   m->np = m->host->np; m->nm = m->host->nm;
   pin_host( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np );
   if( m->np>0 )

@@ -169,6 +169,7 @@ struct SpeciesMirror {
   // Voxel index of every particle as the last advance_p left it (written by the launch that precedes
   // a sort_p); valid until anything else moves, adds or removes particles (mark_dev_written).
   int * d_keys = nullptr; size_t cap_keys = 0; bool keys_valid = false;
+  bool keys_patchable = false;       // d_keys is right for every particle that is not on the mover list (boundary_p patches the rest)
 };
 
 struct Runtime {
@@ -184,6 +185,7 @@ struct Runtime {
   void * d_scratch = nullptr; size_t scratch_bytes = 0;
   void * h_pinned = nullptr;  size_t pinned_bytes = 0;
   long long launches = 0;             // kernels launched (for bench's gpu_launches)
+  long long sorts_from_keys = 0;      // lazy sort_p calls that took the voxel keys advance_p / boundary_p left (4 B per particle read)
   long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued by the entry points
   std::unordered_map<const void *, size_t>          pinned_host;   // host arrays registered with cudaHostRegister
   std::unordered_map<const void *, GridMirror *>    grids;
@@ -236,7 +238,7 @@ void release_lazy_sort( SpeciesMirror * m );
 void to_device( HydroMirror * m );   void to_host( HydroMirror * m );
 void movers_to_host( SpeciesMirror * m );
 template<class M> inline void mark_dev_written( M * m ) { m->dev_valid = true; m->host_valid = false; }
-inline void mark_dev_written( SpeciesMirror * m ) { m->dev_valid = true; m->host_valid = false; m->keys_valid = false; }
+inline void mark_dev_written( SpeciesMirror * m ) { m->dev_valid = true; m->host_valid = false; m->keys_valid = m->keys_patchable = false; }
 // In STRICT mode every entry point finishes by pushing what it wrote back.
 template<class M> inline void finish_write( M * m ) {
   mark_dev_written( m );

@@ -299,13 +299,13 @@ void materialize_sort( SpeciesMirror * m ) {
   k_sort_apply_perm<<< div_up( m->np, 256 ), 256, 0, r.stream >>>( m->d_perm, m->np, m->d_p, out );
   VPB_CHECK_LAUNCH(); r.launches++;
   sort_swap_spare( m );
-  m->keys_valid = false;                 // d_keys is in the old order
+  m->keys_valid = m->keys_patchable = false;   // d_keys is in the old order
 }
 
 void release_lazy_sort( SpeciesMirror * m ) {
   if( m->d_perm ) cudaFree( m->d_perm );
   if( m->d_keys ) cudaFree( m->d_keys );
-  m->d_perm = m->d_keys = nullptr; m->cap_perm = m->cap_keys = 0; m->perm_pending = m->keys_valid = false;
+  m->d_perm = m->d_keys = nullptr; m->cap_perm = m->cap_keys = 0; m->perm_pending = m->keys_valid = m->keys_patchable = false;
 }
 
 static int lazy_sort_enabled() {
@@ -342,7 +342,7 @@ extern "C" void sort_p( vpb_species_t * sp ) {
     if( m->cap_keys<m->cap_p ) {
       VPB_CUDA( cudaStreamSynchronize( r.stream ) );
       if( m->d_keys ) VPB_CUDA( cudaFree( m->d_keys ) );
-      VPB_CUDA( cudaMalloc( &m->d_keys, sizeof(int)*m->cap_p ) ); m->cap_keys = m->cap_p; m->keys_valid = false;
+      VPB_CUDA( cudaMalloc( &m->d_keys, sizeof(int)*m->cap_p ) ); m->cap_keys = m->cap_p; m->keys_valid = m->keys_patchable = false;
     }
     sort_spare( m->cap_p );
   }
@@ -354,7 +354,7 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nv+1 ), r.stream ) );
   if( np>0 ) {
     if( lazy && m->keys_valid && m->d_keys ) {       // the keys are already there: 4 B per particle instead of 32
-      keys = m->d_keys;
+      keys = m->d_keys; r.sorts_from_keys++;
       k_hist_keys<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, np, count );
     } else k_sort_hist<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( m->d_p, np, keys, count );
     VPB_CHECK_LAUNCH(); r.launches++;
@@ -382,6 +382,8 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   m->perm_pending = keep;
   if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
 }
+
+extern "C" long long vpic_b200_sorts_from_keys( void ) { return rt().sorts_from_keys; }
 
 // Number of particles that violate "sorted by voxel, partition[] consistent".
 // Meaningful right after sort_p (0 expected).  Test / diagnostic entry point.
