@@ -657,11 +657,23 @@ def test_tracked_coherence_equals_strict_and_skips_clean_uploads(gpu):
     L = load_b200()
     import ctypes as C
 
-    def run(mode):
+    def run(mode, hostile=False):
         L.vpic_b200_set_coherence(mode)
         L.vpic_b200_set_deposit_mode(1)
         try:
             s = make_sim(gpu, None, kind="periodic", n=(40, 36, 30), ppc=12, sort_interval=3)
+            own = []
+            if hostile:
+                # The particle arrays at odd offsets of ONE allocation, 96 bytes of somebody else's data between
+                # them that is written every step: the arrays' first and last pages are shared with it.
+                nbytes = [s.sp_struct(sp).max_np * 32 for sp in s.species]
+                arena = np.zeros(sum(nbytes) + 96 * 3 + 8192, dtype=np.uint8)
+                at = arena.ctypes.data + 96
+                for sp, nb in zip(s.species, nbytes):
+                    st = s.sp_struct(sp)
+                    own.append((st, C.cast(st.p, C.c_void_p).value))
+                    st.p = C.cast(at, type(st.p))
+                    at += nb + 96
             for k, sp in enumerate(s.species):
                 random_particles(s, sp, 12, 0.2, 300 + k)
             s.fields()[:] = random_fields(s, 9)
@@ -669,6 +681,11 @@ def test_tracked_coherence_equals_strict_and_skips_clean_uploads(gpu):
             b0 = (C.c_longlong * 2)(); L.vpic_b200_transfer_bytes(b0)
             for step in range(6):
                 s.advance()
+                if hostile:
+                    off = 0
+                    for nb in nbytes:
+                        arena[off:off + 96] = step + 1; off += 96 + nb
+                    arena[off:off + 96] = step + 1
                 if step == 1:                                   # the host program edits its arrays in place
                     s.fields()["ex"][1000:1400] += np.float32(0.01)
                     s.particles(s.species[0])["ux"][7::1001] += np.float32(0.05)
@@ -677,6 +694,10 @@ def test_tracked_coherence_equals_strict_and_skips_clean_uploads(gpu):
                     s.particles(s.species[1])["dz"][11::977] = np.float32(0.25)
             b1 = (C.c_longlong * 2)(); L.vpic_b200_transfer_bytes(b1)
             out = (s.fields().copy(), [s.particles(sp).copy() for sp in s.species], s.energies())
+            for sp in s.species:
+                L.vpic_b200_forget(sp)
+            for st, ptr in own:                                 # the library frees what it allocated
+                st.p = C.cast(ptr, type(st.p))
             for sp in s.species:
                 L.vpic_b200_delete_species(sp)
             L.vpic_b200_delete_interpolator_array(s.ia); L.vpic_b200_delete_accumulator_array(s.aa)
@@ -693,6 +714,13 @@ def test_tracked_coherence_equals_strict_and_skips_clean_uploads(gpu):
     assert e1 == e0
     assert abs(down1 - down0) <= 0.01 * down0  # the host copy is kept current exactly as in STRICT mode
     assert up1 < 0.35 * up0, (up0, up1)       # ... but only what the host wrote goes up again
+    # neighbours that share the arrays' edge pages and are written all the time cost nothing: only whole pages
+    # inside an array are protected, the fragments at its ends are compared against a copy
+    (f2, p2, e2), up2, down2 = run(2, hostile=True)
+    assert same_bits(f2, f0) and e2 == e0
+    for a, b in zip(p0, p2):
+        assert same_bits(b, a)
+    assert up2 < 0.35 * up0, (up0, up2)
 
 
 def test_tracked_coherence_streamed_advance_p(gpu):

@@ -287,11 +287,15 @@ void release_sort_buffers();
 __global__ void k_sum_partials( double * out, const double * partial, int nblock, int ncomp, double scale );
 
 // every host<->device copy of the library goes through these two (byte accounting for bench.py's e2e)
+// VPIC_B200_TRACE_TRANSFERS=1: one line on stderr per transfer of 1 MB or more (which arrays a coherence mode moves)
+inline bool trace_transfers() { static const bool on = getenv( "VPIC_B200_TRACE_TRANSFERS" )!=nullptr; return on; }
 inline void h2d( void * dst, const void * src, size_t bytes, cudaStream_t st ) {
   VPB_CUDA( cudaMemcpyAsync( dst, src, bytes, cudaMemcpyHostToDevice, st ) ); rt().h2d_bytes += (long long)bytes;
+  if( bytes>=( 1u<<20 ) && trace_transfers() ) fprintf( stderr, "[vpic_b200] h2d %zu bytes from %p\n", bytes, src );
 }
 inline void d2h( void * dst, const void * src, size_t bytes, cudaStream_t st ) {
   VPB_CUDA( cudaMemcpyAsync( dst, src, bytes, cudaMemcpyDeviceToHost, st ) ); rt().d2h_bytes += (long long)bytes;
+  if( bytes>=( 1u<<20 ) && trace_transfers() ) fprintf( stderr, "[vpic_b200] d2h %zu bytes to %p\n", bytes, dst );
 }
 
 inline int div_up( long long a, long long b ) { return (int)( (a+b-1)/b ); }

@@ -98,30 +98,56 @@ void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n ) {
 // the key histogram against 45 us of traffic), not by their atomics.
 constexpr int SORT_CHUNKS = 16;
 
-__global__ void __launch_bounds__(256)
-k_sort_hist( const vpb_particle_t * __restrict__ p, int np, int * __restrict__ keys, int * __restrict__ count ) {
-  for( int c=0; c<SORT_CHUNKS; c++ ) {
-    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
-    if( i - threadIdx.x>=np ) return;
-    const int key = i<np ? p[i].i : -1;
-    if( i<np ) keys[i] = key;
-    const unsigned m = __match_any_sync( 0xffffffffu, key );
-    if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
+// The kernels are latency bound (one key load, one atomic round trip per warp and chunk at full occupancy: 40 warps
+// stalled on the scoreboard per issue), so every thread works on SORT_ILP chunks at once: the loads, the matches
+// and the atomics of the batch are issued back to back before the first result is needed.
+constexpr int SORT_ILP = 4;
+static_assert( SORT_CHUNKS % SORT_ILP==0, "chunks per block come in batches" );
+
+template<bool FROM_PARTICLES>
+__device__ __forceinline__ void hist_block( const vpb_particle_t * __restrict__ p, const int * __restrict__ keys_in, int np,
+                                            int * __restrict__ keys_out, int * __restrict__ count ) {
+  const int lane = threadIdx.x & 31;
+  for( int c0=0; c0<SORT_CHUNKS; c0+=SORT_ILP ) {
+    const long long i0 = ( (long long)blockIdx.x*SORT_CHUNKS + c0 )*256 + threadIdx.x;
+    if( i0 - threadIdx.x>=np ) return;
+    int key[SORT_ILP]; unsigned m[SORT_ILP];
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) { const long long i = i0 + 256*u; key[u] = i<np ? ( FROM_PARTICLES ? p[i].i : keys_in[i] ) : -1; }
+    if( FROM_PARTICLES ) {
+#     pragma unroll
+      for( int u=0; u<SORT_ILP; u++ ) if( key[u]>=0 ) keys_out[i0 + 256*u] = key[u];
+    }
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) m[u] = __match_any_sync( 0xffffffffu, key[u] );
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) if( key[u]>=0 && lane==__ffs( m[u] )-1 ) atomicAdd( count + key[u], __popc( m[u] ) );
   }
 }
 
 __global__ void __launch_bounds__(256)
+k_sort_hist( const vpb_particle_t * __restrict__ p, int np, int * __restrict__ keys, int * __restrict__ count ) {
+  hist_block<true>( p, nullptr, np, keys, count );
+}
+
+__global__ void __launch_bounds__(256)
 k_sort_scatter_idx( const int * __restrict__ keys, int np, int * __restrict__ next, int * __restrict__ perm ) {
-  for( int c=0; c<SORT_CHUNKS; c++ ) {
-    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
-    if( i - threadIdx.x>=np ) return;
-    const int key = i<np ? keys[i] : -1;
-    const unsigned m = __match_any_sync( 0xffffffffu, key );
-    const int lane = threadIdx.x & 31, leader = __ffs( m )-1;
-    int base = 0;
-    if( key>=0 && lane==leader ) base = atomicAdd( next + key, __popc( m ) );
-    base = __shfl_sync( 0xffffffffu, base, leader );
-    if( key>=0 ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = (int)i;
+  const int lane = threadIdx.x & 31;
+  for( int c0=0; c0<SORT_CHUNKS; c0+=SORT_ILP ) {
+    const long long i0 = ( (long long)blockIdx.x*SORT_CHUNKS + c0 )*256 + threadIdx.x;
+    if( i0 - threadIdx.x>=np ) return;
+    int key[SORT_ILP], base[SORT_ILP]; unsigned m[SORT_ILP];
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) { const long long i = i0 + 256*u; key[u] = i<np ? keys[i] : -1; }
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) m[u] = __match_any_sync( 0xffffffffu, key[u] );
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) { base[u] = 0; if( key[u]>=0 && lane==__ffs( m[u] )-1 ) base[u] = atomicAdd( next + key[u], __popc( m[u] ) ); }
+#   pragma unroll
+    for( int u=0; u<SORT_ILP; u++ ) {
+      base[u] = __shfl_sync( 0xffffffffu, base[u], __ffs( m[u] )-1 );
+      if( key[u]>=0 ) perm[ base[u] + __popc( m[u] & ( ( 1u<<lane )-1u ) ) ] = (int)( i0 + 256*u );
+    }
   }
 }
 
@@ -173,17 +199,13 @@ template<int E> __device__ __forceinline__ void warp_bitonic_regs( int (&x)[E], 
   }
 }
 
-// GATHER: copy the particles to their final places; otherwise (lazy sort_p) only write the
-// ordered indices to out_perm -- the next advance_p gathers through them.
+// GATHER: copy the particles to their final places; otherwise (lazy sort_p) put the segment of perm[] in order
+// IN PLACE -- the next advance_p gathers through it -- which for a segment that arrived in order is no write at all.
 template<int E, bool GATHER> __device__ __forceinline__ void
-fix_gather_regs( const int * __restrict__ perm, int b, int n, int lane,
-                 const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out, int * __restrict__ out_perm ) {
+fix_gather_regs( int * perm, int b, int n, int lane, const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
   int x[E];
 # pragma unroll
   for( int k=0; k<E; k++ ) x[k] = 32*k+lane<n ? perm[b+32*k+lane] : 0x7fffffff;
-  // The atomic slots were handed out to whole warps of a (nearly) sorted array: most segments arrive already
-  // ascending (one or two contiguous groups in order).  One neighbour compare per element finds out and
-  // skips the sorting network (which is what made this kernel issue-bound).
   bool ok = true;
 # pragma unroll
   for( int k=0; k<E; k++ ) {
@@ -191,36 +213,77 @@ fix_gather_regs( const int * __restrict__ perm, int b, int n, int lane,
     const int wrap = __shfl_sync( 0xffffffffu, k+1<E ? x[k+1<E ? k+1 : k] : 0x7fffffff, 0 );
     ok = ok && x[k]<=( lane==31 ? wrap : nxt );
   }
-  if( !__all_sync( 0xffffffffu, ok ) ) warp_bitonic_regs<E>( x, lane );
+  const bool sorted = __all_sync( 0xffffffffu, ok );
+  if( !sorted ) warp_bitonic_regs<E>( x, lane );
 # pragma unroll
-  for( int k=0; k<E; k++ ) if( 32*k+lane<n ) { if( GATHER ) copy_particle( out, b+32*k+lane, in, x[k] ); else out_perm[b+32*k+lane] = x[k]; }
+  for( int k=0; k<E; k++ ) if( 32*k+lane<n ) { if( GATHER ) copy_particle( out, b+32*k+lane, in, x[k] ); else if( !sorted ) perm[b+32*k+lane] = x[k]; }
 }
 
+// A warp owns FIX_REP consecutive voxels.  The kernel was latency bound (partition load -> segment load -> store,
+// one voxel after the other, 34 warps stalled per issue), so the common case -- every one of the warp's segments
+// holds at most 64 indices -- loads all of them before it looks at the first.  The atomic slots of the scatter
+// went to whole warps of a nearly sorted array, so most segments arrive ascending already: one neighbour compare
+// per element finds out and skips the sorting network.
 template<bool GATHER>
 __global__ void __launch_bounds__(32*FIX_WARPS)
-k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * __restrict__ perm, int * __restrict__ big_scratch,
-                   const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out, int * __restrict__ out_perm ) {
+k_sort_fix_gather( const int * __restrict__ partition, int nv, int np, int * perm, int * __restrict__ big_scratch,
+                   const vpb_particle_t * __restrict__ in, vpb_particle_t * __restrict__ out ) {
   __shared__ int s[FIX_WARPS][FIX_SMEM];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  // FIX_REP consecutive voxels per warp (a block per 4 voxels was launch-rate bound like the kernels above)
-  for( int rep=0; rep<FIX_REP; rep++ ) {
-    const int v = ( blockIdx.x*FIX_REP + rep )*FIX_WARPS + w;
-    if( v>=nv ) return;
-    const int b = partition[v], e = v+1<nv ? partition[v+1] : np, n = e-b;
-    if( n<=0 ) continue;
-    // Segments up to 32*FIX_E indices sort in registers, with a network sized for
-    // the segment (ne is warp uniform); lane l of slot k then holds rank 32k+l.
-    if( n<=32 )       { fix_gather_regs<1,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
-    if( n<=64 )       { fix_gather_regs<2,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
-    if( n<=32*FIX_E ) { fix_gather_regs<FIX_E,GATHER>( perm, b, n, lane, in, out, out_perm ); continue; }
-    int n2 = 64; while( n2<n ) n2 <<= 1;
+  const int v0 = ( blockIdx.x*FIX_WARPS + w )*FIX_REP;
+  if( v0>=nv ) return;
+  const int vl = v0 + lane;
+  const int pl = ( lane<=FIX_REP && vl<nv ) ? partition[vl] : np;     // partition[v0 .. v0+FIX_REP], np past the end
+  int b[FIX_REP], n[FIX_REP], nmax = 0;
+# pragma unroll
+  for( int r=0; r<FIX_REP; r++ ) {
+    b[r] = __shfl_sync( 0xffffffffu, pl, r ); n[r] = __shfl_sync( 0xffffffffu, pl, r+1 ) - b[r];
+    nmax = max( nmax, n[r] );
+  }
+  if( nmax<=64 ) {
+    int x[FIX_REP][2];
+#   pragma unroll
+    for( int r=0; r<FIX_REP; r++ ) {
+      x[r][0] = lane<n[r]    ? perm[b[r]+lane]    : 0x7fffffff;
+      x[r][1] = 32+lane<n[r] ? perm[b[r]+32+lane] : 0x7fffffff;
+    }
+#   pragma unroll
+    for( int r=0; r<FIX_REP; r++ ) {
+      if( n[r]<=0 ) continue;
+      const int nxt0 = __shfl_down_sync( 0xffffffffu, x[r][0], 1 ), nxt1 = __shfl_down_sync( 0xffffffffu, x[r][1], 1 );
+      const int wrap = __shfl_sync( 0xffffffffu, x[r][1], 0 );
+      const bool ok = x[r][0]<=( lane==31 ? wrap : nxt0 ) && ( lane==31 || x[r][1]<=nxt1 );
+      const bool sorted = __all_sync( 0xffffffffu, ok );
+      if( !sorted ) {
+        if( n[r]<=32 ) { int y[1] = { x[r][0] }; warp_bitonic_regs<1>( y, lane ); x[r][0] = y[0]; }
+        else warp_bitonic_regs<2>( x[r], lane );
+      }
+      if( GATHER ) {
+        if( lane<n[r] )    copy_particle( out, b[r]+lane, in, x[r][0] );
+        if( 32+lane<n[r] ) copy_particle( out, b[r]+32+lane, in, x[r][1] );
+      } else if( !sorted ) {
+        if( lane<n[r] )    perm[b[r]+lane] = x[r][0];
+        if( 32+lane<n[r] ) perm[b[r]+32+lane] = x[r][1];
+      }
+    }
+    return;
+  }
+  // some segment is longer: one voxel after the other; <= 32*FIX_E indices sort in registers, longer ones in
+  // shared memory, > FIX_SMEM in global memory (rare: a crowded voxel)
+  for( int r=0; r<FIX_REP; r++ ) {
+    const int bb = __shfl_sync( 0xffffffffu, pl, r ), nn = __shfl_sync( 0xffffffffu, pl, r+1 ) - bb;
+    if( nn<=0 ) continue;
+    if( nn<=32 )       { fix_gather_regs<1,GATHER>( perm, bb, nn, lane, in, out ); continue; }
+    if( nn<=64 )       { fix_gather_regs<2,GATHER>( perm, bb, nn, lane, in, out ); continue; }
+    if( nn<=32*FIX_E ) { fix_gather_regs<FIX_E,GATHER>( perm, bb, nn, lane, in, out ); continue; }
+    int n2 = 64; while( n2<nn ) n2 <<= 1;
     int * a;
     if( n2<=FIX_SMEM ) a = s[w];
-    else a = big_scratch + 2*(size_t)b;     // window of n2 < 2n ints starting at 2b: windows of different voxels are disjoint
-    for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+    else a = big_scratch + 2*(size_t)bb;     // window of n2 < 2n ints starting at 2b: windows of different voxels are disjoint
+    for( int t=lane; t<n2; t+=32 ) a[t] = t<nn ? perm[bb+t] : 0x7fffffff;
     __threadfence_block(); __syncwarp();
     bitonic_mem( a, n2, lane );
-    for( int t=lane; t<n; t+=32 ) { if( GATHER ) copy_particle( out, b+t, in, a[t] ); else out_perm[b+t] = a[t]; }
+    for( int t=lane; t<nn; t+=32 ) { if( GATHER ) copy_particle( out, bb+t, in, a[t] ); else perm[bb+t] = a[t]; }
     __syncwarp();
   }
 }
@@ -234,13 +297,7 @@ k_sort_apply_perm( const int * __restrict__ perm, int np, const vpb_particle_t *
 
 __global__ void __launch_bounds__(256)
 k_hist_keys( const int * __restrict__ keys, int n, int * __restrict__ count ) {
-  for( int c=0; c<SORT_CHUNKS; c++ ) {
-    const long long i = ( (long long)blockIdx.x*SORT_CHUNKS + c )*256 + threadIdx.x;
-    if( i - threadIdx.x>=n ) return;
-    const int key = i<n ? keys[i] : -1;
-    const unsigned m = __match_any_sync( 0xffffffffu, key );
-    if( key>=0 && ( threadIdx.x & 31 )==__ffs( m )-1 ) atomicAdd( count + key, __popc( m ) );
-  }
+  hist_block<false>( nullptr, keys, n, nullptr, count );
 }
 
 void bin_indices( const int * keys, int n, int nbin, int * start, int * perm ) {
@@ -361,17 +418,21 @@ extern "C" void sort_p( vpb_species_t * sp ) {
   }
   exclusive_scan( count, m->d_partition, next, tiles, nv+1 );
   if( np>0 ) {
-    k_sort_scatter_idx<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, np, next, perm );
     if( lazy ) {
       if( m->cap_perm<m->cap_p ) {
         VPB_CUDA( cudaStreamSynchronize( r.stream ) );
         if( m->d_perm ) VPB_CUDA( cudaFree( m->d_perm ) );
         VPB_CUDA( cudaMalloc( &m->d_perm, sizeof(int)*m->cap_p ) ); m->cap_perm = m->cap_p;
       }
-      k_sort_fix_gather<false><<< div_up(nv,FIX_WARPS*FIX_REP), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, nullptr, m->d_perm );
+      perm = m->d_perm;                // the indices go straight to where advance_p reads them and are put in order in place
+    }
+    k_sort_scatter_idx<<< div_up(np,256*SORT_CHUNKS), 256, 0, r.stream >>>( keys, np, next, perm );
+    const int fix_blocks = div_up( nv, FIX_WARPS*FIX_REP );
+    if( lazy ) {
+      k_sort_fix_gather<false><<< fix_blocks, 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, nullptr );
       m->perm_pending = true;
     } else {
-      k_sort_fix_gather<true><<< div_up(nv,FIX_WARPS*FIX_REP), 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt, nullptr );
+      k_sort_fix_gather<true><<< fix_blocks, 32*FIX_WARPS, 0, r.stream >>>( m->d_partition, nv, np, perm, big, m->d_p, g_alt );
       sort_swap_spare( m );            // swap the species buffer with the spare
     }
     VPB_CHECK_LAUNCH(); r.launches += 2;

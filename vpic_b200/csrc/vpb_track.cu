@@ -10,8 +10,10 @@
 // host copy is kept current exactly as in STRICT mode (downloads stay), only the redundant uploads go.
 //
 // Scope and limits (why it is a mode a host opts into, not the default):
-//  * the protected range is rounded OUT to page boundaries; a write to the few bytes of a neighbouring
-//    allocation that share the first or last page also faults and merely costs one spurious upload;
+//  * only the pages that lie ENTIRELY inside the array are protected.  The head and the tail of an array that is
+//    not page aligned share their pages with whatever the allocator put next to it (another array, malloc's own
+//    bookkeeping), so those two fragments (< 4 KB each) stay writable and are compared against a copy taken when
+//    the array was armed instead.  A neighbour's stores therefore never fault and never mark this array dirty;
 //  * stores are intercepted, system calls are not: a read()/fread() INTO a protected array fails with
 //    EFAULT instead of faulting.  A host program that fills its arrays that way (restart files are
 //    read into fresh arrays, which are not yet tracked) must stay STRICT or call vpic_b200_forget first;
@@ -29,7 +31,12 @@ namespace vpb {
 namespace {
 
 constexpr int TR_MAX = 256;
-struct Tracked { uintptr_t base; uintptr_t lo, hi; volatile int armed; volatile int dirty; };
+struct Tracked {
+  uintptr_t base; size_t bytes;       // the array as it was armed
+  uintptr_t lo, hi;                   // its interior pages (protected while armed)
+  volatile int armed; volatile int dirty;
+  unsigned char * edge;               // copies of [base,lo) and [hi,base+bytes)
+};
 Tracked g_tr[TR_MAX];
 volatile int g_ntr = 0;
 bool g_on = false, g_handler = false;
@@ -43,12 +50,6 @@ void on_segv( int sig, siginfo_t * si, void * ctx ) {
     if( t.armed && a>=t.lo && a<t.hi ) {
       t.dirty = 1; t.armed = 0;
       mprotect( (void *)t.lo, t.hi-t.lo, PROT_READ|PROT_WRITE );     // async-signal-safe
-      // a neighbouring array that shares a page with this one just lost the protection of that page:
-      // it can no longer vouch for itself either
-      for( int j=0; j<n; j++ ) {
-        Tracked & o = g_tr[j];
-        if( o.armed && o.lo<t.hi && t.lo<o.hi ) { o.dirty = 1; o.armed = 0; mprotect( (void *)o.lo, o.hi-o.lo, PROT_READ|PROT_WRITE ); }
-      }
       return;                                                        // the faulting store is retried
     }
   }
@@ -62,6 +63,12 @@ Tracked * find( const void * p ) {
   const uintptr_t b = (uintptr_t)p;
   for( int k=0; k<g_ntr; k++ ) if( g_tr[k].base==b ) return &g_tr[k];
   return nullptr;
+}
+
+uintptr_t page_size() { static const uintptr_t page = (uintptr_t)sysconf( _SC_PAGESIZE ); return page; }
+
+void unprotect( Tracked * t ) {
+  if( t->armed ) { t->armed = 0; mprotect( (void *)t->lo, t->hi-t->lo, PROT_READ|PROT_WRITE ); }
 }
 
 } // namespace
@@ -83,17 +90,21 @@ void track_enable( bool on ) {
 // The host array at p (bytes long) and its device mirror are identical right now: arm the tracker.
 void track_arm( const void * p, size_t bytes ) {
   if( !g_on || !p || bytes<( 1u<<20 ) ) return;
-  const uintptr_t page = (uintptr_t)sysconf( _SC_PAGESIZE );
+  const uintptr_t page = page_size();
   Tracked * t = find( p );
   if( !t ) {
     if( g_ntr>=TR_MAX ) return;
-    t = &g_tr[g_ntr]; t->base = (uintptr_t)p; t->armed = 0; t->dirty = 1; t->lo = t->hi = 0;
+    t = &g_tr[g_ntr]; t->base = (uintptr_t)p; t->bytes = 0; t->armed = 0; t->dirty = 1; t->lo = t->hi = 0;
+    t->edge = (unsigned char *)malloc( 2*page );
+    if( !t->edge ) return;
     __sync_synchronize();
     g_ntr = g_ntr+1;
   }
-  const uintptr_t lo = (uintptr_t)p & ~( page-1 ), hi = ( (uintptr_t)p + bytes + page-1 ) & ~( page-1 );
-  if( t->armed && ( t->lo!=lo || t->hi!=hi ) ) { mprotect( (void *)t->lo, t->hi-t->lo, PROT_READ|PROT_WRITE ); t->armed = 0; }
-  t->lo = lo; t->hi = hi; t->dirty = 0;
+  const uintptr_t b = (uintptr_t)p, lo = ( b + page-1 ) & ~( page-1 ), hi = ( b + bytes ) & ~( page-1 );
+  if( t->armed && ( t->lo!=lo || t->hi!=hi ) ) unprotect( t );
+  t->bytes = bytes; t->lo = lo; t->hi = hi; t->dirty = 0;
+  memcpy( t->edge, (const void *)b, lo-b );
+  memcpy( t->edge + page, (const void *)hi, b+bytes-hi );
   __sync_synchronize();
   if( !t->armed ) {
     t->armed = 1;
@@ -101,32 +112,29 @@ void track_arm( const void * p, size_t bytes ) {
   }
 }
 
-// true: the host program has not written the array since it was armed (the device mirror is still equal to it)
+// true: the host program has not written the first `bytes` of the array since it was armed (the device mirror is
+// still equal to them)
 bool track_clean( const void * p, size_t bytes ) {
   if( !g_on || !p ) return false;
   Tracked * t = find( p );
-  if( !t || !t->armed || t->dirty ) return false;
-  const uintptr_t page = (uintptr_t)sysconf( _SC_PAGESIZE );
-  const uintptr_t hi = ( (uintptr_t)p + bytes + page-1 ) & ~( page-1 );
-  return hi<=t->hi;                        // (an array that grew in place is not covered)
+  if( !t || !t->armed || t->dirty || bytes>t->bytes ) return false;     // (an array that grew in place is not covered)
+  const uintptr_t b = t->base, end = b + bytes;
+  const size_t head = ( end<t->lo ? end : t->lo ) - b;
+  if( memcmp( t->edge, (const void *)b, head )!=0 ) return false;
+  if( end>t->hi && memcmp( t->edge + page_size(), (const void *)t->hi, end-t->hi )!=0 ) return false;
+  return true;
 }
 
 // The library itself is about to write the host array with CPU stores, or the array is going away.
 void track_disarm( const void * p ) {
   Tracked * t = p ? find( p ) : nullptr;
   if( !t ) return;
-  if( t->armed ) {
-    t->armed = 0; mprotect( (void *)t->lo, t->hi-t->lo, PROT_READ|PROT_WRITE );
-    for( int j=0; j<g_ntr; j++ ) {          // neighbours sharing a page (see on_segv)
-      Tracked & o = g_tr[j];
-      if( o.armed && o.lo<t->hi && t->lo<o.hi ) { o.dirty = 1; o.armed = 0; mprotect( (void *)o.lo, o.hi-o.lo, PROT_READ|PROT_WRITE ); }
-    }
-  }
+  unprotect( t );
   t->dirty = 1;
 }
 
 void track_forget_all() {
-  for( int k=0; k<g_ntr; k++ ) if( g_tr[k].armed ) { g_tr[k].armed = 0; mprotect( (void *)g_tr[k].lo, g_tr[k].hi-g_tr[k].lo, PROT_READ|PROT_WRITE ); }
+  for( int k=0; k<g_ntr; k++ ) { unprotect( &g_tr[k] ); free( g_tr[k].edge ); g_tr[k].edge = nullptr; }
   g_ntr = 0;
 }
 
