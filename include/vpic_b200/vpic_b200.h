@@ -150,6 +150,9 @@ long long vpic_b200_sort_violations( vpb_species_t * sp );
 /* Diagnostic: how many sort_p calls of this process read the 4-byte voxel keys the
    preceding advance_p wrote (and boundary_p patched) instead of the particle records. */
 long long vpic_b200_sorts_from_keys( void );
+/* ... and how many of those were segment sorts (deterministic ranks from the last sort's
+   partition; VPIC_B200_SEG_SORT=0 disables them). */
+long long vpic_b200_segment_sorts( void );
 void vpic_b200_finalize( void );
 /* frees the grow-on-demand device caches (sort_p spare buffer, scratch, boundary_p
    message buffers); objects and their mirrors stay valid */

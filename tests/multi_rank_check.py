@@ -297,7 +297,7 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
     if rank == 0:
         print("transport:", "put (NVLink peer-memory mailboxes)" if want else "ncclSend/ncclRecv")
     L.vpic_b200_set_coherence(1 if resident else 0)
-    keys0 = L.vpic_b200_sorts_from_keys()
+    keys0, seg0 = L.vpic_b200_sorts_from_keys(), L.vpic_b200_segment_sorts()
     sg, origin, ln = build(b200_backend(), kind, gn, topo, rank, 6, 40, sort_interval=2 if resident else 3)
     for s in (so, sg):
         with_cleaning(s)
@@ -350,8 +350,8 @@ def check_gpu(H, so, kind, gn, topo, rank, world, steps, dist, torch, group=None
         # boundary_p moved particles in and out in between
         want = len(sg.species) * ((steps - 1) // 2)
         got = L.vpic_b200_sorts_from_keys() - keys0
-        if got < want:
-            print(f"rank {rank} {kind} {topo}: {got} sorts took the key array, expected {want}"); ok = False
+        if got < want or L.vpic_b200_segment_sorts() - seg0 < want:
+            print(f"rank {rank} {kind} {topo}: {got} sorts took the key array, {L.vpic_b200_segment_sorts() - seg0} were segment sorts, expected {want}"); ok = False
         L.vpic_b200_set_coherence(0)
     return ok
 

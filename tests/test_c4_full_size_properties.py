@@ -53,9 +53,16 @@ def test_full_size_box_conservation_properties():
 
         e0 = sum(sim.energies())
         err0 = div_e_rms()
-        for step in range(6):                                                # sort_p runs at steps 0 and 4
+        for step in range(4):                                                # sort_p runs at step 0; step 3 leaves the voxel keys
             sim.advance()
-        for sp, _, _ in sps:                                                 # a sort of the state as it is now
+        seg0 = L.vpic_b200_segment_sorts()
+        for sp, _, _ in sps:                                                 # the sort step 4 would start with: keys + the order of
+            be.sort_p(sp)                                                    # the last sort are there -> segment sort (lazy: indices)
+            assert L.vpic_b200_sort_violations(sp) == 0                      # (carries the permutation out, then checks the records)
+        assert L.vpic_b200_segment_sorts() - seg0 == 2
+        for step in range(2):
+            sim.advance()
+        for sp, _, _ in sps:                                                 # a sort of the state as it is now (generic path: no keys)
             be.sort_p(sp)
             assert L.vpic_b200_sort_violations(sp) == 0
         assert [sim.sp_struct(sp).np for sp, _, _ in sps] == np0

@@ -591,7 +591,7 @@ def test_lazy_sort_resident_mode_bit_exact_per_step(gpu, kind):
     so, sg = pair(gpu, kind=kind, n=(10, 7, 6), sort_interval=2, ppc=20, vth=0.3)
     nv = so.grid_struct(so.g).nv
     L.vpic_b200_set_coherence(1)
-    keys0 = L.vpic_b200_sorts_from_keys()
+    keys0, seg0 = L.vpic_b200_sorts_from_keys(), L.vpic_b200_segment_sorts()
     try:
         so.initialize(); sg.initialize()
         for step in range(7):
@@ -611,6 +611,8 @@ def test_lazy_sort_resident_mode_bit_exact_per_step(gpu, kind):
         # the sorts of steps 2, 4, 6 read the keys advance_p left, also where boundary_p removed particles in between
         # (it patches the keys of the holes it fills)
         assert L.vpic_b200_sorts_from_keys() - keys0 >= 3 * len(sg.species)
+        # ... and ranked the particles deterministically from the order the previous sort left (segment sort)
+        assert L.vpic_b200_segment_sorts() - seg0 >= 3 * len(sg.species)
     finally:
         L.vpic_b200_set_coherence(0)
 

@@ -119,11 +119,13 @@ def test_ranks_sharing_one_gpu_match_the_n_rank_oracle(nproc, extra):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("nproc", [2, 4])
-def test_ranks_sharing_one_gpu_resident_lazy_sort_match_the_n_rank_oracle(nproc):
+@pytest.mark.parametrize("nproc,small", [(2, "16"), (2, "1"), (4, "16")])
+def test_ranks_sharing_one_gpu_resident_lazy_sort_match_the_n_rank_oracle(nproc, small):
     """RESIDENT coherence, sort every second step: sort_p orders indices only, advance_p gathers through them and
     leaves the voxel keys for the next sort, and boundary_p -- which removes the emigrants (back-fill) and appends
     the immigrants -- patches those keys instead of invalidating them.  Particle order, voxels and bits against
-    the N-rank oracle after every step."""
+    the N-rank oracle after every step.  The sorts after the first are segment sorts (stayers ranked inside their
+    home segment, strays in the two small regions around them, ordered by one thread per voxel -- or, with
+    VPIC_B200_SEG_SMALL=1, by the warp path that crowded voxels take)."""
     launch("gpu", nproc=nproc, extra=("--resident",), timeout=1500, VPIC_B200_TRANSPORT="put", VPB_TEST_BOOTSTRAP="handles",
-           VPIC_B200_PUT_TIMEOUT_S="120")
+           VPIC_B200_PUT_TIMEOUT_S="120", VPIC_B200_SEG_SMALL=small)

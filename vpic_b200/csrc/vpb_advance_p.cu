@@ -428,7 +428,7 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
   }
   VPB_CUDA( cudaStreamSynchronize( r.copy_stream[1] ) );
   ms->dev_valid = true; ms->host_valid = true; ms->partition_dev_valid = false;
-  ms->perm_pending = false; ms->keys_valid = ms->keys_patchable = false;
+  ms->perm_pending = false; ms->keys_valid = ms->keys_patchable = false; ms->home_valid = false;
   track_arm( sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np );
   return true;
 }
@@ -490,7 +490,8 @@ extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, con
   ms->nm = cnt[0]<(int)ms->cap_pm ? cnt[0] : (int)ms->cap_pm;
   if( ms->nm>1 ) sort_movers_by_index( ms );
   ms->movers_sorted = true;
-  if( !streamed ) mark_dev_written( ms );
+  const bool home = ms->home_valid;          // a push moves no record: the array keeps the order of the last sort
+  if( !streamed ) { mark_dev_written( ms ); ms->home_valid = home; }
   // Particles on the mover list carry 8*voxel+face: their keys are wrong until boundary_p has removed them, which
   // patches d_keys at the holes it fills and the records it appends (k_keys_patch).  A mover that did not fit the
   // list (cnt[1]) is in that state for good.

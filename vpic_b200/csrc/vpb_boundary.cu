@@ -677,10 +677,13 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   }
   if( sparse ) sparse_upload( ss );
   // species whose voxel keys (written by advance_p for the lazy sort_p) are worth keeping current
-  std::vector<char> patch( sps.size(), 0 );
+  // (and whose records still have the order of the last sort_p: filling holes and appending keeps the positions'
+  // home segments, which is all the segment sort needs)
+  std::vector<char> patch( sps.size(), 0 ), home( sps.size(), 0 );
   if( !sparse ) for( size_t k=0; k<sps.size(); k++ ) {
     const SpeciesMirror * m = sps[k];
     patch[k] = ( m->keys_valid || m->keys_patchable ) && m->d_keys && m->cap_keys>=m->cap_p;
+    home[k] = m->home_valid;
   }
   GridMirror * gm = particle_grid( sps[0]->grid );
   const GridDev & g = gm->dev;
@@ -871,6 +874,7 @@ extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_
   for( size_t ks=0; ks<sps.size(); ks++ ) {
     SpeciesMirror * m = sps[ks];
     if( patch[ks] ) { m->keys_valid = m->nm==0; m->keys_patchable = m->nm>0; }
+    if( home[ks] ) m->home_valid = true;
     m->host->np = m->np;
     if( m->nm>1 && !m->movers_sorted ) { sort_movers_by_index( m ); m->movers_sorted = true; }
     movers_to_host( m );
@@ -914,12 +918,12 @@ extern "C" int vpic_b200_drop_unprocessed_movers( vpb_species_t * sp_list, vpb_f
     k_bnd_classify<<< 1, BND_T, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, sp->id, q_r8V, mf->comp( F_RHOB ), g, bf, B.d_int+16, true );
     k_bnd_backfill<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_p, m->d_pm, m->nm, m->np );
     VPB_CHECK_LAUNCH(); r.launches += 2;
-    const bool patch = m->keys_patchable && m->d_keys && m->cap_keys>=m->cap_p;
+    const bool patch = m->keys_patchable && m->d_keys && m->cap_keys>=m->cap_p, home = m->home_valid;
     if( patch ) { k_keys_patch<<< div_up( m->nm, 256 ), 256, 0, r.stream >>>( m->d_keys, m->d_p, m->d_pm, m->nm, 0, m->np-m->nm ); VPB_CHECK_LAUNCH(); r.launches++; }
     dropped += m->nm;
     m->np -= m->nm; m->nm = 0; m->partition_dev_valid = false;
     mark_dev_written( m );
-    m->keys_valid = patch;
+    m->keys_valid = patch; m->home_valid = home;
     sp->np = m->np;
     movers_to_host( m );
     if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );

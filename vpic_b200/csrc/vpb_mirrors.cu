@@ -153,7 +153,7 @@ void to_device( SpeciesMirror * m, bool keep_lazy_sort ) {
     if( !keep_lazy_sort ) materialize_sort( m );
     return;
   }
-  m->perm_pending = false; m->keys_valid = m->keys_patchable = false;      // the host copy replaces whatever the device held
+  m->perm_pending = false; m->keys_valid = m->keys_patchable = false; m->home_valid = false;      // the host copy replaces whatever the device held
   m->np = m->host->np; m->nm = m->host->nm;
   pin_host( m->host->p, sizeof(vpb_particle_t)*(size_t)m->host->max_np );
   if( m->np>0 )
@@ -278,7 +278,7 @@ void vpic_b200_forget( void * obj ) {
   Runtime & r = rt();
   if( !r.initialised ) return;
   VPB_CUDA( cudaStreamSynchronize( r.stream ) );
-  if( r.species.count( obj ) ) { auto m = r.species[obj]; unpin_host( m->host->p ); release_lazy_sort( m ); cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
+  if( r.species.count( obj ) ) { auto m = r.species[obj]; unpin_host( m->host->p ); release_lazy_sort( m ); cudaFree( m->d_p ); cudaFree( m->d_pm ); cudaFree( m->d_partition ); cudaFree( m->d_partition_alt ); cudaFree( m->d_counters ); delete m; r.species.erase( obj ); return; }
   if( r.fields.count( obj )  ) { auto m = r.fields[obj]; unpin_host( m->host->f ); cudaFree( m->d ); cudaFree( m->d_mat ); cudaFree( m->d_mc ); cudaFree( m->d_stage ); cudaFree( m->d_en ); cudaFree( m->d_face ); delete m; r.fields.erase( obj ); return; }
   if( r.interps.count( obj ) ) { auto m = r.interps[obj]; unpin_host( m->host->i ); cudaFree( m->d ); cudaFree( m->d_stage ); delete m; r.interps.erase( obj ); return; }
   if( r.accs.count( obj )    ) { auto m = r.accs[obj]; unpin_host( m->host->a ); cudaFree( m->d ); cudaFree( m->d_priv ); delete m; r.accs.erase( obj ); return; }

@@ -251,9 +251,9 @@ void apply_langevin_pipeline( vpb_langevin_t * l ) {
     k_langevin<<< div_up( ms->np, 256 ), 256, 0, r.stream >>>( ms->d_p, ms->np, decay, drive, key, (uint64_t)sp->g->step );
     VPB_CHECK_LAUNCH(); r.launches++;
   }
-  const bool keys = ms->keys_valid;            // momenta only: voxels, order and keys are untouched
+  const bool keys = ms->keys_valid, home = ms->home_valid;     // momenta only: voxels, order and keys are untouched
   finish_write( ms );
-  ms->keys_valid = keys;
+  ms->keys_valid = keys; ms->home_valid = home;
 }
 
 void vpic_b200_load_uniform_maxwellian( vpb_species_t * sp, int ppc, float vth, float w, uint64_t seed ) {

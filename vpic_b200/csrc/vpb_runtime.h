@@ -155,6 +155,9 @@ struct SpeciesMirror {
   vpb_particle_t * d_p = nullptr;  size_t cap_p = 0;
   vpb_particle_mover_t * d_pm = nullptr; size_t cap_pm = 0;
   int * d_partition = nullptr;     // nv+1 ints
+  int * d_partition_alt = nullptr; // the segment sort writes the new partition here while it reads the old one, then swaps
+  bool home_valid = false;         // the array has the order of the last sort_p: position i is in the home segment d_partition gives it
+  int home_np = 0;                 // particles at that sort (later ones were appended by boundary_p)
   int * d_counters = nullptr;      // [0]=nm  [1]=n_ignored  [2..] scratch
   int np = 0, nm = 0;              // device-side truth while resident
   bool movers_sorted = true;       // d_pm ascending in particle index
@@ -185,6 +188,7 @@ struct Runtime {
   void * d_scratch = nullptr; size_t scratch_bytes = 0;
   void * h_pinned = nullptr;  size_t pinned_bytes = 0;
   long long launches = 0;             // kernels launched (for bench's gpu_launches)
+  long long seg_sorts = 0;            // of which: segment sorts (deterministic ranks from the last sort's partition)
   long long sorts_from_keys = 0;      // lazy sort_p calls that took the voxel keys advance_p / boundary_p left (4 B per particle read)
   long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued by the entry points
   std::unordered_map<const void *, size_t>          pinned_host;   // host arrays registered with cudaHostRegister
@@ -238,7 +242,7 @@ void release_lazy_sort( SpeciesMirror * m );
 void to_device( HydroMirror * m );   void to_host( HydroMirror * m );
 void movers_to_host( SpeciesMirror * m );
 template<class M> inline void mark_dev_written( M * m ) { m->dev_valid = true; m->host_valid = false; }
-inline void mark_dev_written( SpeciesMirror * m ) { m->dev_valid = true; m->host_valid = false; m->keys_valid = m->keys_patchable = false; }
+inline void mark_dev_written( SpeciesMirror * m ) { m->dev_valid = true; m->host_valid = false; m->keys_valid = m->keys_patchable = false; m->home_valid = false; }
 // In STRICT mode every entry point finishes by pushing what it wrote back.
 template<class M> inline void finish_write( M * m ) {
   mark_dev_written( m );

@@ -365,6 +365,191 @@ void release_lazy_sort( SpeciesMirror * m ) {
   m->d_perm = m->d_keys = nullptr; m->cap_perm = m->cap_keys = 0; m->perm_pending = m->keys_valid = m->keys_patchable = false;
 }
 
+// ---- segment sort: the deterministic stable rank for a nearly sorted array ------------------------------------
+//
+// Between two sorts the array keeps the order the last sort gave it: position i belongs to the HOME segment of the
+// voxel h with home[h] <= i < home[h+1] (home[] = the last sort's partition).  advance_p changes keys, boundary_p
+// fills holes and appends, nothing moves a record.  So the particles with key k are, in array order (= the order a
+// stable sort must give them):
+//     strays whose home is below k  |  the stayers of k's own home segment  |  strays from above and appended ones
+// The stayers -- the bulk -- get their final slot from a ballot rank inside their home segment, which one warp
+// walks front to back: no atomic, and they arrive in order.  Only the strays take atomic slots in the two small
+// regions before and after the stayers, and only those regions (a handful of indices each) are ordered afterwards,
+// by one thread per voxel with a sorting network in registers.  (The generic path below -- atomic slots for
+// everything, then a warp-wide bitonic network over the whole segment -- spent most of its time ordering
+// electron segments that had a few strays among thirty stayers.)
+constexpr int SEG_REP = 8;          // consecutive home segments per warp
+constexpr int SEG_ROWS = 8;         // rows of 32 keys in flight per warp (eight segments of 32 particles: the warp's whole range)
+
+// A[] = strays from below (before region), B[] = strays from above (after region), C[] = stayers, per key.
+template<bool PLACE>
+__global__ void __launch_bounds__(256)
+k_seg_pass( const int * __restrict__ keys, const int * __restrict__ home, int nv, int np_home,
+            int * __restrict__ A, int * __restrict__ B, int * __restrict__ C, int * __restrict__ curb, int * __restrict__ perm ) {
+  const int lane = threadIdx.x & 31;
+  const int v0 = ( blockIdx.x*( blockDim.x>>5 ) + ( threadIdx.x>>5 ) )*SEG_REP;
+  if( v0>=nv ) return;
+  // home[v0 .. v0+SEG_REP] clamped to the particles that exist, in lanes 0..SEG_REP
+  const int vi = v0+lane<nv ? v0+lane : nv;
+  int pl = 0x7fffffff;
+  if( lane<=SEG_REP ) { pl = home[vi]; pl = pl<np_home ? pl : np_home; }
+  const int b0 = __shfl_sync( 0xffffffffu, pl, 0 ), e0 = __shfl_sync( 0xffffffffu, pl, SEG_REP );
+  // COUNT: lane r counts the stayers of segment r.  PLACE: lane r holds the next stayer slot of segment r (A = the
+  // stayers' base after the prep pass).
+  int mine = 0;
+  if( PLACE && lane<SEG_REP && v0+lane<nv ) mine = A[v0+lane];
+  int r0 = 0;                       // segment that contains the first position of the current row (uniform)
+  for( int o=b0; o<e0; o+=32*SEG_ROWS ) {
+    int k[SEG_ROWS], slot[SEG_ROWS];
+    unsigned strays = 0;            // rows in which this lane holds a stray (PLACE: its slot is on its way in slot[])
+#   pragma unroll
+    for( int u=0; u<SEG_ROWS; u++ ) { const int pos = o + 32*u + lane; k[u] = pos<e0 ? keys[pos] : -1; }
+#   pragma unroll
+    for( int u=0; u<SEG_ROWS; u++ ) {
+      const int ps = o + 32*u, pos = ps + lane;
+      slot[u] = 0;
+      if( ps>=e0 ) break;
+      while( r0+1<SEG_REP && ps>=__shfl_sync( 0xffffffffu, pl, r0+1 ) ) r0++;
+      int h = r0, rmax = r0;
+      for( int t=r0+1; t<SEG_REP; t++ ) {
+        const int nb = __shfl_sync( 0xffffffffu, pl, t );
+        if( nb>=ps+32 || nb>=e0 ) break;
+        h += pos>=nb; rmax = t;
+      }
+      const bool valid = k[u]>=0;
+      const bool stay = valid && k[u]==v0+h;
+      for( int r=r0; r<=rmax; r++ ) {
+        const unsigned m = __ballot_sync( 0xffffffffu, stay && h==r );
+        if( !m ) continue;
+        if( PLACE ) {
+          const int base = __shfl_sync( 0xffffffffu, mine, r );
+          if( stay && h==r ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = pos;
+        }
+        if( lane==r ) mine += __popc( m );
+      }
+      if( valid && !stay ) {
+        const bool below = k[u]>v0+h;                 // its home is below the voxel it is in now
+        // (the slots of all rows are requested before the first one is used: one atomic round trip per batch)
+        if( PLACE ) { slot[u] = atomicAdd( ( below ? curb : B ) + k[u], 1 ); strays |= 1u<<u; }
+        else atomicAdd( ( below ? A : B ) + k[u], 1 );
+      }
+    }
+    if( PLACE ) {
+#     pragma unroll
+      for( int u=0; u<SEG_ROWS; u++ ) if( strays & ( 1u<<u ) ) perm[ slot[u] ] = o + 32*u + lane;
+    }
+  }
+  if( !PLACE && lane<SEG_REP && v0+lane<nv ) C[v0+lane] = mine;
+}
+
+// particles appended since the last sort (positions >= np_home): strays from above for every voxel
+template<bool PLACE>
+__global__ void __launch_bounds__(256)
+k_seg_tail( const int * __restrict__ keys, int first, int np, int * __restrict__ B, int * __restrict__ perm ) {
+  const int pos = first + blockIdx.x*blockDim.x + threadIdx.x;
+  if( pos>=np ) return;
+  const int k = keys[pos];
+  if( PLACE ) perm[ atomicAdd( B + k, 1 ) ] = pos; else atomicAdd( B + k, 1 );
+}
+
+__global__ void __launch_bounds__(256)
+k_seg_sum( const int * __restrict__ A, const int * __restrict__ B, const int * __restrict__ C, int * __restrict__ D, int nv ) {
+  const int v = blockIdx.x*blockDim.x + threadIdx.x;
+  if( v<nv ) D[v] = A[v] + B[v] + C[v]; else if( v==nv ) D[v] = 0;
+}
+
+// after the scan: A = first stayer slot, C = first slot of the after region, B = its cursor
+__global__ void __launch_bounds__(256)
+k_seg_prep( const int * __restrict__ part, int * __restrict__ A, int * __restrict__ B, int * __restrict__ C, int nv ) {
+  const int v = blockIdx.x*blockDim.x + threadIdx.x;
+  if( v>=nv ) return;
+  const int sb = part[v] + A[v], pa = sb + C[v];
+  A[v] = sb; C[v] = pa; B[v] = pa;
+}
+
+// ascending order of perm[b .. b+n), n <= N, by one thread: a bitonic network over N registers
+template<int N> __device__ __forceinline__ void seg_sort_regs( int * __restrict__ perm, int b, int n ) {
+  int x[N];
+# pragma unroll
+  for( int i=0; i<N; i++ ) x[i] = i<n ? perm[b+i] : 0x7fffffff;
+# pragma unroll
+  for( int k=2; k<=N; k<<=1 ) {
+#   pragma unroll
+    for( int j=k>>1; j>0; j>>=1 ) {
+#     pragma unroll
+      for( int i=0; i<N; i++ ) {
+        const int l = i^j;
+        if( l>i ) {
+          const int lo = min( x[i], x[l] ), hi = max( x[i], x[l] );
+          if( ( i & k )==0 ) { x[i] = lo; x[l] = hi; } else { x[i] = hi; x[l] = lo; }
+        }
+      }
+    }
+  }
+# pragma unroll
+  for( int i=0; i<N; i++ ) if( i<n ) perm[b+i] = x[i];
+}
+
+constexpr int SEG_SMALL = 16;       // longest region one thread orders
+
+__device__ __forceinline__ void seg_sort_small( int * __restrict__ perm, int b, int n ) {
+  if( n==2 ) { const int x0 = perm[b], x1 = perm[b+1]; if( x0>x1 ) { perm[b] = x1; perm[b+1] = x0; } return; }
+  if( n<=4 ) { seg_sort_regs<4>( perm, b, n ); return; }
+  if( n<=8 ) { seg_sort_regs<8>( perm, b, n ); return; }
+  seg_sort_regs<16>( perm, b, n );
+}
+
+// ascending order of perm[b .. b+n) by a warp (any n)
+__device__ __forceinline__ void seg_sort_warp( int * perm, int b, int n, int lane, int * smem, int * __restrict__ big_scratch ) {
+  if( n<=32 )       { fix_gather_regs<1,false>( perm, b, n, lane, nullptr, nullptr ); return; }
+  if( n<=64 )       { fix_gather_regs<2,false>( perm, b, n, lane, nullptr, nullptr ); return; }
+  if( n<=32*FIX_E ) { fix_gather_regs<FIX_E,false>( perm, b, n, lane, nullptr, nullptr ); return; }
+  int n2 = 64; while( n2<n ) n2 <<= 1;
+  int * a = n2<=FIX_SMEM ? smem : big_scratch + 2*(size_t)b;
+  for( int t=lane; t<n2; t+=32 ) a[t] = t<n ? perm[b+t] : 0x7fffffff;
+  __threadfence_block(); __syncwarp();
+  bitonic_mem( a, n2, lane );
+  for( int t=lane; t<n; t+=32 ) perm[b+t] = a[t];
+  __syncwarp();
+}
+
+// One thread per voxel orders its two stray regions when they hold up to small_max (<= SEG_SMALL) indices; longer regions
+// (a crowded voxel, a test) are ordered by the whole warp, one after the other.
+__global__ void __launch_bounds__(32*FIX_WARPS)
+k_seg_fix( const int * __restrict__ part, const int * __restrict__ A, const int * __restrict__ C, int nv, int np,
+           int * perm, int small_max, int * __restrict__ big_scratch ) {
+  __shared__ int s[FIX_WARPS][FIX_SMEM];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int v = blockIdx.x*blockDim.x + threadIdx.x;
+  int b[2] = { 0, 0 }, n[2] = { 0, 0 };
+  if( v<nv ) {
+    const int p0 = part[v], sb = A[v], pa = C[v], p1 = part[v+1];
+    b[0] = p0; n[0] = sb-p0; b[1] = pa; n[1] = p1-pa;
+  }
+# pragma unroll
+  for( int q=0; q<2; q++ ) {
+    if( n[q]>=2 && n[q]<=small_max ) seg_sort_small( perm, b[q], n[q] );
+    unsigned big = __ballot_sync( 0xffffffffu, n[q]>small_max );
+    while( big ) {
+      const int src = __ffs( big )-1; big &= big-1;
+      seg_sort_warp( perm, __shfl_sync( 0xffffffffu, b[q], src ), __shfl_sync( 0xffffffffu, n[q], src ), lane, s[w], big_scratch );
+    }
+  }
+}
+
+static int seg_sort_enabled() {
+  static int on = -1;
+  if( on<0 ) { const char * e = getenv( "VPIC_B200_SEG_SORT" ); on = ( e && e[0]=='0' ) ? 0 : 1; }
+  return on;
+}
+
+// regions longer than this are ordered by a warp (VPIC_B200_SEG_SMALL lowers it so that tests reach that path)
+static int seg_small_max() {
+  static int n = -1;
+  if( n<0 ) { const char * e = getenv( "VPIC_B200_SEG_SMALL" ); n = e ? atoi( e ) : SEG_SMALL; if( n<1 ) n = 1; if( n>SEG_SMALL ) n = SEG_SMALL; }
+  return n;
+}
+
 static int lazy_sort_enabled() {
   static int on = -1;
   if( on<0 ) { const char * e = getenv( "VPIC_B200_LAZY_SORT" ); on = ( e && e[0]=='0' ) ? 0 : 1; }
@@ -402,11 +587,40 @@ extern "C" void sort_p( vpb_species_t * sp ) {
       VPB_CUDA( cudaMalloc( &m->d_keys, sizeof(int)*m->cap_p ) ); m->cap_keys = m->cap_p; m->keys_valid = m->keys_patchable = false;
     }
     sort_spare( m->cap_p );
+    if( !m->d_partition_alt && seg_sort_enabled() ) VPB_CUDA( cudaMalloc( &m->d_partition_alt, sizeof(int)*( (size_t)nv + 1 ) ) );
   }
-  // scratch: keys[np] perm[np] count[nv+1] next[nv+1] tiles big[2np]
+  // scratch: keys[np] perm[np] count[nv+1] next[nv+1] tiles big[2np]   (segment sort: five arrays of nv+1, tiles, big)
   const size_t npa = ( (size_t)np + 31 ) & ~(size_t)31, nva = ( (size_t)nv + 1 + 31 ) & ~(size_t)31;
   const size_t ntile = (size_t)div_up( nv+1, SCAN_TILE ) + 32;
-  int * base = (int *)scratch( sizeof(int)*( 2*npa + 2*nva + ntile + 2*npa + 64 ) );
+  const size_t need_generic = 2*npa + 2*nva + ntile + 2*npa + 64, need_seg = 5*nva + ntile + 2*npa + 64;
+  int * base = (int *)scratch( sizeof(int)*( need_generic>need_seg ? need_generic : need_seg ) );
+  const bool seg = lazy && np>0 && m->keys_valid && m->d_keys && m->home_valid && seg_sort_enabled();
+  if( seg ) {
+    // the array still has the order of the last sort and advance_p / boundary_p left the keys: deterministic ranks
+    if( m->cap_perm<m->cap_p ) {
+      VPB_CUDA( cudaStreamSynchronize( r.stream ) );
+      if( m->d_perm ) VPB_CUDA( cudaFree( m->d_perm ) );
+      VPB_CUDA( cudaMalloc( &m->d_perm, sizeof(int)*m->cap_p ) ); m->cap_perm = m->cap_p;
+    }
+    if( !m->d_partition_alt ) VPB_CUDA( cudaMalloc( &m->d_partition_alt, sizeof(int)*( (size_t)nv + 1 ) ) );
+    int * A = base, * B = A + nva, * C = B + nva, * D = C + nva, * E = D + nva, * tiles = E + nva, * big = tiles + ntile;
+    const int * home = m->d_partition; int * part = m->d_partition_alt;
+    const int np_home = m->home_np<np ? m->home_np : np;
+    const int pass_blocks = div_up( nv, 8*SEG_REP );
+    VPB_CUDA( cudaMemsetAsync( A, 0, sizeof(int)*2*nva, r.stream ) );
+    k_seg_pass<false><<< pass_blocks, 256, 0, r.stream >>>( m->d_keys, home, nv, np_home, A, B, C, nullptr, nullptr );
+    if( np>np_home ) { k_seg_tail<false><<< div_up( np-np_home, 256 ), 256, 0, r.stream >>>( m->d_keys, np_home, np, B, nullptr ); r.launches++; }
+    k_seg_sum<<< div_up( nv+1, 256 ), 256, 0, r.stream >>>( A, B, C, D, nv );
+    exclusive_scan( D, part, E, tiles, nv+1 );
+    k_seg_prep<<< div_up( nv, 256 ), 256, 0, r.stream >>>( part, A, B, C, nv );
+    k_seg_pass<true><<< pass_blocks, 256, 0, r.stream >>>( m->d_keys, home, nv, np_home, A, B, C, E, m->d_perm );
+    if( np>np_home ) { k_seg_tail<true><<< div_up( np-np_home, 256 ), 256, 0, r.stream >>>( m->d_keys, np_home, np, B, m->d_perm ); r.launches++; }
+    k_seg_fix<<< div_up( nv, 32*FIX_WARPS ), 32*FIX_WARPS, 0, r.stream >>>( part, A, C, nv, np, m->d_perm, seg_small_max(), big );
+    VPB_CHECK_LAUNCH(); r.launches += 5;
+    m->d_partition_alt = m->d_partition; m->d_partition = part;
+    m->perm_pending = true;
+    r.sorts_from_keys++; r.seg_sorts++;
+  } else {
   int * keys = base, * perm = keys + npa, * count = perm + npa, * next = count + nva, * tiles = next + nva, * big = tiles + ntile;
   VPB_CUDA( cudaMemsetAsync( count, 0, sizeof(int)*( (size_t)nv+1 ), r.stream ) );
   if( np>0 ) {
@@ -437,14 +651,17 @@ extern "C" void sort_p( vpb_species_t * sp ) {
     }
     VPB_CHECK_LAUNCH(); r.launches += 2;
   }
+  }
   m->partition_dev_valid = true;
   const bool keep = m->perm_pending;
   mark_dev_written( m );
   m->perm_pending = keep;
+  m->home_valid = true; m->home_np = np;     // d_partition describes the order the array has (once the gather ran)
   if( r.coherence==VPB_COHERENCE_STRICT ) to_host( m );
 }
 
 extern "C" long long vpic_b200_sorts_from_keys( void ) { return rt().sorts_from_keys; }
+extern "C" long long vpic_b200_segment_sorts( void ) { return rt().seg_sorts; }
 
 // Number of particles that violate "sorted by voxel, partition[] consistent".
 // Meaningful right after sort_p (0 expected).  Test / diagnostic entry point.

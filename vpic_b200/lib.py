@@ -40,7 +40,7 @@ def load_b200():
         "vpic_b200_init": (i, [i, i, i]), "vpic_b200_finalize": (None, []), "vpic_b200_trim": (None, []),
         "vpic_b200_set_world": (None, [i, i]), "vpic_b200_comm_unique_id": (i, [_P, i]),
         "vpic_b200_comm_init": (None, [_P, i]), "vpic_b200_comm_ready": (i, []),
-        "vpic_b200_comm_mailbox_record": (i, [_P, i]), "vpic_b200_comm_init_handles": (None, [_P, i]), "vpic_b200_comm_transport": (i, []), "vpic_b200_sort_violations": (C.c_longlong, [_P]), "vpic_b200_sorts_from_keys": (C.c_longlong, []),
+        "vpic_b200_comm_mailbox_record": (i, [_P, i]), "vpic_b200_comm_init_handles": (None, [_P, i]), "vpic_b200_comm_transport": (i, []), "vpic_b200_sort_violations": (C.c_longlong, [_P]), "vpic_b200_sorts_from_keys": (C.c_longlong, []), "vpic_b200_segment_sorts": (C.c_longlong, []),
         "vpic_b200_set_coherence": (None, [i]), "vpic_b200_set_deposit_mode": (None, [i]),
         "vpic_b200_set_reference_pipelines": (None, [i]),
         "vpic_b200_abi_check": (i, [i] * 6),
