@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", default="512x256x256", help="cells per GPU")
     ap.add_argument("--ppc", type=int, default=32, help="particles per cell per species")
-    ap.add_argument("--sort-interval", default="3,12", help="steps between sorts: one value, or electron,ion (species_t::sort_interval is per "
+    ap.add_argument("--sort-interval", default="3,8", help="steps between sorts: one value, or electron,ion (species_t::sort_interval is per "
                     "species; the thermal electrons leave their cells 10 x faster than the ions and the lazy sort_p is cheap)")
     ap.add_argument("--e2e-cells", default="256x128x128")
     ap.add_argument("--e2e-sort-interval", default="8", help="sort cadence of the e2e leg (host-resident particles: every sort_p is a full "

@@ -20,5 +20,5 @@ M=dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum,lts__t_secto
 ncu --metrics $M --clock-control none -k regex:k_advance_p --launch-skip 6 -c 6 --csv --log-file $O/${TAG}_fullsize_advance_p.csv $CMD > $O/${TAG}_ncu_fs.log 2>&1; echo "full-size counters rc=$?"
 C128="python bench.py --cells 128x128x128 --steps 3 --warmup 3 --no-cpu --no-e2e --no-yee --no-c1 --no-decks"
 ncu --set full --clock-control none --import-source on -k regex:'k_advance_p' --launch-skip 6 -c 4 -o $O/${TAG}_ap128 -f $C128 > $O/${TAG}_ncu_ap128.log 2>&1; echo "ncu advance_p 128 rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:'k_sort|k_hist|k_scan' --launch-skip 10 -c 10 -o $O/${TAG}_sort128 -f $C128 > $O/${TAG}_ncu_sort128.log 2>&1; echo "ncu sort 128 rc=$?"
+ncu --set full --clock-control none --import-source on -k regex:'k_sort|k_hist|k_scan|k_seg' --launch-skip 12 -c 12 -o $O/${TAG}_sort128 -f $C128 > $O/${TAG}_ncu_sort128.log 2>&1; echo "ncu sort 128 rc=$?"
 ls -la $O | grep ${TAG}
