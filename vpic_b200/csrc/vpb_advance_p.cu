@@ -436,6 +436,7 @@ bool advance_p_streamed( SpeciesMirror * ms, AccMirror * ma, InterpMirror * mi, 
 } // namespace
 
 extern "C" void advance_p( vpb_species_t * sp, vpb_accumulator_array_t * aa, const vpb_interpolator_array_t * ia ) {
+  VPB_TRACE_CALL( "advance_p" );
   if( !sp || !aa || !ia || sp->g!=aa->g || sp->g!=ia->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
   SpeciesMirror * ms = mirror( sp );

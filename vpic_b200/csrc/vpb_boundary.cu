@@ -476,22 +476,27 @@ constexpr int MIN_NP = 128;
 void resize_like_reference( SpeciesMirror * m, int max_inj ) {
   vpb_species_t * sp = m->host;
   if( !sp->p ) return;
+  // what the host arrays hold that is worth carrying over: the elements in use, unless the device copy is the
+  // current one (RESIDENT), in which case the host array is a stale mirror
+  // (STRICT keeps everything: its sparse path patches single rows of the host array afterwards)
+  const bool stale = rt().coherence==VPB_COHERENCE_RESIDENT && m->dev_valid && !m->host_valid;
+  const size_t keep_p = stale ? 0 : (size_t)sp->max_np, keep_pm = (size_t)sp->max_nm;
   int n = m->np + max_inj;
   if( n>sp->max_np ) {
     n += 0.3125*n;
     VPB_WARNING( "Resizing local %s particle storage from %i to %i", sp->name, sp->max_np, n );
-    host_resize_particles( sp, (size_t)n );
+    host_resize_particles( sp, (size_t)n, keep_p );
   } else if( sp->max_np>MIN_NP && n<( sp->max_np>>1 ) ) {
     n += 0.125*n;
     if( n<MIN_NP ) n = MIN_NP;
     VPB_WARNING( "Resizing (shrinking) local %s particle storage from %i to %i", sp->name, sp->max_np, n );
-    host_resize_particles( sp, (size_t)n );
+    host_resize_particles( sp, (size_t)n, keep_p );
   }
   int nm = m->nm + max_inj;
   if( nm>sp->max_nm && sp->pm ) {
     nm += 0.3125*nm;
     VPB_WARNING( "This happened.  Resizing local %s mover storage from %i to %i based on not enough movers", sp->name, sp->max_nm, nm );
-    host_resize_movers( sp, (size_t)nm );
+    host_resize_movers( sp, (size_t)nm, keep_pm );
   }
   mirror( sp );                       // device capacities follow max_np / max_nm
 }
@@ -637,6 +642,7 @@ static void exchange_counts( const GridMirror * gm, int * n_recv ) {
 }
 
 extern "C" void boundary_p( void * pbc_list, vpb_species_t * sp_list, vpb_field_array_t * fa, vpb_accumulator_array_t * aa ) {
+  VPB_TRACE_CALL( "boundary_p" );
   if( !sp_list ) return;                                        // boundary_p.cc:77
   if( !fa || !aa || sp_list->g!=aa->g || fa->g!=aa->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();

@@ -445,6 +445,7 @@ extern "C" {
 
 // rho_p.cc:22-112
 void accumulate_rho_p( vpb_field_array_t * fa, const vpb_species_t * sp ) {
+  VPB_TRACE_CALL( "accumulate_rho_p" );
   if( !fa || !sp || fa->g!=sp->g ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
   FieldMirror * m = field_on_device( fa );

@@ -60,7 +60,7 @@ namespace vpb {
 // arrays of a species made by vpic_b200_new_species are this library's; any
 // other species belongs to the host program and is resized with the host
 // program's allocator (the reference's MALLOC_ALIGNED / FREE_ALIGNED).
-static void * host_array_resize( vpb_species_t * sp, void * old, size_t old_bytes, size_t new_bytes ) {
+static void * host_array_resize( vpb_species_t * sp, void * old, size_t old_bytes, size_t new_bytes, size_t keep_bytes ) {
   const bool ours = own_species().count( sp )!=0;
   void * np_ = nullptr;
   if( ours ) np_ = alloc_aligned( new_bytes, 128 );
@@ -68,17 +68,21 @@ static void * host_array_resize( vpb_species_t * sp, void * old, size_t old_byte
     util_malloc_aligned( "libvpic_b200: resizing storage of a species failed (%lu bytes, %lu aligned)", &np_, new_bytes, 128 );
   else VPB_ERROR( "species \"%s\": its arrays were not allocated by this library and the host program has no "
                   "util_malloc_aligned / util_free_aligned to resize them with; raise max_np / max_nm", sp->name );
-  memcpy( np_, old, old_bytes<new_bytes ? old_bytes : new_bytes );
+  // (keep_bytes: how much of the old array means anything -- the elements in use, or nothing at all when the
+  //  device copy is the current one: RESIDENT runs do not copy gigabytes of stale particles around)
+  size_t n = old_bytes<new_bytes ? old_bytes : new_bytes;
+  if( keep_bytes<n ) n = keep_bytes;
+  if( n ) memcpy( np_, old, n );
   unpin_host( old );
   if( ours ) free( old ); else { void * o = old; util_free_aligned( &o ); }
   return np_;
 }
-void host_resize_particles( vpb_species_t * sp, size_t n ) {
-  sp->p = (vpb_particle_t *)host_array_resize( sp, sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np, sizeof(vpb_particle_t)*n );
+void host_resize_particles( vpb_species_t * sp, size_t n, size_t keep ) {
+  sp->p = (vpb_particle_t *)host_array_resize( sp, sp->p, sizeof(vpb_particle_t)*(size_t)sp->max_np, sizeof(vpb_particle_t)*n, sizeof(vpb_particle_t)*keep );
   sp->max_np = (int)n;
 }
-void host_resize_movers( vpb_species_t * sp, size_t n ) {
-  sp->pm = (vpb_particle_mover_t *)host_array_resize( sp, sp->pm, sizeof(vpb_particle_mover_t)*(size_t)sp->max_nm, sizeof(vpb_particle_mover_t)*n );
+void host_resize_movers( vpb_species_t * sp, size_t n, size_t keep ) {
+  sp->pm = (vpb_particle_mover_t *)host_array_resize( sp, sp->pm, sizeof(vpb_particle_mover_t)*(size_t)sp->max_nm, sizeof(vpb_particle_mover_t)*n, sizeof(vpb_particle_mover_t)*keep );
   sp->max_nm = (int)n;
 }
 

@@ -91,6 +91,11 @@ void pin_host( const void * ptr, size_t bytes ) {
     if( it->second>=bytes ) return;
     cudaHostUnregister( const_cast<void *>( ptr ) ); r.pinned_host.erase( it );
   }
+  // Page-locking costs about a second per GB (0.8 s for the 1.7 GB particle array of the LPI deck, against 0.1 s for
+  // the pageable copy it was meant to speed up).  In RESIDENT coherence an array typically crosses the bus once (the
+  // deck's initial state) or now and then (a dump): the first transfer of an array goes pageable, a second one
+  // says the host program syncs this array repeatedly and registers it.  STRICT / TRACKED move the arrays every step.
+  if( r.coherence==VPB_COHERENCE_RESIDENT && r.host_touches[ptr]++<1 ) return;
   track_disarm( ptr );               // registration wants writable pages
   if( cudaHostRegister( const_cast<void *>( ptr ), bytes, cudaHostRegisterDefault )==cudaSuccess ) r.pinned_host[ptr] = bytes;
   else (void)cudaGetLastError();     // already registered by the host program, or not lockable: copies still work
@@ -98,6 +103,7 @@ void pin_host( const void * ptr, size_t bytes ) {
 void unpin_host( const void * ptr ) {
   Runtime & r = rt();
   track_disarm( ptr );
+  r.host_touches.erase( ptr );
   auto it = r.pinned_host.find( ptr );
   if( it==r.pinned_host.end() ) return;
   if( cudaHostUnregister( const_cast<void *>( ptr ) )!=cudaSuccess ) (void)cudaGetLastError();

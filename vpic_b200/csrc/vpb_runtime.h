@@ -11,6 +11,7 @@
 
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <ctime>
 #include <cstdlib>
 #include <cstdint>
 #include <unordered_map>
@@ -192,6 +193,7 @@ struct Runtime {
   long long sorts_from_keys = 0;      // lazy sort_p calls that took the voxel keys advance_p / boundary_p left (4 B per particle read)
   long long h2d_bytes = 0, d2h_bytes = 0;   // host<->device traffic issued by the entry points
   std::unordered_map<const void *, size_t>          pinned_host;   // host arrays registered with cudaHostRegister
+  std::unordered_map<const void *, int>             host_touches;  // RESIDENT: transfers seen per host array (pin_host)
   std::unordered_map<const void *, GridMirror *>    grids;
   std::unordered_map<const void *, FieldMirror *>   fields;
   std::unordered_map<const void *, InterpMirror *>  interps;
@@ -277,8 +279,8 @@ void comm_allsum_d( double * v, int n );
 bool comm_ready();
 void comm_shutdown();
 void release_boundary_buffers();
-void host_resize_particles( vpb_species_t * sp, size_t n );   // boundary_p.cc:346-394 for host-resident arrays
-void host_resize_movers( vpb_species_t * sp, size_t n );
+void host_resize_particles( vpb_species_t * sp, size_t n, size_t keep );   // boundary_p.cc:346-394 for host-resident arrays; keep = elements whose contents matter
+void host_resize_movers( vpb_species_t * sp, size_t n, size_t keep );
 void exclusive_scan( const int * in, int * out, int * out2, int * tmp, int n );
 // field boundary machinery shared by vpb_fields.cu and vpb_divclean.cu
 bool face_is_remote( const GridMirror * gm, int X, int side );
@@ -303,5 +305,22 @@ inline void d2h( void * dst, const void * src, size_t bytes, cudaStream_t st ) {
 }
 
 inline int div_up( long long a, long long b ) { return (int)( (a+b-1)/b ); }
+
+// VPIC_B200_TRACE_CALLS=ms: one line on stderr for every traced entry point call that took at least that many
+// milliseconds of host wall time (first-touch uploads, page-locking, allocations: what a deck's start-up pays)
+struct CallTrace {
+  const char * name; timespec t0; double min_ms;
+  explicit CallTrace( const char * n ) : name( n ) {
+    static const double thr = [](){ const char * e = getenv( "VPIC_B200_TRACE_CALLS" ); return e ? atof( e ) : -1.0; }();
+    min_ms = thr; if( min_ms>=0 ) clock_gettime( CLOCK_MONOTONIC, &t0 );
+  }
+  ~CallTrace() {
+    if( min_ms<0 ) return;
+    timespec t1; clock_gettime( CLOCK_MONOTONIC, &t1 );
+    const double ms = ( t1.tv_sec-t0.tv_sec )*1e3 + ( t1.tv_nsec-t0.tv_nsec )*1e-6;
+    if( ms>=min_ms ) fprintf( stderr, "[vpic_b200] %s: %.2f ms\n", name, ms );
+  }
+};
+#define VPB_TRACE_CALL( name ) vpb::CallTrace vpb_call_trace_( name )
 
 } // namespace vpb

@@ -569,6 +569,7 @@ using namespace vpb;
 //    costs nothing.  If the preceding advance_p left the voxel keys (d_keys), the 32 B records are not read
 //    here at all.  Whatever else touches the particles first carries the permutation out (materialize_sort).
 extern "C" void sort_p( vpb_species_t * sp ) {
+  VPB_TRACE_CALL( "sort_p" );
   if( !sp ) VPB_ERROR( "Bad args" );
   Runtime & r = rt();
   SpeciesMirror * m = mirror( sp );
