@@ -492,7 +492,8 @@ def deck_e2e():
     process (host-side particle loading included -- identical on both sides)."""
     cores = len(os.sched_getaffinity(0))
     out = {"cpu_threads": cores, "cpu_build": "reference V4+V8 AVX2 (oracle/_ref/libvpic_ref_simd.so)",
-           "gpu_mode": "VPIC_B200_COHERENCE=resident VPIC_B200_DEPOSIT=fast, unmodified reference driver"}
+           "gpu_mode": "VPIC_B200_COHERENCE=resident VPIC_B200_DEPOSIT=fast, unmodified reference driver",
+           "gpu_unmodified_deck_mode": "the deck as shipped (no sync lines), VPIC_B200_COHERENCE=tracked VPIC_B200_DEPOSIT=fast"}
     import tempfile
     stages = ("sort_p", "advance_p", "boundary_p", "unload_accumulator", "advance_b", "advance_e", "load_interpolator",
               "clear_accumulators", "reduce_accumulators", "clear_jf", "synchronize_jf", "clear_rhof", "accumulate_rho_p",
@@ -505,8 +506,14 @@ def deck_e2e():
             out[deck] = {"unavailable": "oracle/_ref executables not built (needs /root/reference at build time)"}
             continue
         res = {"workload": what, "particles": npart, "steps": steps}
-        for side, exe, argv, env in (("gpu", gpu_exe, ["--tpp", "1"], dict(VPIC_B200_COHERENCE="resident", VPIC_B200_DEPOSIT="fast", VPIC_B200_REPORT="1")),
-                                     ("cpu", cpu_exe, ["--tpp", str(cores)], {})):
+        # third arm: the deck exactly as the reference ships it (no sync call inserted), TRACKED coherence: every call
+        # leaves the host arrays current, arrays the deck did not write are not uploaded again
+        plain_exe = os.path.join(ROOT, "oracle", "_ref", f"deckrun_{deck}_b200")
+        sides = [("gpu", gpu_exe, ["--tpp", "1"], dict(VPIC_B200_COHERENCE="resident", VPIC_B200_DEPOSIT="fast", VPIC_B200_REPORT="1")),
+                 ("cpu", cpu_exe, ["--tpp", str(cores)], {})]
+        if os.path.exists(plain_exe):
+            sides.append(("gpu_unmodified_deck", plain_exe, ["--tpp", "1"], dict(VPIC_B200_COHERENCE="tracked", VPIC_B200_DEPOSIT="fast", VPIC_B200_REPORT="1")))
+        for side, exe, argv, env in sides:
             with tempfile.TemporaryDirectory() as d:
                 e = dict(os.environ, **env)
                 e["LD_LIBRARY_PATH"] = ":".join(["/usr/local/cuda/lib64", e.get("LD_LIBRARY_PATH", "")])
@@ -537,6 +544,9 @@ def deck_e2e():
                          "stages_s": {k: v[0] for k, v in sorted(tab.items(), key=lambda kv: -kv[1][0])[:8]},
                          "last_energies_line": en[-1] if en else None}
         g, c = res.get("gpu", {}), res.get("cpu", {})
+        u = res.get("gpu_unmodified_deck", {})
+        if u.get("wall_s") and c.get("wall_s"):
+            res["speedup_wall_unmodified_deck_tracked"] = round(c["wall_s"] / u["wall_s"], 2)
         if g.get("step_stages_s") and c.get("step_stages_s"):
             res["speedup_step_stages"] = round(c["step_stages_s"] / g["step_stages_s"], 2)
             res["speedup_wall"] = round(c["wall_s"] / g["wall_s"], 2)
