@@ -4,17 +4,28 @@
 // particles grouped by voxel in ascending voxel order, ORIGINAL ORDER KEPT
 // inside each voxel, partition[v] = first index of voxel v).
 //
-// Device algorithm (all hand-written, no CUB):
-//   1. keys[i] = p[i].i and a voxel histogram (warp-aggregated atomics),
-//   2. exclusive scan of the histogram -> partition[],
-//   3. scatter the particle INDICES into their voxel's segment (atomic slots;
-//      order inside a segment is arbitrary at this point),
-//   4. the warp that owns a voxel ranks its segment ascending (this is what
-//      makes the sort stable and run-to-run deterministic) and, in the same
-//      kernel, copies the 32 B particles to their final places in the spare
-//      buffer (2 x 128-bit loads / stores each); buffers are swapped.
+// Device algorithms (all hand-written, no CUB); which one runs is decided per call in sort_p() below:
+//
+//   generic, immediate (STRICT coherence or PARITY deposit)
+//     1. keys[i] = p[i].i and a voxel histogram (warp-aggregated atomics),
+//     2. exclusive scan of the histogram -> partition[],
+//     3. scatter the particle INDICES into their voxel's segment (atomic slots;
+//        order inside a segment is arbitrary at this point),
+//     4. the warp that owns a voxel ranks its segment ascending (this is what
+//        makes the sort stable and run-to-run deterministic) and, in the same
+//        kernel, copies the 32 B particles to their final places in the spare
+//        buffer (2 x 128-bit loads / stores each); buffers are swapped.
+//   generic, lazy (RESIDENT coherence + FAST deposit)
+//     the same, but step 4 leaves the ordered indices in d_perm and copies nothing:
+//     the next advance_p gathers through them (k_advance_p<GATHER>); step 1 reads
+//     the 4-byte keys the previous advance_p left when they are there.
+//   segment sort (lazy, from a species' second sort on)
+//     deterministic ranks from the order the previous sort left: see the comment
+//     above k_seg_pass.
+//
 // Algorithmic traffic: 4 B key + 32 B read + 32 B write per particle (SURVEY
-// 8d: 68 B); this version moves ~120 B because of the index passes.
+// 8d: 68 B).  The immediate sort moves ~120 B because of the index passes; the
+// lazy ones move 20 - 25 B themselves and leave the 64 B copy to the push.
 #include "vpb_runtime.h"
 #include "vpb_sortutil.cuh"
 
