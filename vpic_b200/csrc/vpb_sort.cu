@@ -409,7 +409,10 @@ k_seg_pass( const int * __restrict__ keys, const int * __restrict__ home, int nv
   // stayers' base after the prep pass).
   int mine = 0;
   if( PLACE && lane<SEG_REP && v0+lane<nv ) mine = A[v0+lane];
-  int r0 = 0;                       // segment that contains the first position of the current row (uniform)
+  const int pl_next = __shfl_down_sync( 0xffffffffu, pl, 1 );          // lane r: where segment r ends
+  const unsigned lt = ( 1u<<lane )-1u;
+  // (The count pass ran at 91 % issue utilisation with a loop over the segments of every row: everything below is
+  //  branch-free per row -- a three-step binary search over the nine boundaries held in lanes 0..8, one ballot.)
   for( int o=b0; o<e0; o+=32*SEG_ROWS ) {
     int k[SEG_ROWS], slot[SEG_ROWS];
     unsigned strays = 0;            // rows in which this lane holds a stray (PLACE: its slot is on its way in slot[])
@@ -420,23 +423,29 @@ k_seg_pass( const int * __restrict__ keys, const int * __restrict__ home, int nv
       const int ps = o + 32*u, pos = ps + lane;
       slot[u] = 0;
       if( ps>=e0 ) break;
-      while( r0+1<SEG_REP && ps>=__shfl_sync( 0xffffffffu, pl, r0+1 ) ) r0++;
-      int h = r0, rmax = r0;
-      for( int t=r0+1; t<SEG_REP; t++ ) {
-        const int nb = __shfl_sync( 0xffffffffu, pl, t );
-        if( nb>=ps+32 || nb>=e0 ) break;
-        h += pos>=nb; rmax = t;
-      }
+      // home segment of the position: the last boundary <= pos (empty segments are skipped by construction)
+      int h = 0, bnd = b0, t;
+      t = __shfl_sync( 0xffffffffu, pl, 4 );     if( pos>=t ) { h = 4;  bnd = t; }
+      t = __shfl_sync( 0xffffffffu, pl, h+2 );   if( pos>=t ) { h += 2; bnd = t; }
+      t = __shfl_sync( 0xffffffffu, pl, h+1 );   if( pos>=t ) { h += 1; bnd = t; }
       const bool valid = k[u]>=0;
       const bool stay = valid && k[u]==v0+h;
-      for( int r=r0; r<=rmax; r++ ) {
-        const unsigned m = __ballot_sync( 0xffffffffu, stay && h==r );
-        if( !m ) continue;
-        if( PLACE ) {
-          const int base = __shfl_sync( 0xffffffffu, mine, r );
-          if( stay && h==r ) perm[ base + __popc( m & ( ( 1u<<lane )-1u ) ) ] = pos;
-        }
-        if( lane==r ) mine += __popc( m );
+      const unsigned sm = __ballot_sync( 0xffffffffu, stay );
+      if( PLACE ) {
+        // rank among the stayers of the same segment in this row: they sit in the lanes from the segment's first
+        // position on (homes are monotone along a row)
+        const int first = bnd - ps;
+        const unsigned same = first<=0 ? 0xffffffffu : ( 0xffffffffu<<first );
+        const int base = __shfl_sync( 0xffffffffu, mine, h );
+        if( stay ) perm[ base + __popc( sm & lt & same ) ] = pos;
+      }
+      {
+        // lane r adds the row's stayers of segment r: the lanes [pl - ps, pl_next - ps) of the row
+        int lo = pl - ps, hi = pl_next - ps;
+        lo = lo<0 ? 0 : lo; hi = hi>32 ? 32 : hi;
+        unsigned m = 0;
+        if( lane<SEG_REP && hi>lo ) m = ( hi==32 ? 0xffffffffu : ( ( 1u<<hi )-1u ) ) & ~( ( 1u<<lo )-1u );
+        mine += __popc( sm & m );
       }
       if( valid && !stay ) {
         const bool below = k[u]>v0+h;                 // its home is below the voxel it is in now
